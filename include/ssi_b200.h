@@ -1,0 +1,110 @@
+/*
+ * ssi_b200 — C ABI of the B200-native (sm_100a) fused tied-LM-head + chunked-cross-entropy path of
+ * anilkeshwani/speech-integration.  This header is the drop-in boundary: plain pointers and sizes, no
+ * torch types.  Every entry point only ENQUEUES work on `stream` (a cudaStream_t passed as void*), never
+ * synchronises the device and never allocates; all pointers are device pointers owned by the caller.
+ *
+ * Return convention: 0 = OK; negative = argument / shape / alignment error detected on the host before
+ * any launch (text via ssi_b200_last_error(), thread-local); positive = cudaError_t of a failed launch.
+ * There is no CPU fallback and no multi-backend dispatch: a device that is not sm_100 is a hard error.
+ *
+ * Layouts (all row-major, contiguous):
+ *   X  [N, D]  bf16  final (normed) hidden states, N = B*S token rows
+ *   W  [V, D]  bf16  tied embedding / LM-head weight (tok_embeddings.weight)
+ *   labels [N] int64 already shifted as ssi/loss.py:16 does; ignore_index rows contribute nothing
+ *   dX [N, D]  bf16 ; dW [V, D] bf16 (the tied weight's .grad buffer)
+ * Requirements: D % 64 == 0, all base pointers 16-byte aligned (TMA), N >= 1, V >= 1.
+ *
+ * Reference interfaces replaced (paths relative to the reference checkout; tt/ = third_party/torchtune/):
+ *   ssi_b200_lmhead_ce_fwd   <- tt/torchtune/modules/transformer.py:499-502 (chunked_output: F.linear per chunk,
+ *                               tt/torchtune/modules/tied_linear.py:25) + tt/torchtune/modules/loss/
+ *                               ce_chunked_output_loss.py:45-83 (CEWithChunkedOutputLoss.forward)
+ *   ssi_b200_lmhead_ce_bwd   <- autograd of the above as driven by ssi/trainer.py:393-394
+ *   ssi_b200_embedding_grad_scatter <- backward of nn.Embedding built at tt/torchtune/models/llama3_2/
+ *                               _component_builders.py:114 and called at tt/torchtune/modules/transformer.py:628
+ *   ssi_b200_label_shift_count <- ssi/loss.py:16 (label shift) + ssi/trainer.py:391 (token count)
+ */
+#ifndef SSI_B200_H_
+#define SSI_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SSI_B200_ABI_VERSION 100
+
+/* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
+int ssi_b200_version(void);
+
+/* Thread-local text of the last error returned on this thread ("" if none). */
+const char* ssi_b200_last_error(void);
+
+/* Number of tcgen05 / helper kernels launched by this process through the library so far
+ * (used by bench.py for its gpu_launches claim). */
+int64_t ssi_b200_launch_count(void);
+
+/* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. */
+int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes, size_t* bwd_bytes,
+                             size_t* scatter_bytes);
+
+/*
+ * Forward: logits = X * W^T are produced tile by tile in tensor memory and consumed by an online
+ * log-sum-exp epilogue; they never reach HBM.
+ *   lse      [N]  out  fp32 natural-log logsumexp per row (saved for backward)
+ *   loss_out [2]  out  fp32 {sum over valid rows of (lse - z_label), that sum / n_valid}
+ *                      (n_valid == 0 -> loss_out[1] = NaN, as 0/0 in ce_chunked_output_loss.py:83)
+ *   n_valid  [1]  out  int64 count of labels != ignore_index (ce_chunked_output_loss.py:66)
+ */
+int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, int64_t N, int64_t V, int64_t D,
+                           int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* ws,
+                           size_t ws_bytes, void* stream);
+
+/*
+ * Backward: recomputes the logits tiles, forms dlogits = (softmax - onehot) * grad_out / n_valid_total in
+ * bf16 one vocabulary block at a time (bounded scratch inside `ws`), and contracts
+ *   dX = dlogits * W      (overwritten)
+ *   dW (+)= dlogits^T * X (accumulate_dW != 0 adds to the existing buffer, else overwrites)
+ * on the tensor cores.
+ *   grad_out      [1] fp32 device scalar: upstream dL/dloss (ssi/trainer.py:393 multiplies the loss by
+ *                     num_tokens_iter, so this is that count)
+ *   n_valid_total [1] int64 device scalar: divisor of the mean (the local n_valid from forward, or the
+ *                     all-reduced global count under data parallelism)
+ */
+int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, const float* lse,
+                           const float* grad_out, const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                           int64_t ignore_index, void* dX, void* dW, int accumulate_dW, void* ws, size_t ws_bytes,
+                           void* stream);
+
+/*
+ * Tied-embedding gradient: dW[ids[i], :] += dH[i, :] for i in [0, N), ids in [0, V) (ids < 0 or >= V are
+ * skipped).  Rows are grouped by a stable radix sort of the ids and reduced in fp32 by a warp-level
+ * segmented reduction in sorted order (deterministic: no floating-point atomics), one read-modify-write
+ * of each touched dW row.
+ */
+int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
+                                    void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * labels_out[b, s] = labels[b, s+1] for s < S-1, ignore_index for s == S-1 (ssi/loss.py:16);
+ * counts[0] = #(labels != ignore_index) on the UNSHIFTED labels (ssi/trainer.py:391),
+ * counts[1] = the same count on the shifted labels.
+ */
+int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int64_t ignore_index,
+                               int64_t* labels_out, int64_t* counts, void* stream);
+
+/*
+ * Test hook: C[M, N] (fp32, row-major, ldc = N) = A * B^T-style contraction on the same tcgen05 mainloop
+ * the product kernels use.  a_mn_major == 0: A is [M, K] row-major (K contiguous); != 0: A is [K, M]
+ * row-major (M contiguous).  Likewise B: [N, K] or [K, N].  accumulate != 0 adds into C (TMA reduce-add).
+ * Supported (a_mn_major, b_mn_major): (0,0), (1,1), (0,1).
+ */
+int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64_t N, int64_t K, int a_mn_major,
+                        int b_mn_major, int accumulate, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SSI_B200_H_ */

@@ -1,0 +1,494 @@
+// C ABI of libssi_b200.so (see include/ssi_b200.h).  Host side only builds TMA descriptors, picks the
+// tile schedule and enqueues kernels on the caller's stream: no allocation, no synchronisation.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+#include <cuda_bf16.h>
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+
+#include "../../include/ssi_b200.h"
+#include "aux_kernels.cuh"
+#include "gemm.cuh"
+
+namespace {
+
+thread_local char g_err[512] = "";
+std::atomic<long long> g_launches{0};
+
+int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define SSI_CHECK_ARG(cond, ...) \
+  do {                           \
+    if (!(cond)) return fail(-1, __VA_ARGS__); \
+  } while (0)
+
+#define SSI_CUDA(expr)                                                                          \
+  do {                                                                                          \
+    cudaError_t e_ = (expr);                                                                    \
+    if (e_ != cudaSuccess) return fail(static_cast<int>(e_), "%s: %s", #expr, cudaGetErrorString(e_)); \
+  } while (0)
+
+#define SSI_LAUNCH_OK(name)                                                                      \
+  do {                                                                                           \
+    cudaError_t e_ = cudaGetLastError();                                                         \
+    if (e_ != cudaSuccess) return fail(static_cast<int>(e_), "launch %s: %s", name, cudaGetErrorString(e_)); \
+    g_launches.fetch_add(1, std::memory_order_relaxed);                                          \
+  } while (0)
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+struct DeviceInfo {
+  int ok = 0;  // 1 = sm_100, -1 = unusable
+  int sms = 0;
+  int cc_major = 0, cc_minor = 0;
+  char why[256] = "";
+};
+
+int device_info(DeviceInfo** out) {
+  static DeviceInfo infos[64];
+  static std::mutex mu;
+  int dev = 0;
+  SSI_CUDA(cudaGetDevice(&dev));
+  SSI_CHECK_ARG(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  DeviceInfo& d = infos[dev];
+  if (d.ok == 0) {
+    cudaDeviceProp prop;
+    SSI_CUDA(cudaGetDeviceProperties(&prop, dev));
+    d.sms = prop.multiProcessorCount;
+    d.cc_major = prop.major;
+    d.cc_minor = prop.minor;
+    if (prop.major != 10) {
+      d.ok = -1;
+      snprintf(d.why, sizeof(d.why), "device %d is sm_%d%d; ssi_b200 kernels are built for sm_100a only (no fallback)",
+               dev, prop.major, prop.minor);
+    } else {
+      d.ok = 1;
+    }
+  }
+  if (d.ok < 0) return fail(-2, "%s", d.why);
+  *out = &d;
+  return 0;
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 get_encode() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+// 2D row-major tensor [outer, inner] of `esize`-byte elements, 128-byte swizzle, OOB reads -> zeros.
+int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr, uint64_t inner, uint64_t outer,
+              uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer) {
+  auto enc = get_encode();
+  if (!enc) return fail(-3, "cuTensorMapEncodeTiled entry point not available");
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "tensor base %p is not 16-byte aligned", ptr);
+  SSI_CHECK_ARG(row_stride_bytes % 16 == 0, "row stride %llu B is not a multiple of 16",
+                static_cast<unsigned long long>(row_stride_bytes));
+  SSI_CHECK_ARG(box_inner * esize == 128 && box_outer <= 256, "bad TMA box %u x %u", box_inner, box_outer);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(-4, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return 0;
+}
+
+template <int EPI, bool A_MN, bool B_MN>
+int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name) {
+  auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    SSI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::GEMM_SMEM_BYTES));
+    attr_set = true;
+  }
+  const int items = p.tiles_m * p.tiles_n;
+  if (items <= 0) return 0;
+  const int grid = items < sms ? items : sms;
+  kern<<<grid, ssi::GEMM_THREADS, ssi::GEMM_SMEM_BYTES, st>>>(p);
+  SSI_LAUNCH_OK(name);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Schedules
+// ---------------------------------------------------------------------------------------------------
+struct FwdPlan {
+  int64_t n_pad;
+  int tiles_m, vtiles_total, splits, vtiles_per_split, combine_blocks;
+  size_t off_m, off_l, off_z, off_bl, off_bc, bytes;
+};
+
+FwdPlan plan_fwd(int64_t N, int64_t V, int sms) {
+  FwdPlan f;
+  f.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
+  f.tiles_m = static_cast<int>(f.n_pad / ssi::BM);
+  f.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
+  // pick the number of vocabulary splits that minimises the persistent-grid makespan (in tile units)
+  long long best_cost = -1;
+  int best_s = 1;
+  const int max_s = f.vtiles_total < 148 ? f.vtiles_total : 148;
+  for (int s = 1; s <= max_s; ++s) {
+    const int per = static_cast<int>(ceil_div(f.vtiles_total, s));
+    const int s_eff = static_cast<int>(ceil_div(f.vtiles_total, per));
+    if (s_eff != s) continue;
+    const long long items = static_cast<long long>(f.tiles_m) * s;
+    const long long cost = ceil_div(items, sms) * per;
+    if (best_cost < 0 || cost < best_cost) {
+      best_cost = cost;
+      best_s = s;
+    }
+  }
+  f.splits = best_s;
+  f.vtiles_per_split = static_cast<int>(ceil_div(f.vtiles_total, best_s));
+  f.combine_blocks = static_cast<int>(ceil_div(N, ssi::COMBINE_THREADS));
+  size_t o = 0;
+  const size_t part = align_up(static_cast<size_t>(f.splits) * f.n_pad * sizeof(float), 256);
+  f.off_m = o, o += part;
+  f.off_l = o, o += part;
+  f.off_z = o, o += part;
+  f.off_bl = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(float), 256);
+  f.off_bc = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(int), 256);
+  f.bytes = o;
+  return f;
+}
+
+struct BwdPlan {
+  int64_t n_pad;
+  int tiles_m, vtiles_total, nblocks, vtiles_per_block;
+  int64_t vc;  // columns of the dlogits block buffer
+  size_t off_g, off_dxacc, bytes;
+};
+
+BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
+  BwdPlan b;
+  b.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
+  b.tiles_m = static_cast<int>(b.n_pad / ssi::BM);
+  b.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
+  const int64_t target_elems = int64_t(1) << 29;  // 1 GiB of bf16 dlogits per block
+  int64_t tiles = target_elems / b.n_pad / ssi::BN;
+  if (tiles < 4) tiles = 4;
+  if (tiles > b.vtiles_total) tiles = b.vtiles_total;
+  b.nblocks = static_cast<int>(ceil_div(b.vtiles_total, tiles));
+  b.vtiles_per_block = static_cast<int>(ceil_div(b.vtiles_total, b.nblocks));
+  b.vc = static_cast<int64_t>(b.vtiles_per_block) * ssi::BN;
+  size_t o = 0;
+  b.off_g = o, o += align_up(static_cast<size_t>(b.n_pad) * b.vc * 2, 1024);
+  b.off_dxacc = o;
+  if (b.nblocks > 1) o += align_up(static_cast<size_t>(N) * D * sizeof(float), 1024);
+  b.bytes = o;
+  return b;
+}
+
+struct ScatPlan {
+  int blocks, nwarps, passes;
+  size_t off_k0, off_v0, off_k1, off_v1, off_hist, off_partial, off_info, bytes;
+};
+
+ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
+  ScatPlan s;
+  s.blocks = static_cast<int>(ceil_div(N, ssi::SORT_CHUNK));
+  s.nwarps = static_cast<int>(ceil_div(N, 32));
+  int bits = 1;
+  while ((int64_t(1) << bits) <= V) ++bits;  // keys are in [0, V] (V = out-of-range sentinel)
+  s.passes = (bits + 7) / 8;
+  size_t o = 0;
+  const size_t arr = align_up(static_cast<size_t>(N) * 4, 256);
+  s.off_k0 = o, o += arr;
+  s.off_v0 = o, o += arr;
+  s.off_k1 = o, o += arr;
+  s.off_v1 = o, o += arr;
+  s.off_hist = o, o += align_up(static_cast<size_t>(256) * s.blocks * 4, 256);
+  s.off_partial = o, o += align_up(static_cast<size_t>(s.nwarps) * 2 * D * sizeof(float), 256);
+  s.off_info = o, o += align_up(static_cast<size_t>(s.nwarps) * sizeof(ssi::ScatInfo), 256);
+  s.bytes = o;
+  return s;
+}
+
+int check_common(const void* X, const void* W, int64_t N, int64_t V, int64_t D) {
+  SSI_CHECK_ARG(X && W, "null X/W pointer");
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64, "bad shape N=%lld V=%lld D=%lld", (long long)N, (long long)V,
+                (long long)D);
+  SSI_CHECK_ARG(D % 64 == 0, "D=%lld must be a multiple of 64", (long long)D);
+  SSI_CHECK_ARG(N < (int64_t(1) << 30) && V < (int64_t(1) << 30), "N/V too large for 32-bit tile coordinates");
+  return 0;
+}
+
+}  // namespace
+
+// ===================================================================================================
+extern "C" {
+
+int ssi_b200_version(void) { return SSI_B200_ABI_VERSION; }
+
+const char* ssi_b200_last_error(void) { return g_err; }
+
+int64_t ssi_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes, size_t* bwd_bytes,
+                             size_t* scatter_bytes) {
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
+                (long long)V, (long long)D);
+  if (fwd_bytes || bwd_bytes)
+    SSI_CHECK_ARG(D % 64 == 0, "D=%lld must be a multiple of 64 for the LM-head kernels", (long long)D);
+  const int sms = 148;  // the plan (and so the size) must not depend on a device being present
+  if (fwd_bytes) *fwd_bytes = plan_fwd(N, V, sms).bytes;
+  if (bwd_bytes) *bwd_bytes = plan_bwd(N, V, D).bytes;
+  if (scatter_bytes) *scatter_bytes = plan_scatter(N, V, D).bytes;
+  return 0;
+}
+
+int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, int64_t N, int64_t V, int64_t D,
+                           int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* ws,
+                           size_t ws_bytes, void* stream) {
+  if (int r = check_common(X, W, N, V, D)) return r;
+  SSI_CHECK_ARG(labels && lse && loss_out && n_valid && ws, "null pointer argument");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // The split count is sized for 148 SMs so that workspace_bytes() is device independent.
+  const FwdPlan f = plan_fwd(N, V, 148);
+  SSI_CHECK_ARG(ws_bytes >= f.bytes, "forward workspace too small: %zu < %zu", ws_bytes, f.bytes);
+  char* wsb = static_cast<char*>(ws);
+
+  ssi::GemmParams p;
+  memset(&p, 0, sizeof(p));
+  if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, ssi::BM)) return r;
+  if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  p.tiles_m = f.tiles_m;
+  p.tiles_n = f.splits;
+  p.k_blocks = static_cast<int>(D / ssi::BK);
+  p.group_m = f.tiles_m;  // all m-tiles of one split run together: they stream the same W tiles through L2
+  p.labels = labels;
+  p.ignore_index = ignore_index;
+  p.n_rows = static_cast<int>(N);
+  p.vocab = static_cast<int>(V);
+  p.col0 = 0;
+  p.vtiles_per_split = f.vtiles_per_split;
+  p.vtiles_total = f.vtiles_total;
+  p.part_m = reinterpret_cast<float*>(wsb + f.off_m);
+  p.part_l = reinterpret_cast<float*>(wsb + f.off_l);
+  p.part_z = reinterpret_cast<float*>(wsb + f.off_z);
+  p.part_stride = static_cast<int>(f.n_pad);
+  if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse")) return r;
+
+  float* blk_loss = reinterpret_cast<float*>(wsb + f.off_bl);
+  int* blk_cnt = reinterpret_cast<int*>(wsb + f.off_bc);
+  ssi::lse_combine_kernel<<<f.combine_blocks, ssi::COMBINE_THREADS, 0, st>>>(
+      p.part_m, p.part_l, p.part_z, f.splits, p.part_stride, labels, ignore_index, static_cast<int>(N), lse, blk_loss,
+      blk_cnt);
+  SSI_LAUNCH_OK("lse_combine");
+  ssi::loss_finalize_kernel<<<1, 256, 0, st>>>(blk_loss, blk_cnt, f.combine_blocks, loss_out, n_valid);
+  SSI_LAUNCH_OK("loss_finalize");
+  return 0;
+}
+
+int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, const float* lse,
+                           const float* grad_out, const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                           int64_t ignore_index, void* dX, void* dW, int accumulate_dW, void* ws, size_t ws_bytes,
+                           void* stream) {
+  if (int r = check_common(X, W, N, V, D)) return r;
+  SSI_CHECK_ARG(labels && lse && grad_out && n_valid_total && dX && dW && ws, "null pointer argument");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const BwdPlan b = plan_bwd(N, V, D);
+  SSI_CHECK_ARG(ws_bytes >= b.bytes, "backward workspace too small: %zu < %zu", ws_bytes, b.bytes);
+  char* wsb = static_cast<char*>(ws);
+  void* G = wsb + b.off_g;
+  float* dxacc = reinterpret_cast<float*>(wsb + b.off_dxacc);
+  const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
+
+  // tensor maps that do not change across vocabulary blocks
+  CUtensorMap tmX_k, tmX_mn, tmW_k, tmW_mn, tmG_st, tmG_k, tmG_mn, tmdW, tmdX;
+  if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, ssi::BM)) return r;
+  if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  if (int r = make_tmap(&tmW_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmG_st, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, G, b.vc, b.n_pad, b.vc * 2, 64, ssi::BM))
+    return r;
+  tmG_k = tmG_st;  // K-major A operand of dX = G W uses the same {64 v, 128 tok} box
+  if (int r = make_tmap(&tmG_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, G, b.vc, b.n_pad, b.vc * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmdW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dW, D, V, D * 2, 64, ssi::BM)) return r;
+  if (b.nblocks > 1) {
+    if (int r = make_tmap(&tmdX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dxacc, D, N, D * 4, 32, ssi::BM)) return r;
+  } else {
+    if (int r = make_tmap(&tmdX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dX, D, N, D * 2, 64, ssi::BM)) return r;
+  }
+
+  for (int blk = 0; blk < b.nblocks; ++blk) {
+    const int vt0 = blk * b.vtiles_per_block;
+    const int vtn = (b.vtiles_total - vt0) < b.vtiles_per_block ? (b.vtiles_total - vt0) : b.vtiles_per_block;
+    const int v0 = vt0 * ssi::BN;  // first vocabulary row of this block
+
+    // ---- K2a: recompute logits tiles, emit dlogits block G[:, v0 : v0 + vtn*256) in bf16
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmX_k, p.tmB = tmW_k, p.tmC = tmG_st;
+      p.tiles_m = b.tiles_m, p.tiles_n = vtn, p.k_blocks = static_cast<int>(D / ssi::BK);
+      p.group_m = 16;
+      p.b_r0 = v0;
+      p.labels = labels, p.ignore_index = ignore_index;
+      p.n_rows = static_cast<int>(N), p.vocab = static_cast<int>(V), p.col0 = v0;
+      p.lse = lse, p.grad_out = grad_out, p.n_valid = n_valid_total;
+      if (int r = launch_gemm<ssi::EPI_GRAD, false, false>(p, di->sms, st, "lmhead_dlogits")) return r;
+    }
+    // ---- K2b: dW[v0 : v0 + rows) (+)= G^T X   (M = vocabulary rows, N = D, K = tokens)
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmG_mn, p.tmB = tmX_mn, p.tmC = tmdW;
+      const int64_t vrows = (V - v0) < int64_t(vtn) * ssi::BN ? (V - v0) : int64_t(vtn) * ssi::BN;
+      p.tiles_m = static_cast<int>(ceil_div(vrows, ssi::BM));
+      p.tiles_n = d_tiles;
+      p.k_blocks = static_cast<int>(b.n_pad / ssi::BK);
+      p.group_m = 16;
+      p.c_r0 = v0;
+      p.c_reduce = accumulate_dW ? 1 : 0;
+      if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW")) return r;
+    }
+    // ---- K2c: dX (+)= G W[v0 : v0 + vtn*256)   (M = tokens, N = D, K = vocabulary block)
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmG_k, p.tmB = tmW_mn, p.tmC = tmdX;
+      p.tiles_m = b.tiles_m, p.tiles_n = d_tiles;
+      p.k_blocks = vtn * (ssi::BN / ssi::BK);
+      p.group_m = 16;
+      p.b_k0 = v0;
+      p.c_reduce = (blk > 0) ? 1 : 0;
+      if (b.nblocks > 1) {
+        if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX_f32")) return r;
+      } else {
+        if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX_bf16")) return r;
+      }
+    }
+  }
+  if (b.nblocks > 1) {
+    const size_t n4 = static_cast<size_t>(N) * D / 4;
+    const int grid = di->sms * 8;
+    ssi::cast_f32_bf16_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(dxacc),
+                                                    reinterpret_cast<uint2*>(dX), n4);
+    SSI_LAUNCH_OK("cast_dX");
+  }
+  return 0;
+}
+
+int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
+                                    void* ws, size_t ws_bytes, void* stream) {
+  SSI_CHECK_ARG(dH && ids && dW && ws, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
+                (long long)V, (long long)D);
+  SSI_CHECK_ARG(N < (int64_t(1) << 31) && V < (int64_t(1) << 31), "N/V too large");
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dH) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
+                "dH/dW must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const ScatPlan s = plan_scatter(N, V, D);
+  SSI_CHECK_ARG(ws_bytes >= s.bytes, "scatter workspace too small: %zu < %zu", ws_bytes, s.bytes);
+  char* wsb = static_cast<char*>(ws);
+  uint32_t* k[2] = {reinterpret_cast<uint32_t*>(wsb + s.off_k0), reinterpret_cast<uint32_t*>(wsb + s.off_k1)};
+  uint32_t* v[2] = {reinterpret_cast<uint32_t*>(wsb + s.off_v0), reinterpret_cast<uint32_t*>(wsb + s.off_v1)};
+  uint32_t* hist = reinterpret_cast<uint32_t*>(wsb + s.off_hist);
+  const int n = static_cast<int>(N);
+
+  ssi::sort_prepare_kernel<<<static_cast<int>(ceil_div(N, 256)), 256, 0, st>>>(ids, n, V, k[0], v[0]);
+  SSI_LAUNCH_OK("sort_prepare");
+  int cur = 0;
+  for (int pass = 0; pass < s.passes; ++pass) {
+    const int shift = pass * 8;
+    ssi::sort_hist_kernel<<<s.blocks, ssi::SORT_THREADS, 0, st>>>(k[cur], n, shift, hist, s.blocks);
+    SSI_LAUNCH_OK("sort_hist");
+    ssi::sort_scan_kernel<<<1, 1024, 0, st>>>(hist, 256 * s.blocks);
+    SSI_LAUNCH_OK("sort_scan");
+    ssi::sort_scatter_kernel<<<s.blocks, ssi::SORT_THREADS, 0, st>>>(k[cur], v[cur], k[cur ^ 1], v[cur ^ 1], n, shift,
+                                                                     hist, s.blocks);
+    SSI_LAUNCH_OK("sort_scatter");
+    cur ^= 1;
+  }
+  float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
+  ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
+  const int grid = static_cast<int>(ceil_div(s.nwarps, 8));
+  ssi::scatter_reduce_kernel<<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
+                                                   static_cast<uint32_t>(V), static_cast<int>(D),
+                                                   static_cast<__nv_bfloat16*>(dW), partial, info);
+  SSI_LAUNCH_OK("scatter_reduce");
+  ssi::scatter_fixup_kernel<<<grid, 256, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
+                                                  static_cast<int>(D), static_cast<__nv_bfloat16*>(dW));
+  SSI_LAUNCH_OK("scatter_fixup");
+  return 0;
+}
+
+int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int64_t ignore_index,
+                               int64_t* labels_out, int64_t* counts, void* stream) {
+  SSI_CHECK_ARG(labels && labels_out && counts, "null pointer argument");
+  SSI_CHECK_ARG(B >= 1 && S >= 1, "bad shape B=%lld S=%lld", (long long)B, (long long)S);
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  SSI_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), st));
+  const int64_t total = B * S;
+  int grid = static_cast<int>(ceil_div(total, 256));
+  if (grid > di->sms * 8) grid = di->sms * 8;
+  ssi::label_shift_count_kernel<<<grid, 256, 0, st>>>(labels, B, S, ignore_index, labels_out,
+                                                      reinterpret_cast<unsigned long long*>(counts));
+  SSI_LAUNCH_OK("label_shift_count");
+  return 0;
+}
+
+int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64_t N, int64_t K, int a_mn_major,
+                        int b_mn_major, int accumulate, void* stream) {
+  SSI_CHECK_ARG(A && B && C, "null pointer argument");
+  SSI_CHECK_ARG(M >= 1 && N >= 1 && K >= 1, "bad shape");
+  SSI_CHECK_ARG(K % 8 == 0 && M % 8 == 0 && N % 8 == 0, "M, N, K must be multiples of 8 (16-byte TMA strides)");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ssi::GemmParams p;
+  memset(&p, 0, sizeof(p));
+  if (!a_mn_major) {
+    if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, K, M, K * 2, 64, ssi::BM)) return r;
+  } else {
+    if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, M, K, M * 2, 64, 64)) return r;
+  }
+  if (!b_mn_major) {
+    if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, K, N, K * 2, 64, ssi::BN)) return r;
+  } else {
+    if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, N, K, N * 2, 64, 64)) return r;
+  }
+  if (int r = make_tmap(&p.tmC, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, C, N, M, N * 4, 32, ssi::BM)) return r;
+  p.tiles_m = static_cast<int>(ceil_div(M, ssi::BM));
+  p.tiles_n = static_cast<int>(ceil_div(N, ssi::BN));
+  p.k_blocks = static_cast<int>(ceil_div(K, ssi::BK));
+  p.group_m = 8;
+  p.c_reduce = accumulate ? 1 : 0;
+  if (!a_mn_major && !b_mn_major) return launch_gemm<ssi::EPI_F32, false, false>(p, di->sms, st, "debug_gemm_kk");
+  if (a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "debug_gemm_mm");
+  if (!a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "debug_gemm_km");
+  return fail(-1, "unsupported operand majors (a_mn=%d, b_mn=%d)", a_mn_major, b_mn_major);
+}
+
+}  // extern "C"

@@ -1,0 +1,435 @@
+// Persistent, warp-specialised tcgen05 contraction used by every tensor-core stage of the path:
+//   EPI_LSE   logits tile -> online log-sum-exp partials              (forward,  K1)
+//   EPI_GRAD  logits tile -> dlogits block G in bf16                  (backward, K2a)
+//   EPI_BF16  accumulator -> bf16 tile store / reduce-add             (dW = G^T X, K2b; dX when one block)
+//   EPI_F32   accumulator -> fp32 tile store / reduce-add             (dX accumulation, K2c; test hook)
+// One CTA per SM: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM owner), warps 2..5 = epilogue
+// (one thread per accumulator row).  128x256 fp32 accumulators, double-buffered in the 512 TMEM columns, so
+// the epilogue of tile j overlaps the MMAs of tile j+1.  Operands are staged by TMA with 128-byte swizzle.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <cstdint>
+
+#include "ptx.cuh"
+
+namespace ssi {
+
+constexpr int BM = 128;
+constexpr int BN = 256;
+constexpr int BK = 64;
+constexpr int UMMA_K = 16;
+constexpr int STAGES = 4;
+constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
+constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
+constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+constexpr int MN_BOX_BYTES = 64 * BK * 2;  // one {64 MN, 64 K} TMA box of an MN-major operand = 8 KiB
+constexpr int EPI_BUF_BYTES = 128 * 128;   // 128 rows x 128 B staging tile for TMA stores
+constexpr int NUM_EPI_BUFS = 2;
+constexpr int SMEM_BAR_BYTES = 256;
+constexpr int GEMM_SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + NUM_EPI_BUFS * EPI_BUF_BYTES + SMEM_BAR_BYTES;
+constexpr int GEMM_THREADS = 192;
+constexpr int EPI_THREADS = 128;
+constexpr int TMEM_COLS = 512;
+constexpr float LOG2E = 1.4426950408889634f;
+constexpr float LN2 = 0.6931471805599453f;
+
+enum Epi { EPI_LSE = 0, EPI_GRAD = 1, EPI_BF16 = 2, EPI_F32 = 3 };
+
+struct GemmParams {
+  CUtensorMap tmA;
+  CUtensorMap tmB;
+  CUtensorMap tmC;
+  int tiles_m, tiles_n, k_blocks, group_m;
+  int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
+  int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
+  // ---- EPI_LSE / EPI_GRAD
+  const int64_t* labels;
+  long long ignore_index;
+  int n_rows;  // N (rows >= n_rows are padding)
+  int vocab;   // V (columns >= vocab are padding)
+  int col0;    // global vocabulary index of column 0 of n-tile 0 (EPI_GRAD: start of the vocab block)
+  // EPI_LSE: tiles_n = number of vocabulary splits; split s sweeps n-tiles [s*per, min((s+1)*per, total))
+  int vtiles_per_split, vtiles_total;
+  float* part_m;  // [splits][part_stride]  running max (log2 domain)
+  float* part_l;  // [splits][part_stride]  running sum of 2^(s*log2e - m)
+  float* part_z;  // [splits][part_stride]  logit of the label if it fell in this split, else -inf
+  int part_stride;
+  // EPI_GRAD
+  const float* lse;          // [N] natural log
+  const float* grad_out;     // [1]
+  const int64_t* n_valid;    // [1]
+};
+
+struct TileItem {
+  int m, n0, ncount;
+};
+
+template <int EPI>
+__device__ __forceinline__ TileItem decode_item(const GemmParams& p, int item) {
+  const int per_group = p.group_m * p.tiles_n;
+  const int g = item / per_group;
+  const int r = item - g * per_group;
+  const int m0 = g * p.group_m;
+  const int gm = min(p.group_m, p.tiles_m - m0);
+  TileItem it;
+  it.m = m0 + r % gm;
+  const int n = r / gm;
+  if constexpr (EPI == EPI_LSE) {
+    it.n0 = n * p.vtiles_per_split;
+    it.ncount = min(p.vtiles_per_split, p.vtiles_total - it.n0);
+  } else {
+    it.n0 = n;
+    it.ncount = 1;
+  }
+  return it;
+}
+
+// 128-byte-swizzled staging row write: 8 x 16-byte chunks of row `row`, chunk j lands at (j ^ (row & 7)).
+__device__ __forceinline__ void stage_row_128B(uint32_t buf, int row, const uint32_t (&w)[32]) {
+  const uint32_t base = buf + row * 128;
+  const int sw = row & 7;
+#pragma unroll
+  for (int j = 0; j < 8; ++j)
+    st_shared_v4(base + ((j ^ sw) << 4), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
+}
+
+template <int EPI, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t smem_stage0 = smem_base;
+  const uint32_t smem_epi0 = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t smem_bar0 = smem_epi0 + NUM_EPI_BUFS * EPI_BUF_BYTES;
+  // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then the TMEM base address slot
+  auto full_bar = [&](int s) { return smem_bar0 + 8u * s; };
+  auto empty_bar = [&](int s) { return smem_bar0 + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return smem_bar0 + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return smem_bar0 + 8u * (2 * STAGES + 2 + s); };
+  const uint32_t tmem_slot = smem_bar0 + 8u * (2 * STAGES + 4);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int total_items = p.tiles_m * p.tiles_n;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&p.tmA);
+    tma_prefetch_desc(&p.tmB);
+    if constexpr (EPI == EPI_BF16 || EPI == EPI_F32 || EPI == EPI_GRAD) tma_prefetch_desc(&p.tmC);
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar(s), 1);
+      mbar_init(empty_bar(s), 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(tfull_bar(s), 1);
+      mbar_init(tempty_bar(s), 4);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 1) {
+    tmem_alloc<1>(tmem_slot, TMEM_COLS);
+    tmem_relinquish<1>();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  uint32_t tmem_base;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
+
+  if (warp == 0) {
+    // ===================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const TileItem it = decode_item<EPI>(p, item);
+        for (int t = 0; t < it.ncount; ++t) {
+          const int nt = it.n0 + t;
+          for (int kb = 0; kb < p.k_blocks; ++kb) {
+            mbar_wait(empty_bar(stage), phase ^ 1u);
+            const uint32_t fb = full_bar(stage);
+            mbar_expect_tx(fb, STAGE_BYTES);
+            const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
+            const uint32_t sB = sA + A_STAGE_BYTES;
+            if constexpr (!A_MN) {
+              tma_load_2d(sA, &p.tmA, p.a_k0 + kb * BK, p.a_r0 + it.m * BM, fb);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j)
+                tma_load_2d(sA + j * MN_BOX_BYTES, &p.tmA, p.a_r0 + it.m * BM + 64 * j, p.a_k0 + kb * BK, fb);
+            }
+            if constexpr (!B_MN) {
+              tma_load_2d(sB, &p.tmB, p.b_k0 + kb * BK, p.b_r0 + nt * BN, fb);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tma_load_2d(sB + j * MN_BOX_BYTES, &p.tmB, p.b_r0 + nt * BN + 64 * j, p.b_k0 + kb * BK, fb);
+            }
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================== MMA issuer (single thread)
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+      constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
+      constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
+      constexpr uint32_t A_KADV = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);  // bytes per UMMA_K step
+      constexpr uint32_t B_KADV = B_MN ? (UMMA_K * 128) : (UMMA_K * 2);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+        const TileItem it = decode_item<EPI>(p, item);
+        for (int t = 0; t < it.ncount; ++t) {
+          mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + acc * BN;
+          for (int kb = 0; kb < p.k_blocks; ++kb) {
+            mbar_wait(full_bar(stage), phase);
+            tc_fence_after();
+            const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
+            const uint32_t sB = sA + A_STAGE_BYTES;
+#pragma unroll
+            for (int k = 0; k < BK / UMMA_K; ++k) {
+              const uint64_t adesc = make_smem_desc(sA + k * A_KADV, A_LBO, 1024);
+              const uint64_t bdesc = make_smem_desc(sB + k * B_KADV, B_LBO, 1024);
+              umma_bf16<1>(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(empty_bar(stage));
+            if (++stage == STAGES) {
+              stage = 0;
+              phase ^= 1u;
+            }
+          }
+          umma_commit(tfull_bar(acc));
+          if (++acc == 2) {
+            acc = 0;
+            acc_phase ^= 1u;
+          }
+        }
+      }
+    }
+  } else {
+    // ===================================================== epilogue warps (one thread per accumulator row)
+    const int q = warp & 3;               // TMEM lane quadrant this warp may access
+    const int row_in_tile = q * 32 + lane;
+    const bool issuer = (threadIdx.x == 64);
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    uint32_t chunk_ctr = 0;  // alternates the staging buffers across the whole kernel
+    (void)issuer;
+    (void)chunk_ctr;
+
+    float gscale = 0.f;
+    if constexpr (EPI == EPI_GRAD) {
+      const long long nv = *p.n_valid;
+      gscale = (nv > 0) ? (*p.grad_out / static_cast<float>(nv)) : 0.f;
+    }
+
+    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+      const TileItem it = decode_item<EPI>(p, item);
+      const int row = it.m * BM + row_in_tile;  // global row of this thread
+
+      // per-item row state
+      long long label = p.ignore_index;
+      bool valid = false;
+      float m_run = -INFINITY, l_run = 0.f, z_lab = -INFINITY;  // EPI_LSE
+      float lse2 = 0.f;                                         // EPI_GRAD
+      if constexpr (EPI == EPI_LSE || EPI == EPI_GRAD) {
+        if (row < p.n_rows) {
+          label = p.labels[row];
+          valid = (label != p.ignore_index);
+        }
+        if constexpr (EPI == EPI_GRAD) {
+          if (valid) lse2 = p.lse[row] * LOG2E;
+        }
+      }
+
+      for (int t = 0; t < it.ncount; ++t) {
+        const int nt = it.n0 + t;
+        mbar_wait(tfull_bar(acc), acc_phase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+
+        if constexpr (EPI == EPI_LSE) {
+          const int cbase = p.col0 + nt * BN;
+          const bool tile_has_pad = (cbase + BN > p.vocab);
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            const int c0 = cbase + c * 32;
+            if (c0 >= p.vocab) break;
+            float v[32];
+            tmem_ld32(taddr + c * 32, v);
+            if (tile_has_pad) {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (c0 + j >= p.vocab) v[j] = -INFINITY;
+            }
+            if (valid && label >= c0 && label < c0 + 32) {
+              const int jl = static_cast<int>(label - c0);
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                if (j == jl) z_lab = v[j];
+            }
+            float cmax = v[0];
+#pragma unroll
+            for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, v[j]);
+            const float m_new = fmaxf(m_run, cmax * LOG2E);
+            float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              s0 += fast_exp2(fmaf(v[j], LOG2E, -m_new));
+              s1 += fast_exp2(fmaf(v[j + 1], LOG2E, -m_new));
+              s2 += fast_exp2(fmaf(v[j + 2], LOG2E, -m_new));
+              s3 += fast_exp2(fmaf(v[j + 3], LOG2E, -m_new));
+            }
+            l_run = l_run * fast_exp2(m_run - m_new) + ((s0 + s1) + (s2 + s3));
+            m_run = m_new;
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
+        } else if constexpr (EPI == EPI_GRAD) {
+          const int cbase = p.col0 + nt * BN;  // global vocab index of tile column 0
+#pragma unroll 1
+          for (int c = 0; c < BN / 64; ++c) {
+            const int c0 = cbase + c * 64;
+            uint32_t w[32];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float v[32];
+              tmem_ld32(taddr + c * 64 + h * 32, v);
+              const int ch0 = c0 + h * 32;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                float g = valid ? fast_exp2(fmaf(v[j], LOG2E, -lse2)) * gscale : 0.f;
+                if (ch0 + j >= p.vocab) g = 0.f;
+                v[j] = g;
+              }
+              if (valid && label >= ch0 && label < ch0 + 32) {
+                const int jl = static_cast<int>(label - ch0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (j == jl) v[j] -= gscale;
+              }
+#pragma unroll
+              for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            }
+            if (c == BN / 64 - 1) {  // accumulator fully read: release it to the MMA warp
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(tempty_bar(acc));
+            }
+            const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
+            if (issuer) tma_wait_group_read<1>();
+            named_bar_sync(1, EPI_THREADS);
+            stage_row_128B(buf, row_in_tile, w);
+            fence_proxy_async_smem();
+            named_bar_sync(1, EPI_THREADS);
+            if (issuer) {
+              tma_store_2d(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM);
+              tma_commit_group();
+            }
+            ++chunk_ctr;
+          }
+        } else if constexpr (EPI == EPI_BF16) {
+#pragma unroll 1
+          for (int c = 0; c < BN / 64; ++c) {
+            uint32_t w[32];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float v[32];
+              tmem_ld32(taddr + c * 64 + h * 32, v);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            }
+            if (c == BN / 64 - 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(tempty_bar(acc));
+            }
+            const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
+            if (issuer) tma_wait_group_read<1>();
+            named_bar_sync(1, EPI_THREADS);
+            stage_row_128B(buf, row_in_tile, w);
+            fence_proxy_async_smem();
+            named_bar_sync(1, EPI_THREADS);
+            if (issuer) {
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + it.m * BM;
+              if (p.c_reduce)
+                tma_reduce_add_2d(&p.tmC, buf, cc, cr);
+              else
+                tma_store_2d(&p.tmC, buf, cc, cr);
+              tma_commit_group();
+            }
+            ++chunk_ctr;
+          }
+        } else {  // EPI_F32
+#pragma unroll 1
+          for (int c = 0; c < BN / 32; ++c) {
+            uint32_t w[32];
+            {
+              float v[32];
+              tmem_ld32(taddr + c * 32, v);
+#pragma unroll
+              for (int j = 0; j < 32; ++j) w[j] = __float_as_uint(v[j]);
+            }
+            if (c == BN / 32 - 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(tempty_bar(acc));
+            }
+            const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
+            if (issuer) tma_wait_group_read<1>();
+            named_bar_sync(1, EPI_THREADS);
+            stage_row_128B(buf, row_in_tile, w);
+            fence_proxy_async_smem();
+            named_bar_sync(1, EPI_THREADS);
+            if (issuer) {
+              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + it.m * BM;
+              if (p.c_reduce)
+                tma_reduce_add_2d(&p.tmC, buf, cc, cr);
+              else
+                tma_store_2d(&p.tmC, buf, cc, cr);
+              tma_commit_group();
+            }
+            ++chunk_ctr;
+          }
+        }
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1u;
+        }
+      }
+
+      if constexpr (EPI == EPI_LSE) {
+        // item.n0 / vtiles_per_split is the split index
+        const int split = it.n0 / p.vtiles_per_split;
+        const size_t o = static_cast<size_t>(split) * p.part_stride + row;
+        p.part_m[o] = m_run;
+        p.part_l[o] = l_run;
+        p.part_z[o] = z_lab;
+      }
+    }
+    if constexpr (EPI != EPI_LSE) {
+      if (issuer) tma_wait_group<0>();
+    }
+  }
+
+  // ---- teardown
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+  }
+}
+
+}  // namespace ssi

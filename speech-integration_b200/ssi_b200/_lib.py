@@ -1,0 +1,94 @@
+"""ctypes binding of ``libssi_b200.so`` (C ABI declared in ``include/ssi_b200.h``).
+
+The library is built in-tree by ``ssi_b200.build.build()`` (nvcc, sm_100a only).  There is deliberately no
+fallback: if the shared object is missing or fails to load, every op raises ``RuntimeError``.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
+ABI_VERSION = 100
+
+# name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
+SYMBOLS = {
+    "ssi_b200_version": (c_int, []),
+    "ssi_b200_last_error": (c_char_p, []),
+    "ssi_b200_launch_count": (c_int64, []),
+    "ssi_b200_workspace_bytes": (
+        c_int,
+        [c_int64, c_int64, c_int64, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)],
+    ),
+    "ssi_b200_lmhead_ce_fwd": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_size_t, c_void_p],
+    ),
+    "ssi_b200_lmhead_ce_bwd": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p,
+         c_void_p, c_int, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_embedding_grad_scatter": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_label_shift_count": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ssi_b200_debug_gemm": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_void_p],
+    ),
+}
+
+_lib = None
+
+
+def load() -> ctypes.CDLL:
+    """Load the shared library (once). Raises RuntimeError if it is missing or has the wrong ABI."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"ssi_b200: CUDA extension {LIB_PATH} is not built. Run `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (nvcc, sm_100a). There is no CPU or PyTorch fallback for this path."
+        )
+    try:
+        lib = ctypes.CDLL(LIB_PATH)
+    except OSError as e:  # pragma: no cover - depends on the box
+        raise RuntimeError(f"ssi_b200: failed to load {LIB_PATH}: {e}") from e
+    for name, (restype, argtypes) in SYMBOLS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError as e:
+            raise RuntimeError(f"ssi_b200: {LIB_PATH} does not export {name}") from e
+        fn.restype = restype
+        fn.argtypes = argtypes
+    v = lib.ssi_b200_version()
+    if v != ABI_VERSION:
+        raise RuntimeError(f"ssi_b200: ABI version mismatch: library {v}, binding {ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().ssi_b200_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"ssi_b200.{what} failed (rc={rc}): {msg}")
+
+
+def workspace_bytes(N: int, V: int, D: int, which: str = "all") -> tuple[int, int, int]:
+    """(forward, backward, scatter) workspace sizes in bytes; ``which`` = "all" | "lmhead" | "scatter"."""
+    f, b, s = c_size_t(0), c_size_t(0), c_size_t(0)
+    pf = ctypes.byref(f) if which in ("all", "lmhead") else None
+    pb = ctypes.byref(b) if which in ("all", "lmhead") else None
+    ps = ctypes.byref(s) if which in ("all", "scatter") else None
+    check(load().ssi_b200_workspace_bytes(N, V, D, pf, pb, ps), "workspace_bytes")
+    return f.value, b.value, s.value
+
+
+def launch_count() -> int:
+    return int(load().ssi_b200_launch_count())

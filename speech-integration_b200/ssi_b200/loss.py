@@ -1,0 +1,143 @@
+"""Drop-in replacement for torchtune's ``CEWithChunkedOutputLoss`` that fuses the tied output projection.
+
+Reference call signature (ssi/trainer.py:299-304, ssi/loss.py:7-22): the trainer builds the loss, reads
+``num_output_chunks`` / ``ignore_index`` and calls ``loss_fn(model_output, labels)`` where ``model_output`` is a
+list of ``num_output_chunks`` tensors ``[b, s/n, *]`` (labels ``[b, s]``) or a single 2-D tensor (labels
+``[b*s]``).  With :class:`ssi_b200.HiddenPassthroughOutput` installed as ``model.output`` the model returns
+the final normed HIDDEN states in those positions and this module does projection + CE in one fused pass.
+"""
+from __future__ import annotations
+
+from typing import List, Sequence, Union
+
+import torch
+from torch import nn
+
+from . import ops
+
+
+class _FusedLinearCE(torch.autograd.Function):
+    """loss = mean_{valid rows} CE(X W^T, labels). Saves only X, W, labels and the per-row logsumexp."""
+
+    @staticmethod
+    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override):
+        loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
+        ctx.ignore_index = ignore_index
+        ctx.holder = holder
+        n_div = n_valid if n_valid_override is None else n_valid_override
+        ctx.save_for_backward(X, W, labels, lse, n_div)
+        if holder is not None:
+            holder.last_loss_sum = loss_out[0:1]
+            holder.last_n_valid = n_valid
+        if n_valid_override is None:
+            return loss_out[1]
+        # data parallel: mean over the GLOBAL number of valid tokens (this rank's share of it)
+        return loss_out[0] / n_valid_override[0].to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        X, W, labels, lse, n_div = ctx.saved_tensors
+        g = grad_out.detach().to(torch.float32).reshape(1).contiguous()
+        holder = ctx.holder
+        wparam = holder.weight_param() if holder is not None else None
+        write_into_grad = (
+            wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == W.data_ptr()
+        )
+        if write_into_grad:
+            # Write the LM-head gradient straight into the tied weight's .grad buffer (the buffer the
+            # embedding scatter-add and the DP all-reduce also use) and hand autograd nothing to accumulate.
+            if wparam.grad is None:
+                wparam.grad = torch.empty_like(wparam)
+                dX, _ = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index, dW=wparam.grad,
+                                          accumulate_dW=False)
+            else:
+                dX, _ = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index, dW=wparam.grad,
+                                          accumulate_dW=True)
+            return dX, None, None, None, None, None
+        dX, dW = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index)
+        return dX, dW, None, None, None, None
+
+
+def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
+                               ignore_index: int = -100, n_valid_total: torch.Tensor | None = None,
+                               _holder=None) -> torch.Tensor:
+    """Functional form: ``hidden [N, D]`` bf16, ``weight [V, D]`` bf16, ``labels [N]`` int64 -> fp32 0-dim loss."""
+    return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
+
+
+class FusedLinearCrossEntropyLoss(nn.Module):
+    """Same constructor attributes and call signature as ``CEWithChunkedOutputLoss``
+    (tt/torchtune/modules/loss/ce_chunked_output_loss.py:30-33,45) plus the tied module whose ``.weight`` is
+    the projection (tt/torchtune/modules/tied_linear.py:47-53).
+
+    Args:
+        tied_module: module owning the ``[V, D]`` bf16 weight (``model.tok_embeddings``).
+        num_output_chunks: kept for ``model.set_num_output_chunks`` (ssi/trainer.py:303-304); the fused kernel
+            does not need chunking, any value works.
+        ignore_index: label value that contributes nothing (default -100).
+        accumulate_into_grad: write dW directly into ``tied_module.weight.grad`` instead of returning it to
+            autograd (saves a ``[V, D]`` temporary and an AccumulateGrad pass).
+    """
+
+    def __init__(self, tied_module: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
+                 accumulate_into_grad: bool = True):
+        super().__init__()
+        if not hasattr(tied_module, "weight"):
+            raise AttributeError(
+                "Provided module does not have attribute 'weight'. Please check your tied_module."
+            )
+        # not registered as a submodule: the weight must stay owned by the model (state-dict keys unchanged)
+        object.__setattr__(self, "_tied", tied_module)
+        self.num_output_chunks = num_output_chunks
+        self.ignore_index = ignore_index
+        self.accumulate_into_grad = accumulate_into_grad
+        self.n_valid_total: torch.Tensor | None = None  # set by ssi_b200.dist for data parallelism
+        self.last_loss_sum: torch.Tensor | None = None
+        self.last_n_valid: torch.Tensor | None = None
+
+    @property
+    def tied_module(self) -> nn.Module:
+        return self._tied
+
+    def weight_param(self):
+        w = self._tied.weight
+        return w if isinstance(w, nn.Parameter) else None
+
+    def compute_cross_entropy(self, hidden: torch.Tensor, labels: torch.Tensor, normalize: bool = True):
+        """Sum-reduced CE of one chunk of hidden states (mirrors ce_chunked_output_loss.py:35-43, which takes
+        logits): returned so that ``training.compile_loss``-style wrappers that call it keep working."""
+        loss = fused_linear_cross_entropy(hidden.reshape(-1, hidden.size(-1)), self._tied.weight,
+                                          labels.reshape(-1), self.ignore_index, None, self)
+        return loss * self.last_n_valid[0].to(torch.float32)
+
+    def forward(self, hidden: Union[torch.Tensor, Sequence[torch.Tensor]], labels: torch.Tensor) -> torch.Tensor:
+        W = self._tied.weight
+        if isinstance(hidden, (list, tuple)):
+            # list of [b, s_c, D] chunks along dim 1 (tt/torchtune/modules/transformer.py:499-502)
+            h = hidden[0] if len(hidden) == 1 else torch.cat(list(hidden), dim=1)
+        else:
+            h = hidden
+        D = h.size(-1)
+        X = h.reshape(-1, D)
+        if not X.is_contiguous():
+            X = X.contiguous()
+        lab = labels.reshape(-1)
+        if not lab.is_contiguous():
+            lab = lab.contiguous()
+        if lab.numel() != X.size(0):
+            raise ValueError(f"labels ({tuple(labels.shape)}) do not match hidden rows ({X.size(0)})")
+        return fused_linear_cross_entropy(X, W, lab, self.ignore_index, self.n_valid_total, self)
+
+
+def make_torchtune_subclass():
+    """If torchtune is importable, return a subclass of BOTH CEWithChunkedOutputLoss and the fused loss so that
+    ``isinstance(loss_fn, CEWithChunkedOutputLoss)`` in ssi/trainer.py:303 keeps holding; else None."""
+    try:  # pragma: no cover - torchtune is not importable in the build image
+        from torchtune.modules.loss import CEWithChunkedOutputLoss
+    except Exception:
+        return None
+
+    class FusedCEWithChunkedOutputLoss(FusedLinearCrossEntropyLoss, CEWithChunkedOutputLoss):  # pragma: no cover
+        pass
+
+    return FusedCEWithChunkedOutputLoss

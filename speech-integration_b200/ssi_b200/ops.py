@@ -1,0 +1,180 @@
+"""Thin tensor-level wrappers over the C ABI: argument checking, workspace reuse, current-stream plumbing.
+
+PyTorch is used only for device memory and streams; all arithmetic happens in libssi_b200.so.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _lib
+
+_WS: dict[tuple, torch.Tensor] = {}
+
+
+def _workspace(kind: str, nbytes: int, device: torch.device) -> torch.Tensor:
+    """Grow-only per-(kind, device, stream) scratch buffer; the kernels of one call only use it in stream order."""
+    key = (kind, device.index, torch.cuda.current_stream(device).cuda_stream)
+    buf = _WS.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 256), dtype=torch.uint8, device=device)
+        _WS[key] = buf
+    return buf
+
+
+def free_workspaces() -> None:
+    _WS.clear()
+
+
+def _stream(device: torch.device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+def _require_cuda(*ts: torch.Tensor) -> torch.device:
+    dev = ts[0].device
+    for t in ts:
+        if t.device.type != "cuda":
+            raise RuntimeError(
+                "ssi_b200: tensors must live on a CUDA (sm_100a) device; there is no CPU fallback for this path"
+            )
+        if t.device != dev:
+            raise RuntimeError("ssi_b200: all tensors must be on the same device")
+    return dev
+
+
+def _check_xw(X: torch.Tensor, W: torch.Tensor) -> tuple[int, int, int]:
+    if X.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
+        raise TypeError(f"ssi_b200: X and W must be bfloat16 (got {X.dtype}, {W.dtype})")
+    if X.dim() != 2 or W.dim() != 2 or X.size(1) != W.size(1):
+        raise ValueError(f"ssi_b200: expected X [N, D] and W [V, D], got {tuple(X.shape)} and {tuple(W.shape)}")
+    if not X.is_contiguous() or not W.is_contiguous():
+        raise ValueError("ssi_b200: X and W must be contiguous")
+    return X.size(0), W.size(0), X.size(1)
+
+
+def lmhead_ce_fwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, ignore_index: int = -100):
+    """Fused ``X @ W.T`` + cross entropy forward.
+
+    Returns ``(loss_out, lse, n_valid)``: ``loss_out`` fp32 ``[2]`` = {sum of per-row losses, mean over valid
+    rows}, ``lse`` fp32 ``[N]``, ``n_valid`` int64 ``[1]``.  Replaces chunked_output + CEWithChunkedOutputLoss
+    (tt/torchtune/modules/transformer.py:499-502, tt/torchtune/modules/loss/ce_chunked_output_loss.py:45-83).
+    """
+    dev = _require_cuda(X, W, labels)
+    N, V, D = _check_xw(X, W)
+    if labels.dtype != torch.int64 or labels.numel() != N or not labels.is_contiguous():
+        raise ValueError("ssi_b200: labels must be a contiguous int64 tensor with one entry per row of X")
+    lib = _lib.load()
+    fwd_b, _, _ = _lib.workspace_bytes(N, V, D, "lmhead")
+    ws = _workspace("fwd", fwd_b, dev)
+    lse = torch.empty(N, dtype=torch.float32, device=dev)
+    loss_out = torch.empty(2, dtype=torch.float32, device=dev)
+    n_valid = torch.empty(1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_lmhead_ce_fwd(X.data_ptr(), W.data_ptr(), labels.data_ptr(), N, V, D, int(ignore_index),
+                                        lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), ws.data_ptr(),
+                                        ws.numel(), _stream(dev))
+    _lib.check(rc, "lmhead_ce_fwd")
+    return loss_out, lse, n_valid
+
+
+def lmhead_ce_bwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, lse: torch.Tensor,
+                  grad_out: torch.Tensor, n_valid_total: torch.Tensor, ignore_index: int = -100,
+                  dW: torch.Tensor | None = None, accumulate_dW: bool = False):
+    """Backward of :func:`lmhead_ce_fwd`: returns ``(dX, dW)`` (bf16).
+
+    ``grad_out``: fp32 device scalar (upstream gradient of the mean loss); ``n_valid_total``: int64 device
+    scalar used as the mean's divisor.  If ``dW`` is given it is written in place (added to when
+    ``accumulate_dW``), which is how the tied weight's ``.grad`` buffer is shared with the embedding gradient.
+    """
+    dev = _require_cuda(X, W, labels, lse, grad_out, n_valid_total)
+    N, V, D = _check_xw(X, W)
+    if grad_out.dtype != torch.float32 or grad_out.numel() != 1:
+        raise ValueError("ssi_b200: grad_out must be a single fp32 value on the device")
+    if n_valid_total.dtype != torch.int64 or n_valid_total.numel() != 1:
+        raise ValueError("ssi_b200: n_valid_total must be a single int64 value on the device")
+    if lse.dtype != torch.float32 or lse.numel() != N:
+        raise ValueError("ssi_b200: lse must be fp32 [N]")
+    if dW is None:
+        if accumulate_dW:
+            raise ValueError("ssi_b200: accumulate_dW needs an existing dW buffer")
+        dW = torch.empty_like(W)
+    elif dW.shape != W.shape or dW.dtype != torch.bfloat16 or not dW.is_contiguous() or dW.device != dev:
+        raise ValueError("ssi_b200: dW must be a contiguous bf16 tensor shaped like W on the same device")
+    lib = _lib.load()
+    _, bwd_b, _ = _lib.workspace_bytes(N, V, D, "lmhead")
+    ws = _workspace("bwd", bwd_b, dev)
+    dX = torch.empty_like(X)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_lmhead_ce_bwd(X.data_ptr(), W.data_ptr(), labels.data_ptr(), lse.data_ptr(),
+                                        grad_out.data_ptr(), n_valid_total.data_ptr(), N, V, D, int(ignore_index),
+                                        dX.data_ptr(), dW.data_ptr(), 1 if accumulate_dW else 0, ws.data_ptr(),
+                                        ws.numel(), _stream(dev))
+    _lib.check(rc, "lmhead_ce_bwd")
+    return dX, dW
+
+
+def embedding_grad_scatter(dH: torch.Tensor, ids: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
+    """``dW[ids[i]] += dH[i]`` in place (sorted-id warp-segmented reduction, deterministic). Returns ``dW``.
+
+    Replaces the backward of the tied ``nn.Embedding`` (tt/torchtune/models/llama3_2/_component_builders.py:114,
+    tt/torchtune/modules/transformer.py:628).
+    """
+    dev = _require_cuda(dH, ids, dW)
+    if dH.dtype != torch.bfloat16 or dW.dtype != torch.bfloat16:
+        raise TypeError("ssi_b200: dH and dW must be bfloat16")
+    if dH.dim() != 2 or dW.dim() != 2 or dH.size(1) != dW.size(1):
+        raise ValueError("ssi_b200: expected dH [N, D] and dW [V, D]")
+    if ids.dtype != torch.int64 or ids.numel() != dH.size(0):
+        raise ValueError("ssi_b200: ids must be int64 with one entry per row of dH")
+    if not (dH.is_contiguous() and dW.is_contiguous() and ids.is_contiguous()):
+        raise ValueError("ssi_b200: dH, ids and dW must be contiguous")
+    N, D = dH.shape
+    V = dW.size(0)
+    lib = _lib.load()
+    _, _, sc_b = _lib.workspace_bytes(N, V, D, "scatter")
+    ws = _workspace("scatter", sc_b, dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_embedding_grad_scatter(dH.data_ptr(), ids.data_ptr(), N, V, D, dW.data_ptr(),
+                                                 ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "embedding_grad_scatter")
+    return dW
+
+
+def label_shift_count(labels: torch.Tensor, ignore_index: int = -100):
+    """Shift labels left by one (ssi/loss.py:16) and count non-ignored tokens before/after the shift.
+
+    Returns ``(shifted_labels [B, S], counts int64 [2])`` with counts[0] the unshifted count used by
+    ssi/trainer.py:391 and counts[1] the shifted count the loss divides by.
+    """
+    dev = _require_cuda(labels)
+    if labels.dtype != torch.int64 or labels.dim() != 2 or not labels.is_contiguous():
+        raise ValueError("ssi_b200: labels must be a contiguous int64 [B, S] tensor")
+    B, S = labels.shape
+    out = torch.empty_like(labels)
+    counts = torch.empty(2, dtype=torch.int64, device=dev)
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_label_shift_count(labels.data_ptr(), B, S, int(ignore_index), out.data_ptr(),
+                                            counts.data_ptr(), _stream(dev))
+    _lib.check(rc, "label_shift_count")
+    return out, counts
+
+
+def debug_gemm(A: torch.Tensor, B: torch.Tensor, a_mn_major: bool = False, b_mn_major: bool = False,
+               C: torch.Tensor | None = None) -> torch.Tensor:
+    """Test hook for the shared tcgen05 mainloop: fp32 ``C[M, N] (+)= op(A) @ op(B)^T`` (see ssi_b200.h)."""
+    dev = _require_cuda(A, B)
+    if A.dtype != torch.bfloat16 or B.dtype != torch.bfloat16 or not A.is_contiguous() or not B.is_contiguous():
+        raise ValueError("ssi_b200: A and B must be contiguous bf16")
+    M, K = (A.size(1), A.size(0)) if a_mn_major else (A.size(0), A.size(1))
+    N, K2 = (B.size(1), B.size(0)) if b_mn_major else (B.size(0), B.size(1))
+    if K != K2:
+        raise ValueError("ssi_b200: contraction sizes differ")
+    acc = C is not None
+    if C is None:
+        C = torch.empty(M, N, dtype=torch.float32, device=dev)
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_debug_gemm(A.data_ptr(), B.data_ptr(), C.data_ptr(), M, N, K, int(a_mn_major),
+                                     int(b_mn_major), int(acc), _stream(dev))
+    _lib.check(rc, "debug_gemm")
+    return C

@@ -1,0 +1,37 @@
+"""The shared tcgen05/TMA mainloop against torch fp32 matmul, for every operand-major combination the product
+kernels use: (K,K) logits = X W^T; (MN,MN) dW = G^T X; (K,MN) dX = G W.  Inputs are bf16-exact, so the only
+difference from an fp32 reference is accumulation order: tolerance 1e-3 relative to the result scale."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+SHAPES = [(128, 256, 64), (128, 256, 256), (256, 512, 192), (200, 264, 136), (8, 8, 8), (1000, 2048, 520),
+          (384, 1024, 2048)]
+
+
+def _mk(shape, seed):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return torch.randn(*shape, generator=g).to(torch.bfloat16).cuda()
+
+
+@pytest.mark.parametrize("M,N,K", SHAPES)
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True), (False, True)])
+def test_debug_gemm(M, N, K, a_mn, b_mn):
+    from ssi_b200 import ops
+
+    A = _mk((K, M) if a_mn else (M, K), 1)
+    B = _mk((K, N) if b_mn else (N, K), 2)
+    Af = A.float().t() if a_mn else A.float()
+    Bf = B.float().t() if b_mn else B.float()
+    ref = Af @ Bf.t()
+    C = ops.debug_gemm(A, B, a_mn, b_mn)
+    torch.cuda.synchronize()
+    scale = ref.abs().max().item() + 1e-6
+    err = (C - ref).abs().max().item()
+    assert err <= 1e-3 * scale, f"max err {err} vs scale {scale}"
+    # accumulate: TMA reduce-add on top of the previous result
+    C2 = ops.debug_gemm(A, B, a_mn, b_mn, C=C.clone())
+    torch.cuda.synchronize()
+    err2 = (C2 - 2 * ref).abs().max().item()
+    assert err2 <= 2e-3 * scale
