@@ -1,0 +1,354 @@
+#!/usr/bin/env python
+"""Benchmark of the fused tied-LM-head + chunked-CE path (BASELINE.json metric) on N B200s of one node.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c5]
+
+One "step" = one pass of the hot path over one batch of synthetic input: label shift + token
+counts, K1 fused projection + online-LSE CE forward, K2 recompute backward (dX, dW), K3 tied-embedding scatter-add
+and, for N > 1, the NCCL all-reduce of the token counts and of the tied gradient.  The default workload is
+BASELINE.json configs[4] / SURVEY c5 — HuBERT 5000-DSU vocabulary (V = 133,258, the "@133k vocab" the metric is
+quoted on), global batch 64 x 2048 — sharded by sequences over the ranks (strong scaling: the global batch is
+fixed; at N = 1 the whole batch runs on one GPU).
+
+Prints ONE JSON line on rank 0.  `value` = global token positions per second with inputs resident in HBM;
+`e2e` = the same through the public module API with pinned-host inputs copied in and the loss read back every
+step; `roofline` = the dominant kernel class timed live with CUDA events on its own stream; `cpu_baseline` = the
+CPU restatement of the reference path (oracle/, bf16 like the reference) on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "speech-integration_b200"))
+
+METRIC = "fused LM-head+CE fwd/bwd tokens/sec @133k vocab"
+UNIT = "tokens/s"
+CPU_SAMPLE_ROWS = 2048  # 1 x 2048 tokens = BASELINE.json configs[0] (the reference's own CPU-runnable case)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", default="c5", help="SURVEY.md §8d configuration (c1..c5)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            p = json.load(f)
+        return {"bf16_tflops": p["bf16_tflops"], "bf16_tflops_sustained": p.get("bf16_tflops_sustained"),
+                "hbm_gbs": p["hbm_gbs"], "source": "measured (MEASURED_PEAKS.json)"}
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0,
+            "source": "fallback (B200_PROFILING.md)"}
+
+
+# ----------------------------------------------------------------------------------------- clocks sampling
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines: list[str] = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits", "-lms", "200",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, val in zip(names, f[5:9]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
+                "samples": len(sm), "power_w_max": max(power) if power else None}
+
+
+# ----------------------------------------------------------------------------------------- CPU reference arm
+def cpu_reference_tokens_per_s(cfg, iters: int, warmup: int):
+    """The reference's CPU path (oracle restatement, bf16 like the reference: conf/common.yaml:32) on a bounded
+    sample of the workload: 1 x 2048 token rows at the workload's vocabulary, fwd + bwd + embedding backward."""
+    import torch
+
+    from oracle import reference_path as oracle
+    from ssi_b200 import synth
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    inp = synth.make_inputs(cfg, batch=1, seq=CPU_SAMPLE_ROWS)
+    times = []
+    for i in range(warmup + iters):
+        t0 = time.perf_counter()
+        oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"], inp["dH0"], inp["W"],
+                               compute_dtype=torch.bfloat16)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    return CPU_SAMPLE_ROWS / (sum(times) / len(times)), times, cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from ssi_b200 import synth
+
+    cfg = synth.CONFIGS[args.config]
+    # each step = one bounded sample; keep the whole run within a few minutes
+    steps = max(1, min(args.steps, 20))
+    warm = max(1, min(args.warmup, 3))
+    tps, times, cores = cpu_reference_tokens_per_s(cfg, steps, warm)
+    ms = 1e3 * sum(times) / len(times)
+    sample = (f"{CPU_SAMPLE_ROWS} token rows (1x2048) of {cfg.name} at V={cfg.vocab}, D=2048, bf16, fwd+bwd+embedding "
+              f"backward per step")
+    line = {
+        "impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(cfg), "reference_arm": "CPU restatement of the reference path "
+                   "(oracle/reference_path.py: same torch ops at the reference's call sites), host cores only"},
+        "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_name(cfg) -> str:
+    return (f"{cfg.name}: {cfg.desc}; V={cfg.vocab}, D=2048, global batch {cfg.batch}x{cfg.seq} "
+            f"= {cfg.rows} token rows, bf16 in / fp32 accumulate")
+
+
+# ----------------------------------------------------------------------------------------- our arm
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from ssi_b200 import _lib, synth
+    from ssi_b200 import dist as ddist
+    from ssi_b200.step import PathStep
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the ssi_b200 path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    pg = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        pg = dist.group.WORLD
+    _lib.load()
+    peaks = load_peaks()
+    cfg = synth.CONFIGS[args.config]
+    D = synth.HIDDEN
+    V = cfg.vocab
+
+    # ---- synthetic inputs: W replicated (global seed), this rank's sequences of the global batch
+    b0, b1 = ddist.shard_rows(cfg.batch, rank, world)
+    Bl = b1 - b0
+    gw = torch.Generator().manual_seed(synth.SEED)
+    W = (torch.randn(V, D, generator=gw) * 0.02).to(torch.bfloat16).to(dev)
+    g = torch.Generator().manual_seed(synth.SEED + 1 + rank)
+    tokens_h, labels_h = synth.make_tokens_labels(cfg, g, batch=Bl)
+    gd = torch.Generator(device=dev).manual_seed(synth.SEED + 1 + rank)
+    X = torch.randn(Bl, cfg.seq, D, generator=gd, device=dev).to(torch.bfloat16)
+    dH0 = (torch.randn(Bl, cfg.seq, D, generator=gd, device=dev) * 1e-3).to(torch.bfloat16)
+    tokens, labels = tokens_h.to(dev), labels_h.to(dev)
+    n_valid_local = int((labels_h[:, 1:] != synth.IGNORE).sum())
+    nv = torch.tensor([n_valid_local], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(nv)
+    n_valid_global = int(nv.item())
+
+    path = PathStep(W, process_group=pg)
+
+    def step():
+        path.zero_grad(set_to_none=True)  # ssi/trainer.py:410
+        return path(tokens, labels, X, dH0)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+
+    # ---- timed region: EXACTLY K steps, CUDA events, max over ranks
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    launches0 = _lib.launch_count()
+    _lib.profile_begin()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        out = step()
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    classes = _lib.profile_end()
+    launches = _lib.launch_count() - launches0
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = t.item() / args.steps
+    value = cfg.rows / (ms_step * 1e-3)
+    loss_batch = float(out[0].item())
+
+    # ---- end to end through the public API with pinned host inputs
+    e2e = None
+    if not args.no_e2e:
+        hx, hd = X.cpu().pin_memory(), dH0.cpu().pin_memory()
+        ht, hl = tokens_h.pin_memory(), labels_h.pin_memory()
+        h2d = sum(x.numel() * x.element_size() for x in (hx, hd, ht, hl))
+
+        def e2e_step():
+            path.zero_grad(set_to_none=True)
+            dx_ = hx.to(dev, non_blocking=True)
+            dd_ = hd.to(dev, non_blocking=True)
+            dt_ = ht.to(dev, non_blocking=True)
+            dl_ = hl.to(dev, non_blocking=True)
+            lb, _, _ = path(dt_, dl_, dx_, dd_)
+            return lb.item()  # device -> host read of the step's result
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        k2 = max(3, min(args.steps, 10))
+        e0.record()
+        for _ in range(k2):
+            e2e_step()
+        e1.record()
+        barrier()
+        t2 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t2, op=dist.ReduceOp.MAX)
+        e2e = {"value": cfg.rows / (t2.item() / k2 * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4, "steps": k2, "ms_per_step": t2.item() / k2}
+        del hx, hd
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel class (timed live above with events on the launching stream)
+    alg_total = 6.0 * n_valid_local * V * D  # this rank: fwd 2NVD + dX 2NVD + dW 2NVD on valid rows only
+    alg = {"lse_fwd": 2.0 * n_valid_local * V * D, "dlogits": 0.0, "dW": 2.0 * n_valid_local * V * D,
+           "dX": 2.0 * n_valid_local * V * D}
+    n_local = Bl * cfg.seq
+    executed = {k: 2.0 * n_local * V * D for k in ("lse_fwd", "dlogits", "dW", "dX")}
+    kern = {}
+    for k, (ms, cnt) in classes.items():
+        per_step = ms / args.steps
+        kern[k] = {"ms_per_step": per_step, "launches_per_step": cnt / args.steps,
+                   "share_of_step": per_step / ms_step}
+        if k in executed and per_step > 0:
+            kern[k]["executed_tflops"] = executed[k] / (per_step * 1e-3) / 1e12
+            kern[k]["algorithmic_tflops"] = alg[k] / (per_step * 1e-3) / 1e12
+    dom = max((k for k in ("lse_fwd", "dW", "dX")), key=lambda k: classes[k][0])
+    dom_ms = classes[dom][0] / max(classes[dom][1], 1)
+    dom_alg = alg[dom] * args.steps / max(classes[dom][1], 1)
+    achieved = dom_alg / (dom_ms * 1e-3) / 1e12
+    peak = peaks["bf16_tflops_sustained"] or peaks["bf16_tflops"]
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(dom)
+        except Exception:
+            traffic = None
+    roofline = {"bound": "tensor", "kernel": f"gemm_kernel<{dom}>", "achieved": achieved, "peak": peak,
+                "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "peak_kind": "sustained bf16 cuBLAS, " + peaks["source"],
+                "frac_of_burst_peak": achieved / peaks["bf16_tflops"],
+                "algorithmic_flops_per_launch": dom_alg, "avg_launch_ms": dom_ms}
+    step_tflops = alg_total / (ms_step * 1e-3) / 1e12
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": workload_name(cfg), "rows_per_rank": n_local, "valid_rows_global": n_valid_global,
+                   "parallelism": f"dp{world}", "l2": "inputs (X, W, dlogits blocks) are several times larger than "
+                   "the 126 MB L2, no explicit flush", "loss_batch_rank0": loss_batch},
+        "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
+        "step_algorithmic_tflops_per_gpu": step_tflops,
+        "step_frac_of_bf16_peak": {"burst": step_tflops / peaks["bf16_tflops"], "sustained": step_tflops / peak},
+        "kernels": kern,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        tps, times, cores = cpu_reference_tokens_per_s(cfg, 2, 1)
+        line["cpu_baseline"] = {
+            "value": tps, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"{CPU_SAMPLE_ROWS} token rows (1x2048) of {cfg.name} at V={V}, bf16, fwd+bwd+embedding "
+                      f"backward, mean of {len(times)} iterations after 1 warm-up"}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

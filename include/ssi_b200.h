@@ -96,6 +96,17 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
                                int64_t* labels_out, int64_t* counts, void* stream);
 
 /*
+ * Optional per-kernel-class timing (used by bench.py for the roofline figure): between profile_begin and
+ * profile_end every launch made through this library is bracketed by CUDA events on its own stream.
+ * profile_end waits for those events and fills ms_by_class[8] / launches_by_class[8] (either may be NULL):
+ *   0 = K1 logits + online-LSE (fwd), 1 = K2a dlogits recompute, 2 = K2b dW contraction, 3 = K2c dX contraction,
+ *   4 = K3 embedding scatter (sort + segmented reduce, one entry per call), 5 = small helper kernels, 6-7 unused.
+ * This pair is the only part of the ABI that synchronises (profile_end) or allocates (events, lazily).
+ */
+int ssi_b200_profile_begin(void);
+int ssi_b200_profile_end(double* ms_by_class, int64_t* launches_by_class);
+
+/*
  * Test hook: C[M, N] (fp32, row-major, ldc = N) = A * B^T-style contraction on the same tcgen05 mainloop
  * the product kernels use.  a_mn_major == 0: A is [M, K] row-major (K contiguous); != 0: A is [K, M]
  * row-major (M contiguous).  Likewise B: [N, K] or [K, N].  accumulate != 0 adds into C (TMA reduce-add).

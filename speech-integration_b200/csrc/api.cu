@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 #include "../../include/ssi_b200.h"
 #include "aux_kernels.cuh"
@@ -19,6 +20,44 @@ namespace {
 
 thread_local char g_err[512] = "";
 std::atomic<long long> g_launches{0};
+
+// ---- optional per-kernel-class timing with CUDA events on the launching stream (bench.py's roofline leg)
+enum ProfCat { CAT_LSE = 0, CAT_DLOGITS = 1, CAT_DW = 2, CAT_DX = 3, CAT_SCATTER = 4, CAT_AUX = 5, CAT_COUNT = 8 };
+struct ProfRec {
+  int cat;
+  cudaEvent_t a, b;
+};
+struct ProfState {
+  std::mutex mu;
+  bool on = false;
+  std::vector<ProfRec> recs;
+  std::vector<cudaEvent_t> pool;
+  size_t used = 0;
+  cudaEvent_t get() {
+    if (used == pool.size()) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      pool.push_back(e);
+    }
+    return pool[used++];
+  }
+};
+ProfState g_prof;
+struct ProfScope {
+  cudaStream_t st;
+  cudaEvent_t b = nullptr;
+  ProfScope(int cat, cudaStream_t s) : st(s) {
+    if (!g_prof.on) return;
+    std::lock_guard<std::mutex> lk(g_prof.mu);
+    cudaEvent_t a = g_prof.get();
+    b = g_prof.get();
+    g_prof.recs.push_back({cat, a, b});
+    cudaEventRecord(a, st);
+  }
+  ~ProfScope() {
+    if (b) cudaEventRecord(b, st);
+  }
+};
 
 int fail(int code, const char* fmt, ...) {
   va_list ap;
@@ -116,7 +155,7 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
 }
 
 template <int EPI, bool A_MN, bool B_MN>
-int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name) {
+int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat) {
   auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
@@ -126,7 +165,10 @@ int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* 
   const int items = p.tiles_m * p.tiles_n;
   if (items <= 0) return 0;
   const int grid = items < sms ? items : sms;
-  kern<<<grid, ssi::GEMM_THREADS, ssi::GEMM_SMEM_BYTES, st>>>(p);
+  {
+    ProfScope ps(cat, st);
+    kern<<<grid, ssi::GEMM_THREADS, ssi::GEMM_SMEM_BYTES, st>>>(p);
+  }
   SSI_LAUNCH_OK(name);
   return 0;
 }
@@ -291,8 +333,9 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   p.part_l = reinterpret_cast<float*>(wsb + f.off_l);
   p.part_z = reinterpret_cast<float*>(wsb + f.off_z);
   p.part_stride = static_cast<int>(f.n_pad);
-  if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse")) return r;
+  if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse", CAT_LSE)) return r;
 
+  ProfScope ps_aux(CAT_AUX, st);
   float* blk_loss = reinterpret_cast<float*>(wsb + f.off_bl);
   int* blk_cnt = reinterpret_cast<int*>(wsb + f.off_bc);
   ssi::lse_combine_kernel<<<f.combine_blocks, ssi::COMBINE_THREADS, 0, st>>>(
@@ -353,7 +396,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.labels = labels, p.ignore_index = ignore_index;
       p.n_rows = static_cast<int>(N), p.vocab = static_cast<int>(V), p.col0 = v0;
       p.lse = lse, p.grad_out = grad_out, p.n_valid = n_valid_total;
-      if (int r = launch_gemm<ssi::EPI_GRAD, false, false>(p, di->sms, st, "lmhead_dlogits")) return r;
+      if (int r = launch_gemm<ssi::EPI_GRAD, false, false>(p, di->sms, st, "lmhead_dlogits", CAT_DLOGITS)) return r;
     }
     // ---- K2b: dW[v0 : v0 + rows) (+)= G^T X   (M = vocabulary rows, N = D, K = tokens)
     {
@@ -367,7 +410,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.group_m = 16;
       p.c_r0 = v0;
       p.c_reduce = accumulate_dW ? 1 : 0;
-      if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW")) return r;
+      if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
     }
     // ---- K2c: dX (+)= G W[v0 : v0 + vtn*256)   (M = tokens, N = D, K = vocabulary block)
     {
@@ -380,15 +423,16 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.b_k0 = v0;
       p.c_reduce = (blk > 0) ? 1 : 0;
       if (b.nblocks > 1) {
-        if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX_f32")) return r;
+        if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX_f32", CAT_DX)) return r;
       } else {
-        if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX_bf16")) return r;
+        if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX_bf16", CAT_DX)) return r;
       }
     }
   }
   if (b.nblocks > 1) {
     const size_t n4 = static_cast<size_t>(N) * D / 4;
     const int grid = di->sms * 8;
+    ProfScope ps_aux(CAT_AUX, st);
     ssi::cast_f32_bf16_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(dxacc),
                                                     reinterpret_cast<uint2*>(dX), n4);
     SSI_LAUNCH_OK("cast_dX");
@@ -415,6 +459,7 @@ int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t 
   uint32_t* hist = reinterpret_cast<uint32_t*>(wsb + s.off_hist);
   const int n = static_cast<int>(N);
 
+  ProfScope ps_scat(CAT_SCATTER, st);
   ssi::sort_prepare_kernel<<<static_cast<int>(ceil_div(N, 256)), 256, 0, st>>>(ids, n, V, k[0], v[0]);
   SSI_LAUNCH_OK("sort_prepare");
   int cur = 0;
@@ -459,6 +504,33 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
   return 0;
 }
 
+int ssi_b200_profile_begin(void) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.recs.clear();
+  g_prof.used = 0;
+  g_prof.on = true;
+  return 0;
+}
+
+int ssi_b200_profile_end(double* ms_by_class, int64_t* launches_by_class) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.on = false;
+  for (int i = 0; i < CAT_COUNT; ++i) {
+    if (ms_by_class) ms_by_class[i] = 0.0;
+    if (launches_by_class) launches_by_class[i] = 0;
+  }
+  for (const ProfRec& r : g_prof.recs) {
+    SSI_CUDA(cudaEventSynchronize(r.b));
+    float ms = 0.f;
+    SSI_CUDA(cudaEventElapsedTime(&ms, r.a, r.b));
+    if (ms_by_class) ms_by_class[r.cat] += ms;
+    if (launches_by_class) launches_by_class[r.cat] += 1;
+  }
+  g_prof.recs.clear();
+  g_prof.used = 0;
+  return 0;
+}
+
 int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64_t N, int64_t K, int a_mn_major,
                         int b_mn_major, int accumulate, void* stream) {
   SSI_CHECK_ARG(A && B && C, "null pointer argument");
@@ -485,9 +557,9 @@ int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64
   p.k_blocks = static_cast<int>(ceil_div(K, ssi::BK));
   p.group_m = 8;
   p.c_reduce = accumulate ? 1 : 0;
-  if (!a_mn_major && !b_mn_major) return launch_gemm<ssi::EPI_F32, false, false>(p, di->sms, st, "debug_gemm_kk");
-  if (a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "debug_gemm_mm");
-  if (!a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "debug_gemm_km");
+  if (!a_mn_major && !b_mn_major) return launch_gemm<ssi::EPI_F32, false, false>(p, di->sms, st, "debug_gemm_kk", CAT_AUX);
+  if (a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "debug_gemm_mm", CAT_AUX);
+  if (!a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "debug_gemm_km", CAT_AUX);
   return fail(-1, "unsupported operand majors (a_mn=%d, b_mn=%d)", a_mn_major, b_mn_major);
 }
 

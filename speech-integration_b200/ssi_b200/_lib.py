@@ -37,6 +37,8 @@ SYMBOLS = {
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
     "ssi_b200_label_shift_count": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ssi_b200_profile_begin": (c_int, []),
+    "ssi_b200_profile_end": (c_int, [c_void_p, c_void_p]),
     "ssi_b200_debug_gemm": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_void_p],
@@ -92,3 +94,18 @@ def workspace_bytes(N: int, V: int, D: int, which: str = "all") -> tuple[int, in
 
 def launch_count() -> int:
     return int(load().ssi_b200_launch_count())
+
+
+PROFILE_CLASSES = ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux", "_6", "_7")
+
+
+def profile_begin() -> None:
+    check(load().ssi_b200_profile_begin(), "profile_begin")
+
+
+def profile_end() -> dict[str, tuple[float, int]]:
+    """{class: (total ms, launches)} for the launches made since profile_begin (synchronises)."""
+    ms = (ctypes.c_double * 8)()
+    cnt = (ctypes.c_int64 * 8)()
+    check(load().ssi_b200_profile_end(ctypes.cast(ms, c_void_p), ctypes.cast(cnt, c_void_p)), "profile_end")
+    return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(6)}

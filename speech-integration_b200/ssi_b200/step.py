@@ -1,0 +1,79 @@
+"""One micro-batch of the graded path, driven the way ``Trainer._train_step`` drives the reference
+(ssi/trainer.py:385-395) with the 16 decoder layers cut out:
+
+    num_tokens_iter = (labels != ignore).sum()                 # ssi/trainer.py:391 (unshifted labels)
+    labels' = shift(labels)                                    # ssi/loss.py:16
+    loss = loss_fn(hidden, labels')                            # fused projection + CE  (K1)
+    (loss * num_tokens_iter).backward()                        # K2: dX, dW into W.grad
+    tok_embeddings backward: W.grad[tokens] += dH0             # K3
+    [data parallel] all-reduce W.grad, loss_sum, n_valid       # K4 (ssi_b200.dist)
+
+``hidden`` stands for the final normed hidden state and ``dH0`` for the gradient arriving at the embedding
+output; both are inputs here because the decoder layers are outside the path.
+"""
+from __future__ import annotations
+
+import torch
+from torch import nn
+
+from . import ops
+from .loss import FusedLinearCrossEntropyLoss
+
+
+class PathStep:
+    def __init__(self, weight: nn.Parameter | torch.Tensor, ignore_index: int = -100, num_output_chunks: int = 8,
+                 process_group=None):
+        if not isinstance(weight, nn.Parameter):
+            weight = nn.Parameter(weight)
+        self.emb = nn.Embedding(weight.size(0), weight.size(1), device="meta", dtype=weight.dtype)
+        self.emb.weight = weight
+        self.loss_fn = FusedLinearCrossEntropyLoss(self.emb, num_output_chunks, ignore_index)
+        self.ignore_index = ignore_index
+        self.pg = process_group
+        self.world = 1
+        if process_group is not None:
+            import torch.distributed as dist
+
+            self.world = dist.get_world_size(process_group)
+
+    @property
+    def weight(self) -> nn.Parameter:
+        return self.emb.weight
+
+    def zero_grad(self, set_to_none: bool = True) -> None:
+        if set_to_none:
+            self.weight.grad = None
+        elif self.weight.grad is not None:
+            self.weight.grad.zero_()
+
+    def forward_only(self, hidden: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+        """Eval path (ssi/eval.py:26-33): loss under inference_mode, no backward."""
+        with torch.inference_mode():
+            shifted, _ = ops.label_shift_count(labels, self.ignore_index)
+            return self.loss_fn(hidden, shifted)
+
+    def __call__(self, tokens: torch.Tensor, labels: torch.Tensor, hidden: torch.Tensor, dH0: torch.Tensor):
+        """Returns ``(loss_batch, dX, counts)``: loss_batch = mean loss * num_tokens_iter (fp32 0-dim, what
+        ssi/trainer.py:393-395 accumulates), dX bf16 like ``hidden``, counts int64 [2] (unshifted, shifted).
+        ``self.weight.grad`` holds LM-head + embedding gradient (all-reduced when a process group is set)."""
+        shifted, counts = ops.label_shift_count(labels, self.ignore_index)
+        hidden = hidden.detach().requires_grad_(True)
+        gcounts = counts
+        if self.world > 1:
+            from . import dist as ddist
+
+            # global counts: every rank scales by the GLOBAL token numbers, so gradients are those of the
+            # single-process loss on the concatenated batch
+            gcounts = ddist.global_counts(counts, self.pg)
+            self.loss_fn.n_valid_total = gcounts[1:2]
+        n_iter = gcounts[0].to(torch.float32)
+        loss = self.loss_fn(hidden, shifted)
+        loss_batch = loss * n_iter
+        loss_batch.backward()
+        D = dH0.size(-1)
+        ops.embedding_grad_scatter(dH0.reshape(-1, D), tokens.reshape(-1), self.weight.grad)
+        if self.world > 1:
+            from . import dist as ddist
+
+            ddist.allreduce_tied_grad(self.weight.grad, self.pg)
+        return loss_batch.detach(), hidden.grad, counts
