@@ -1,0 +1,91 @@
+"""Host-side logic that needs no GPU: module surface (same attributes / errors as the reference's loss and
+TiedLinear), synthetic generators, row sharding, and the loud failure of the product path without CUDA."""
+import pytest
+import torch
+from torch import nn
+
+import ssi_b200
+from ssi_b200 import dist as ddist
+from ssi_b200 import ops, synth
+
+
+def test_loss_module_surface_matches_reference():
+    emb = nn.Embedding(100, 64, dtype=torch.bfloat16)
+    loss = ssi_b200.FusedLinearCrossEntropyLoss(emb)
+    # defaults of CEWithChunkedOutputLoss (tt/torchtune/modules/loss/ce_chunked_output_loss.py:30-33)
+    assert loss.num_output_chunks == 8 and loss.ignore_index == -100
+    assert loss.tied_module is emb
+    # the tied weight must not be registered under the loss (state-dict keys unchanged)
+    assert list(loss.state_dict().keys()) == [] and list(loss.parameters()) == []
+    with pytest.raises(AttributeError, match="does not have attribute 'weight'"):
+        ssi_b200.FusedLinearCrossEntropyLoss(nn.ReLU())  # same error as tied_linear.py:50-53
+    with pytest.raises(AttributeError):
+        ssi_b200.HiddenPassthroughOutput(nn.ReLU())
+
+
+def test_no_cpu_fallback():
+    emb = nn.Embedding(100, 64, dtype=torch.bfloat16)
+    loss = ssi_b200.FusedLinearCrossEntropyLoss(emb)
+    h = torch.randn(2, 8, 64, dtype=torch.bfloat16)
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        loss(h, torch.zeros(2, 8, dtype=torch.int64))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        ops.embedding_grad_scatter(torch.zeros(4, 64, dtype=torch.bfloat16), torch.zeros(4, dtype=torch.int64),
+                                   torch.zeros(10, 64, dtype=torch.bfloat16))
+
+
+def test_install_swaps_output_and_embedding_without_touching_state_dict():
+    class Tiny(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.tok_embeddings = nn.Embedding(50, 16)
+            self.output = lambda x: x @ self.tok_embeddings.weight.t()
+            self.num_output_chunks = 0
+
+        def set_num_output_chunks(self, n):
+            self.num_output_chunks = n
+
+    m = Tiny()
+    w = m.tok_embeddings.weight
+    keys = list(m.state_dict().keys())
+    loss = ssi_b200.install(m)
+    assert list(m.state_dict().keys()) == keys == ["tok_embeddings.weight"]
+    assert m.tok_embeddings.weight is w and isinstance(m.tok_embeddings, ssi_b200.TiedEmbeddingB200)
+    assert isinstance(m.output, ssi_b200.HiddenPassthroughOutput) and m.output.tied_module is m.tok_embeddings
+    assert m.num_output_chunks == loss.num_output_chunks == 8  # ssi/trainer.py:303-304
+    x = torch.randn(2, 3, 16)
+    assert m.output(x) is x
+    # CPU forward of the swapped embedding still works (plain gather)
+    assert m.tok_embeddings(torch.tensor([[1, 2]])).shape == (1, 2, 16)
+
+
+def test_vocab_sizes_follow_reference_formula():
+    # ssi/llama_configs.py:98-99: 128000 + 256 + n_dsus + 2 modality tokens
+    assert synth.CONFIGS["c1"].vocab == 133258
+    assert synth.CONFIGS["c2"].vocab == 129282
+    assert synth.CONFIGS["c3"].vocab == 130306
+    assert synth.CONFIGS["c4"].vocab == 136450
+    assert synth.CONFIGS["c5"].rows == 131072
+
+
+@pytest.mark.parametrize("name", ["c1", "c2", "c3", "c4"])
+def test_synth_tokens_in_range_and_deterministic(name):
+    cfg = synth.CONFIGS[name]
+    g1, g2 = torch.Generator().manual_seed(3), torch.Generator().manual_seed(3)
+    t1, l1 = synth.make_tokens_labels(cfg, g1, batch=2)
+    t2, l2 = synth.make_tokens_labels(cfg, g2, batch=2)
+    assert torch.equal(t1, t2) and torch.equal(l1, l2)
+    assert t1.min() >= 0 and t1.max() < cfg.vocab
+    assert ((l1 == -100) | ((l1 >= 0) & (l1 < cfg.vocab))).all()
+    if name == "c2":
+        assert (l1 == -100).float().mean() > 0.3  # prompt + padding masked
+    if name in ("c1", "c3"):
+        assert (l1 != -100).all()  # labels = tokens (ssi/data/cpt.py:153)
+
+
+def test_shard_rows_partitions_exactly():
+    for n, w in [(64, 8), (64, 3), (5, 8), (16, 1)]:
+        spans = [ddist.shard_rows(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
+        assert max(e - b for b, e in spans) - min(e - b for b, e in spans) <= 1
