@@ -50,6 +50,11 @@ int64_t ssi_b200_launch_count(void);
 int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes, size_t* bwd_bytes,
                              size_t* scatter_bytes);
 
+/* Tile schedule the library will use for this problem: out[8] = {forward vocabulary splits, 256-column tiles
+ * per split, 128-row token tiles, 256-column vocabulary tiles, backward dlogits blocks, tiles per block,
+ * block width in columns, padded rows}. Host only. */
+int ssi_b200_plan_info(int64_t N, int64_t V, int64_t D, int64_t* out);
+
 /*
  * Forward: logits = X * W^T are produced tile by tile in tensor memory and consumed by an online
  * log-sum-exp epilogue; they never reach HBM.

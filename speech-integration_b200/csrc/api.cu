@@ -8,6 +8,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <vector>
@@ -188,18 +189,25 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int sms) {
   f.tiles_m = static_cast<int>(f.n_pad / ssi::BM);
   f.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
   // pick the number of vocabulary splits that minimises the persistent-grid makespan (in tile units)
-  long long best_cost = -1;
-  int best_s = 1;
+  // cost(s) = makespan in tile units on a static persistent grid; take the SMALLEST s within 1% of the best
+  // (fewer splits = fewer partials to combine and longer register-resident sweeps).
   const int max_s = f.vtiles_total < 148 ? f.vtiles_total : 148;
-  for (int s = 1; s <= max_s; ++s) {
+  auto cost_of = [&](int s) -> long long {
     const int per = static_cast<int>(ceil_div(f.vtiles_total, s));
-    const int s_eff = static_cast<int>(ceil_div(f.vtiles_total, per));
-    if (s_eff != s) continue;
-    const long long items = static_cast<long long>(f.tiles_m) * s;
-    const long long cost = ceil_div(items, sms) * per;
-    if (best_cost < 0 || cost < best_cost) {
-      best_cost = cost;
+    if (static_cast<int>(ceil_div(f.vtiles_total, per)) != s) return -1;
+    return ceil_div(static_cast<long long>(f.tiles_m) * s, sms) * per;
+  };
+  long long best_cost = -1;
+  for (int s = 1; s <= max_s; ++s) {
+    const long long c = cost_of(s);
+    if (c >= 0 && (best_cost < 0 || c < best_cost)) best_cost = c;
+  }
+  int best_s = 1;
+  for (int s = 1; s <= max_s; ++s) {
+    const long long c = cost_of(s);
+    if (c >= 0 && c * 100 <= best_cost * 101) {
       best_s = s;
+      break;
     }
   }
   f.splits = best_s;
@@ -216,6 +224,27 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int sms) {
   return f;
 }
 
+// Tuning knobs (environment, read once): for experiments from bench.py without rebuilding.
+struct Tune {
+  int64_t g_cap_elems = int64_t(1) << 31;  // dlogits block scratch cap: 4 GiB of bf16
+  int64_t g_tiles = 0;                     // force the block width (256-column tiles); 0 = auto
+  int group_m_grad = 16, group_m_dw = 16, group_m_dx = 16;
+  int store_hint = 0;  // 1 = evict-first L2 policy on the dlogits / dW / dX tile stores
+};
+const Tune& tune() {
+  static Tune t = [] {
+    Tune x;
+    if (const char* e = getenv("SSI_B200_G_CAP_MIB")) x.g_cap_elems = atoll(e) * (int64_t(1) << 19);
+    if (const char* e = getenv("SSI_B200_G_TILES")) x.g_tiles = atoll(e);
+    if (const char* e = getenv("SSI_B200_GROUP_M_GRAD")) x.group_m_grad = atoi(e);
+    if (const char* e = getenv("SSI_B200_GROUP_M_DW")) x.group_m_dw = atoi(e);
+    if (const char* e = getenv("SSI_B200_GROUP_M_DX")) x.group_m_dx = atoi(e);
+    if (const char* e = getenv("SSI_B200_STORE_HINT")) x.store_hint = atoi(e);
+    return x;
+  }();
+  return t;
+}
+
 struct BwdPlan {
   int64_t n_pad;
   int tiles_m, vtiles_total, nblocks, vtiles_per_block;
@@ -228,12 +257,27 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   b.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
   b.tiles_m = static_cast<int>(b.n_pad / ssi::BM);
   b.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
-  const int64_t target_elems = int64_t(1) << 29;  // 1 GiB of bf16 dlogits per block
-  int64_t tiles = target_elems / b.n_pad / ssi::BN;
-  if (tiles < 4) tiles = 4;
-  if (tiles > b.vtiles_total) tiles = b.vtiles_total;
-  b.nblocks = static_cast<int>(ceil_div(b.vtiles_total, tiles));
-  b.vtiles_per_block = static_cast<int>(ceil_div(b.vtiles_total, b.nblocks));
+  // Block width t (in 256-column tiles): as wide as the dlogits scratch cap allows, chosen so that the dW
+  // contraction of a block (2t x ceil(D/256) output tiles on 148 persistent CTAs) wastes the fewest waves;
+  // a small per-block charge prefers fewer, longer launches.
+  const int64_t cap_elems = tune().g_cap_elems;
+  int64_t t_max = cap_elems / b.n_pad / ssi::BN;
+  if (t_max < 4) t_max = 4;
+  if (t_max > b.vtiles_total) t_max = b.vtiles_total;
+  const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
+  const int sms = 148;
+  int64_t best_t = t_max;
+  double best_cost = -1.0;
+  for (int64_t t = (tune().g_tiles > 0 ? tune().g_tiles : 4); t <= t_max; ++t) {
+    const int64_t full = b.vtiles_total / t, rem = b.vtiles_total % t;
+    double waves = static_cast<double>(full) * ceil_div(2 * t * d_tiles, sms);
+    if (rem) waves += ceil_div(2 * rem * d_tiles, sms);
+    const double cost = waves + 0.25 * (full + (rem ? 1 : 0));
+    if (best_cost < 0 || cost <= best_cost) best_cost = cost, best_t = t;
+    if (tune().g_tiles > 0) break;
+  }
+  b.vtiles_per_block = static_cast<int>(best_t);
+  b.nblocks = static_cast<int>(ceil_div(b.vtiles_total, best_t));
   b.vc = static_cast<int64_t>(b.vtiles_per_block) * ssi::BN;
   size_t o = 0;
   b.off_g = o, o += align_up(static_cast<size_t>(b.n_pad) * b.vc * 2, 1024);
@@ -391,7 +435,8 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       memset(&p, 0, sizeof(p));
       p.tmA = tmX_k, p.tmB = tmW_k, p.tmC = tmG_st;
       p.tiles_m = b.tiles_m, p.tiles_n = vtn, p.k_blocks = static_cast<int>(D / ssi::BK);
-      p.group_m = 16;
+      p.group_m = tune().group_m_grad;
+      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.b_r0 = v0;
       p.labels = labels, p.ignore_index = ignore_index;
       p.n_rows = static_cast<int>(N), p.vocab = static_cast<int>(V), p.col0 = v0;
@@ -407,7 +452,8 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.tiles_m = static_cast<int>(ceil_div(vrows, ssi::BM));
       p.tiles_n = d_tiles;
       p.k_blocks = static_cast<int>(b.n_pad / ssi::BK);
-      p.group_m = 16;
+      p.group_m = tune().group_m_dw;
+      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.c_r0 = v0;
       p.c_reduce = accumulate_dW ? 1 : 0;
       if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
@@ -419,7 +465,8 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.tmA = tmG_k, p.tmB = tmW_mn, p.tmC = tmdX;
       p.tiles_m = b.tiles_m, p.tiles_n = d_tiles;
       p.k_blocks = vtn * (ssi::BN / ssi::BK);
-      p.group_m = 16;
+      p.group_m = tune().group_m_dx;
+      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.b_k0 = v0;
       p.c_reduce = (blk > 0) ? 1 : 0;
       if (b.nblocks > 1) {
@@ -501,6 +548,17 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
   ssi::label_shift_count_kernel<<<grid, 256, 0, st>>>(labels, B, S, ignore_index, labels_out,
                                                       reinterpret_cast<unsigned long long*>(counts));
   SSI_LAUNCH_OK("label_shift_count");
+  return 0;
+}
+
+int ssi_b200_plan_info(int64_t N, int64_t V, int64_t D, int64_t* out) {
+  SSI_CHECK_ARG(out, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64 && D % 64 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
+                (long long)V, (long long)D);
+  const FwdPlan f = plan_fwd(N, V, 148);
+  const BwdPlan b = plan_bwd(N, V, D);
+  out[0] = f.splits, out[1] = f.vtiles_per_split, out[2] = f.tiles_m, out[3] = f.vtiles_total;
+  out[4] = b.nblocks, out[5] = b.vtiles_per_block, out[6] = b.vc, out[7] = b.n_pad;
   return 0;
 }
 

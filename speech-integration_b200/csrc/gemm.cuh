@@ -43,6 +43,7 @@ struct GemmParams {
   int tiles_m, tiles_n, k_blocks, group_m;
   int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
+  unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
   // ---- EPI_LSE / EPI_GRAD
   const int64_t* labels;
   long long ignore_index;
@@ -334,7 +335,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer) {
-              tma_store_2d(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM);
+              if (p.store_policy)
+                tma_store_2d_hint(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM, p.store_policy);
+              else
+                tma_store_2d(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM);
               tma_commit_group();
             }
             ++chunk_ctr;
@@ -365,6 +369,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + it.m * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
+              else if (p.store_policy)
+                tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
               else
                 tma_store_2d(&p.tmC, buf, cc, cr);
               tma_commit_group();
@@ -396,6 +402,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + it.m * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
+              else if (p.store_policy)
+                tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
               else
                 tma_store_2d(&p.tmC, buf, cc, cr);
               tma_commit_group();

@@ -22,6 +22,7 @@ SYMBOLS = {
         c_int,
         [c_int64, c_int64, c_int64, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)],
     ),
+    "ssi_b200_plan_info": (c_int, [c_int64, c_int64, c_int64, c_void_p]),
     "ssi_b200_lmhead_ce_fwd": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
@@ -109,3 +110,11 @@ def profile_end() -> dict[str, tuple[float, int]]:
     cnt = (ctypes.c_int64 * 8)()
     check(load().ssi_b200_profile_end(ctypes.cast(ms, c_void_p), ctypes.cast(cnt, c_void_p)), "profile_end")
     return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(6)}
+
+
+def plan_info(N: int, V: int, D: int) -> dict[str, int]:
+    out = (ctypes.c_int64 * 8)()
+    check(load().ssi_b200_plan_info(N, V, D, ctypes.cast(out, c_void_p)), "plan_info")
+    keys = ("fwd_splits", "vtiles_per_split", "tiles_m", "vtiles_total", "bwd_blocks", "vtiles_per_block",
+            "block_cols", "rows_padded")
+    return {k: int(out[i]) for i, k in enumerate(keys)}
