@@ -46,7 +46,8 @@ const char* ssi_b200_last_error(void);
  * (used by bench.py for its gpu_launches claim). */
 int64_t ssi_b200_launch_count(void);
 
-/* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. */
+/* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. Workspaces must be 256-byte
+ * aligned. */
 int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes, size_t* bwd_bytes,
                              size_t* scatter_bytes);
 
@@ -58,7 +59,8 @@ int ssi_b200_plan_info(int64_t N, int64_t V, int64_t D, int64_t* out);
 /*
  * Forward: logits = X * W^T are produced tile by tile in tensor memory and consumed by an online
  * log-sum-exp epilogue; they never reach HBM.
- *   lse      [N]  out  fp32 natural-log logsumexp per row (saved for backward)
+ *   lse      [N]  out  fp32 natural-log logsumexp per row (saved for backward); 0 for ignored rows, which are
+ *                      compacted away before the tensor-core stages and never touch them
  *   loss_out [2]  out  fp32 {sum over valid rows of (lse - z_label), that sum / n_valid}
  *                      (n_valid == 0 -> loss_out[1] = NaN, as 0/0 in ce_chunked_output_loss.py:83)
  *   n_valid  [1]  out  int64 count of labels != ignore_index (ce_chunked_output_loss.py:66)

@@ -156,16 +156,17 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
 }
 
 template <int EPI, bool A_MN, bool B_MN>
-int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat) {
+int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat,
+                int grid_override = 0) {
   auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     SSI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::GEMM_SMEM_BYTES));
     attr_set = true;
   }
-  const int items = p.tiles_m * p.tiles_n;
-  if (items <= 0) return 0;
-  const int grid = items < sms ? items : sms;
+  const int items = p.tiles_m * p.tiles_n;  // host-side upper bound when the schedule is device-side
+  if (items <= 0 && grid_override <= 0) return 0;
+  const int grid = grid_override > 0 ? grid_override : (items < sms ? items : sms);
   {
     ProfScope ps(cat, st);
     kern<<<grid, ssi::GEMM_THREADS, ssi::GEMM_SMEM_BYTES, st>>>(p);
@@ -177,44 +178,40 @@ int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* 
 // ---------------------------------------------------------------------------------------------------
 // Schedules
 // ---------------------------------------------------------------------------------------------------
+// Workspace layouts.  Sizes depend on (N, V, D) only; everything that depends on the number of VALID rows is
+// decided on the device (ssi::DevPlan).
+struct CompactWs {  // shared head of the forward and backward workspaces
+  size_t off_plan, off_pos, off_idx, off_labels_c, off_xc, end;
+};
+CompactWs plan_compact(int64_t N, int64_t n_pad, int64_t D, size_t o) {
+  CompactWs c;
+  c.off_plan = o, o += 256;
+  c.off_pos = o, o += align_up(static_cast<size_t>(N) * sizeof(int), 256);
+  c.off_idx = o, o += align_up(static_cast<size_t>(n_pad) * sizeof(int), 256);
+  c.off_labels_c = o, o += align_up(static_cast<size_t>(n_pad) * sizeof(int64_t), 256);
+  c.off_xc = o, o += align_up(static_cast<size_t>(n_pad) * D * 2, 1024);
+  c.end = o;
+  return c;
+}
+
 struct FwdPlan {
   int64_t n_pad;
-  int tiles_m, vtiles_total, splits, vtiles_per_split, combine_blocks;
+  int tiles_m, vtiles_total, combine_blocks;
+  CompactWs cw;
   size_t off_m, off_l, off_z, off_bl, off_bc, bytes;
 };
 
-FwdPlan plan_fwd(int64_t N, int64_t V, int sms) {
+FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
   FwdPlan f;
   f.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
   f.tiles_m = static_cast<int>(f.n_pad / ssi::BM);
   f.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
-  // pick the number of vocabulary splits that minimises the persistent-grid makespan (in tile units)
-  // cost(s) = makespan in tile units on a static persistent grid; take the SMALLEST s within 1% of the best
-  // (fewer splits = fewer partials to combine and longer register-resident sweeps).
-  const int max_s = f.vtiles_total < 148 ? f.vtiles_total : 148;
-  auto cost_of = [&](int s) -> long long {
-    const int per = static_cast<int>(ceil_div(f.vtiles_total, s));
-    if (static_cast<int>(ceil_div(f.vtiles_total, per)) != s) return -1;
-    return ceil_div(static_cast<long long>(f.tiles_m) * s, sms) * per;
-  };
-  long long best_cost = -1;
-  for (int s = 1; s <= max_s; ++s) {
-    const long long c = cost_of(s);
-    if (c >= 0 && (best_cost < 0 || c < best_cost)) best_cost = c;
-  }
-  int best_s = 1;
-  for (int s = 1; s <= max_s; ++s) {
-    const long long c = cost_of(s);
-    if (c >= 0 && c * 100 <= best_cost * 101) {
-      best_s = s;
-      break;
-    }
-  }
-  f.splits = best_s;
-  f.vtiles_per_split = static_cast<int>(ceil_div(f.vtiles_total, best_s));
   f.combine_blocks = static_cast<int>(ceil_div(N, ssi::COMBINE_THREADS));
-  size_t o = 0;
-  const size_t part = align_up(static_cast<size_t>(f.splits) * f.n_pad * sizeof(float), 256);
+  f.cw = plan_compact(N, f.n_pad, D, 0);
+  size_t o = f.cw.end;
+  // per-split partials: the device plan keeps tiles_m * splits <= max(MAX_LSE_ITEMS, tiles_m)
+  const size_t items = f.tiles_m > ssi::MAX_LSE_ITEMS ? f.tiles_m : ssi::MAX_LSE_ITEMS;
+  const size_t part = align_up(items * ssi::BM * sizeof(float), 256);
   f.off_m = o, o += part;
   f.off_l = o, o += part;
   f.off_z = o, o += part;
@@ -249,7 +246,8 @@ struct BwdPlan {
   int64_t n_pad;
   int tiles_m, vtiles_total, nblocks, vtiles_per_block;
   int64_t vc;  // columns of the dlogits block buffer
-  size_t off_g, off_dxacc, bytes;
+  CompactWs cw;
+  size_t off_lse_c, off_g, off_dxacc, bytes;
 };
 
 BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
@@ -279,10 +277,11 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   b.vtiles_per_block = static_cast<int>(best_t);
   b.nblocks = static_cast<int>(ceil_div(b.vtiles_total, best_t));
   b.vc = static_cast<int64_t>(b.vtiles_per_block) * ssi::BN;
-  size_t o = 0;
+  b.cw = plan_compact(N, b.n_pad, D, 0);
+  size_t o = b.cw.end;
+  b.off_lse_c = o, o += align_up(static_cast<size_t>(b.n_pad) * sizeof(float), 256);
   b.off_g = o, o += align_up(static_cast<size_t>(b.n_pad) * b.vc * 2, 1024);
-  b.off_dxacc = o;
-  if (b.nblocks > 1) o += align_up(static_cast<size_t>(N) * D * sizeof(float), 1024);
+  b.off_dxacc = o, o += align_up(static_cast<size_t>(b.n_pad) * D * sizeof(float), 1024);
   b.bytes = o;
   return b;
 }
@@ -338,8 +337,7 @@ int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes,
                 (long long)V, (long long)D);
   if (fwd_bytes || bwd_bytes)
     SSI_CHECK_ARG(D % 64 == 0, "D=%lld must be a multiple of 64 for the LM-head kernels", (long long)D);
-  const int sms = 148;  // the plan (and so the size) must not depend on a device being present
-  if (fwd_bytes) *fwd_bytes = plan_fwd(N, V, sms).bytes;
+  if (fwd_bytes) *fwd_bytes = plan_fwd(N, V, D).bytes;
   if (bwd_bytes) *bwd_bytes = plan_bwd(N, V, D).bytes;
   if (scatter_bytes) *scatter_bytes = plan_scatter(N, V, D).bytes;
   return 0;
@@ -353,38 +351,56 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  // The split count is sized for 148 SMs so that workspace_bytes() is device independent.
-  const FwdPlan f = plan_fwd(N, V, 148);
+  const FwdPlan f = plan_fwd(N, V, D);
   SSI_CHECK_ARG(ws_bytes >= f.bytes, "forward workspace too small: %zu < %zu", ws_bytes, f.bytes);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-byte aligned");
   char* wsb = static_cast<char*>(ws);
+  ssi::DevPlan* dplan = reinterpret_cast<ssi::DevPlan*>(wsb + f.cw.off_plan);
+  int* pos = reinterpret_cast<int*>(wsb + f.cw.off_pos);
+  int* idx = reinterpret_cast<int*>(wsb + f.cw.off_idx);
+  int64_t* labels_c = reinterpret_cast<int64_t*>(wsb + f.cw.off_labels_c);
+  void* Xc = wsb + f.cw.off_xc;
+
+  // ---- compaction of the valid rows + device-side schedule
+  {
+    ProfScope ps(CAT_AUX, st);
+    ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(f.n_pad),
+                                                  ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms);
+    SSI_LAUNCH_OK("compact_scan");
+    ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
+                                                         static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
+                                                         nullptr);
+    SSI_LAUNCH_OK("gather_rows");
+  }
 
   ssi::GemmParams p;
   memset(&p, 0, sizeof(p));
-  if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, ssi::BM)) return r;
+  if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
   if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
-  p.tiles_m = f.tiles_m;
-  p.tiles_n = f.splits;
+  p.dplan = dplan;
+  p.m_from_plan = 1;
+  p.tiles_m = f.tiles_m;  // upper bounds; the kernel takes tiles_m / splits from *dplan
+  p.tiles_n = 1;
   p.k_blocks = static_cast<int>(D / ssi::BK);
   p.group_m = f.tiles_m;  // all m-tiles of one split run together: they stream the same W tiles through L2
-  p.labels = labels;
+  p.labels = labels_c;
   p.ignore_index = ignore_index;
-  p.n_rows = static_cast<int>(N);
+  p.n_rows = static_cast<int>(f.n_pad);
   p.vocab = static_cast<int>(V);
   p.col0 = 0;
-  p.vtiles_per_split = f.vtiles_per_split;
+  p.vtiles_per_split = f.vtiles_total;
   p.vtiles_total = f.vtiles_total;
   p.part_m = reinterpret_cast<float*>(wsb + f.off_m);
   p.part_l = reinterpret_cast<float*>(wsb + f.off_l);
   p.part_z = reinterpret_cast<float*>(wsb + f.off_z);
   p.part_stride = static_cast<int>(f.n_pad);
-  if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse", CAT_LSE)) return r;
+  if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse", CAT_LSE, di->sms)) return r;
 
   ProfScope ps_aux(CAT_AUX, st);
   float* blk_loss = reinterpret_cast<float*>(wsb + f.off_bl);
   int* blk_cnt = reinterpret_cast<int*>(wsb + f.off_bc);
   ssi::lse_combine_kernel<<<f.combine_blocks, ssi::COMBINE_THREADS, 0, st>>>(
-      p.part_m, p.part_l, p.part_z, f.splits, p.part_stride, labels, ignore_index, static_cast<int>(N), lse, blk_loss,
-      blk_cnt);
+      p.part_m, p.part_l, p.part_z, dplan, pos, static_cast<int>(N), lse, blk_loss, blk_cnt);
   SSI_LAUNCH_OK("lse_combine");
   ssi::loss_finalize_kernel<<<1, 256, 0, st>>>(blk_loss, blk_cnt, f.combine_blocks, loss_out, n_valid);
   SSI_LAUNCH_OK("loss_finalize");
@@ -402,15 +418,33 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const BwdPlan b = plan_bwd(N, V, D);
   SSI_CHECK_ARG(ws_bytes >= b.bytes, "backward workspace too small: %zu < %zu", ws_bytes, b.bytes);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-byte aligned");
   char* wsb = static_cast<char*>(ws);
+  ssi::DevPlan* dplan = reinterpret_cast<ssi::DevPlan*>(wsb + b.cw.off_plan);
+  int* pos = reinterpret_cast<int*>(wsb + b.cw.off_pos);
+  int* idx = reinterpret_cast<int*>(wsb + b.cw.off_idx);
+  int64_t* labels_c = reinterpret_cast<int64_t*>(wsb + b.cw.off_labels_c);
+  void* Xc = wsb + b.cw.off_xc;
+  float* lse_c = reinterpret_cast<float*>(wsb + b.off_lse_c);
   void* G = wsb + b.off_g;
   float* dxacc = reinterpret_cast<float*>(wsb + b.off_dxacc);
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
 
-  // tensor maps that do not change across vocabulary blocks
+  // ---- the same compaction as forward (stateless ABI: recomputed from the labels, ~0.1 ms)
+  {
+    ProfScope ps(CAT_AUX, st);
+    ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(b.n_pad),
+                                                  ignore_index, pos, idx, labels_c, dplan, b.vtiles_total, di->sms);
+    SSI_LAUNCH_OK("compact_scan");
+    ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
+                                                         static_cast<int>(D / 8), static_cast<uint4*>(Xc), lse, lse_c);
+    SSI_LAUNCH_OK("gather_rows");
+  }
+
+  // tensor maps that do not change across vocabulary blocks (X_c and G hold COMPACT rows)
   CUtensorMap tmX_k, tmX_mn, tmW_k, tmW_mn, tmG_st, tmG_k, tmG_mn, tmdW, tmdX;
-  if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, ssi::BM)) return r;
-  if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, X, D, N, D * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, b.n_pad, D * 2, 64, ssi::BM)) return r;
+  if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, b.n_pad, D * 2, 64, 64)) return r;
   if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
   if (int r = make_tmap(&tmW_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, 64)) return r;
   if (int r = make_tmap(&tmG_st, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, G, b.vc, b.n_pad, b.vc * 2, 64, ssi::BM))
@@ -418,11 +452,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
   tmG_k = tmG_st;  // K-major A operand of dX = G W uses the same {64 v, 128 tok} box
   if (int r = make_tmap(&tmG_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, G, b.vc, b.n_pad, b.vc * 2, 64, 64)) return r;
   if (int r = make_tmap(&tmdW, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dW, D, V, D * 2, 64, ssi::BM)) return r;
-  if (b.nblocks > 1) {
-    if (int r = make_tmap(&tmdX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dxacc, D, N, D * 4, 32, ssi::BM)) return r;
-  } else {
-    if (int r = make_tmap(&tmdX, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dX, D, N, D * 2, 64, ssi::BM)) return r;
-  }
+  if (int r = make_tmap(&tmdX, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dxacc, D, b.n_pad, D * 4, 32, ssi::BM)) return r;
 
   for (int blk = 0; blk < b.nblocks; ++blk) {
     const int vt0 = blk * b.vtiles_per_block;
@@ -434,20 +464,22 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       ssi::GemmParams p;
       memset(&p, 0, sizeof(p));
       p.tmA = tmX_k, p.tmB = tmW_k, p.tmC = tmG_st;
+      p.dplan = dplan, p.m_from_plan = 1;
       p.tiles_m = b.tiles_m, p.tiles_n = vtn, p.k_blocks = static_cast<int>(D / ssi::BK);
       p.group_m = tune().group_m_grad;
       p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.b_r0 = v0;
-      p.labels = labels, p.ignore_index = ignore_index;
-      p.n_rows = static_cast<int>(N), p.vocab = static_cast<int>(V), p.col0 = v0;
-      p.lse = lse, p.grad_out = grad_out, p.n_valid = n_valid_total;
+      p.labels = labels_c, p.ignore_index = ignore_index;
+      p.n_rows = static_cast<int>(b.n_pad), p.vocab = static_cast<int>(V), p.col0 = v0;
+      p.lse = lse_c, p.grad_out = grad_out, p.n_valid = n_valid_total;
       if (int r = launch_gemm<ssi::EPI_GRAD, false, false>(p, di->sms, st, "lmhead_dlogits", CAT_DLOGITS)) return r;
     }
-    // ---- K2b: dW[v0 : v0 + rows) (+)= G^T X   (M = vocabulary rows, N = D, K = tokens)
+    // ---- K2b: dW[v0 : v0 + rows) (+)= G^T X_c   (M = vocabulary rows, N = D, K = valid tokens)
     {
       ssi::GemmParams p;
       memset(&p, 0, sizeof(p));
       p.tmA = tmG_mn, p.tmB = tmX_mn, p.tmC = tmdW;
+      p.dplan = dplan, p.k_from_plan = 1;
       const int64_t vrows = (V - v0) < int64_t(vtn) * ssi::BN ? (V - v0) : int64_t(vtn) * ssi::BN;
       p.tiles_m = static_cast<int>(ceil_div(vrows, ssi::BM));
       p.tiles_n = d_tiles;
@@ -458,31 +490,27 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.c_reduce = accumulate_dW ? 1 : 0;
       if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
     }
-    // ---- K2c: dX (+)= G W[v0 : v0 + vtn*256)   (M = tokens, N = D, K = vocabulary block)
+    // ---- K2c: dXacc_c (+)= G W[v0 : v0 + vtn*256)   (M = valid tokens, N = D, K = vocabulary block)
     {
       ssi::GemmParams p;
       memset(&p, 0, sizeof(p));
       p.tmA = tmG_k, p.tmB = tmW_mn, p.tmC = tmdX;
+      p.dplan = dplan, p.m_from_plan = 1;
       p.tiles_m = b.tiles_m, p.tiles_n = d_tiles;
       p.k_blocks = vtn * (ssi::BN / ssi::BK);
       p.group_m = tune().group_m_dx;
-      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.b_k0 = v0;
       p.c_reduce = (blk > 0) ? 1 : 0;
-      if (b.nblocks > 1) {
-        if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX_f32", CAT_DX)) return r;
-      } else {
-        if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX_bf16", CAT_DX)) return r;
-      }
+      if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
     }
   }
-  if (b.nblocks > 1) {
-    const size_t n4 = static_cast<size_t>(N) * D / 4;
-    const int grid = di->sms * 8;
+  {
+    // dX[r] = bf16(dXacc_c[pos[r]]) for valid rows, exact zeros for ignored rows
     ProfScope ps_aux(CAT_AUX, st);
-    ssi::cast_f32_bf16_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(dxacc),
-                                                    reinterpret_cast<uint2*>(dX), n4);
-    SSI_LAUNCH_OK("cast_dX");
+    ssi::dx_finalize_kernel<<<di->sms * 8, 256, 0, st>>>(reinterpret_cast<const float4*>(dxacc), pos,
+                                                         static_cast<int>(N), static_cast<int>(D / 4),
+                                                         reinterpret_cast<uint2*>(dX));
+    SSI_LAUNCH_OK("dx_finalize");
   }
   return 0;
 }
@@ -555,9 +583,9 @@ int ssi_b200_plan_info(int64_t N, int64_t V, int64_t D, int64_t* out) {
   SSI_CHECK_ARG(out, "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64 && D % 64 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
-  const FwdPlan f = plan_fwd(N, V, 148);
+  const FwdPlan f = plan_fwd(N, V, D);
   const BwdPlan b = plan_bwd(N, V, D);
-  out[0] = f.splits, out[1] = f.vtiles_per_split, out[2] = f.tiles_m, out[3] = f.vtiles_total;
+  out[0] = 0, out[1] = 0, out[2] = f.tiles_m, out[3] = f.vtiles_total;  // splits are chosen on the device
   out[4] = b.nblocks, out[5] = b.vtiles_per_block, out[6] = b.vc, out[7] = b.n_pad;
   return 0;
 }

@@ -12,34 +12,169 @@
 namespace ssi {
 
 // ---------------------------------------------------------------------------------------------------
+// Row compaction: rows whose label is ignore_index contribute nothing to the loss or to any gradient, so the
+// tensor-core stages only see the valid rows, gathered into a dense X_c.  The valid count lives on the device;
+// the tile schedule that depends on it (DevPlan) is computed on the device too, so there is no host sync.
+// ---------------------------------------------------------------------------------------------------
+struct DevPlan {
+  int n_valid;           // rows with label != ignore_index
+  int tiles_m;           // ceil(n_valid / 128)
+  int splits;            // K1: vocabulary splits
+  int vtiles_per_split;  // K1: 256-column tiles per split
+  int k_blocks_tok;      // K2b: K loop over tokens = tiles_m * 2 (64-row blocks)
+  int part_stride;       // K1 partial arrays: floats per split = tiles_m * 128
+  int pad0, pad1;
+};
+constexpr int MAX_LSE_ITEMS = 8192;  // cap on tiles_m * splits (bounds the partial arrays)
+
+// One block: stable compaction of the valid rows. pos[r] = compact position or -1, idx[c] = original row,
+// labels_c[c] = label (ignore_index beyond n_valid up to n_pad), then the device-side plan.
+__global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __restrict__ labels, int n, int n_pad,
+                                                            long long ignore_index, int* __restrict__ pos,
+                                                            int* __restrict__ idx, int64_t* __restrict__ labels_c,
+                                                            DevPlan* __restrict__ plan, int vtiles_total, int sms) {
+  __shared__ int s_sum[1024];
+  const int per = (n + 1023) / 1024;
+  const int b = threadIdx.x * per;
+  const int e = min(b + per, n);
+  int a = 0;
+  for (int i = b; i < e; ++i) a += (labels[i] != ignore_index);
+  s_sum[threadIdx.x] = a;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {
+    int v = 0;
+    if (threadIdx.x >= off) v = s_sum[threadIdx.x - off];
+    __syncthreads();
+    s_sum[threadIdx.x] += v;
+    __syncthreads();
+  }
+  int run = (threadIdx.x == 0) ? 0 : s_sum[threadIdx.x - 1];
+  const int n_valid = s_sum[1023];
+  for (int i = b; i < e; ++i) {
+    const long long l = labels[i];
+    if (l != ignore_index) {
+      pos[i] = run;
+      idx[run] = i;
+      labels_c[run] = l;
+      ++run;
+    } else {
+      pos[i] = -1;
+    }
+  }
+  for (int i = n_valid + threadIdx.x; i < n_pad; i += 1024) labels_c[i] = ignore_index;
+  if (threadIdx.x == 0) {
+    DevPlan d;
+    d.n_valid = n_valid;
+    d.tiles_m = (n_valid + 127) / 128;
+    d.k_blocks_tok = d.tiles_m * 2;
+    d.part_stride = d.tiles_m * 128;
+    // K1 split count: smallest s whose static-schedule makespan is within 1% of the best
+    int best_s = 1;
+    if (d.tiles_m > 0) {
+      const int max_s = min(vtiles_total, 148);
+      long long best = -1;
+      for (int pass = 0; pass < 2; ++pass) {
+        for (int s2 = 1; s2 <= max_s; ++s2) {
+          if (s2 > 1 && static_cast<long long>(s2) * d.tiles_m > MAX_LSE_ITEMS) break;
+          const int pr = (vtiles_total + s2 - 1) / s2;
+          if ((vtiles_total + pr - 1) / pr != s2) continue;
+          const long long items = static_cast<long long>(d.tiles_m) * s2;
+          const long long c = ((items + sms - 1) / sms) * pr;
+          if (pass == 0) {
+            if (best < 0 || c < best) best = c;
+          } else if (c * 100 <= best * 101) {
+            best_s = s2;
+            break;
+          }
+        }
+      }
+    }
+    d.splits = best_s;
+    d.vtiles_per_split = (vtiles_total + best_s - 1) / best_s;
+    d.pad0 = d.pad1 = 0;
+    *plan = d;
+  }
+}
+
+// X_c[c, :] = X[idx[c], :] for c < n_valid, zeros for the padding rows of the last 128-row tile; optionally
+// lse_c[c] = lse[idx[c]].  One warp per compact row, 16-byte accesses.
+__global__ void __launch_bounds__(256) gather_rows_kernel(const uint4* __restrict__ X, const int* __restrict__ idx,
+                                                          const DevPlan* __restrict__ plan, int row_u4,
+                                                          uint4* __restrict__ Xc, const float* __restrict__ lse,
+                                                          float* __restrict__ lse_c) {
+  const int n_valid = plan->n_valid;
+  const int rows = plan->tiles_m * 128;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < rows; c += warps) {
+    uint4* dst = Xc + static_cast<size_t>(c) * row_u4;
+    if (c < n_valid) {
+      const int r = idx[c];
+      const uint4* src = X + static_cast<size_t>(r) * row_u4;
+      for (int j = lane; j < row_u4; j += 32) dst[j] = __ldg(src + j);
+      if (lse_c && lane == 0) lse_c[c] = lse[r];
+    } else {
+      for (int j = lane; j < row_u4; j += 32) dst[j] = make_uint4(0, 0, 0, 0);
+      if (lse_c && lane == 0) lse_c[c] = 0.f;
+    }
+  }
+}
+
+// dX[r, :] = bf16(dXacc_c[pos[r], :]) for valid rows, zeros for ignored rows. One warp per original row.
+__global__ void __launch_bounds__(256) dx_finalize_kernel(const float4* __restrict__ acc, const int* __restrict__ pos,
+                                                          int n, int row_f4, uint2* __restrict__ dX) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n; r += warps) {
+    const int c = pos[r];
+    uint2* dst = dX + static_cast<size_t>(r) * row_f4;
+    if (c >= 0) {
+      const float4* src = acc + static_cast<size_t>(c) * row_f4;
+      for (int j = lane; j < row_f4; j += 32) {
+        const float4 v = src[j];
+        uint2 o;
+        o.x = pack_bf16x2(v.x, v.y);
+        o.y = pack_bf16x2(v.z, v.w);
+        dst[j] = o;
+      }
+    } else {
+      for (int j = lane; j < row_f4; j += 32) dst[j] = make_uint2(0, 0);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
 // Forward tail: combine the per-split (max, sum, label-logit) partials of each row in split order.
 // ---------------------------------------------------------------------------------------------------
 constexpr int COMBINE_THREADS = 256;
 
 __global__ void __launch_bounds__(COMBINE_THREADS) lse_combine_kernel(
-    const float* __restrict__ part_m, const float* __restrict__ part_l, const float* __restrict__ part_z, int splits,
-    int part_stride, const int64_t* __restrict__ labels, long long ignore_index, int n_rows, float* __restrict__ lse,
+    const float* __restrict__ part_m, const float* __restrict__ part_l, const float* __restrict__ part_z,
+    const DevPlan* __restrict__ plan, const int* __restrict__ pos, int n_rows, float* __restrict__ lse,
     float* __restrict__ blk_loss, int* __restrict__ blk_cnt) {
   __shared__ float s_loss[COMBINE_THREADS];
   __shared__ int s_cnt[COMBINE_THREADS];
-  const int row = blockIdx.x * COMBINE_THREADS + threadIdx.x;
+  const int row = blockIdx.x * COMBINE_THREADS + threadIdx.x;  // ORIGINAL row
+  const int splits = plan->splits, part_stride = plan->part_stride;
   float loss = 0.f;
   int cnt = 0;
   if (row < n_rows) {
-    float M = -INFINITY;
-    for (int s = 0; s < splits; ++s) M = fmaxf(M, part_m[static_cast<size_t>(s) * part_stride + row]);
-    float L = 0.f, z = -INFINITY;
-    for (int s = 0; s < splits; ++s) {
-      const size_t o = static_cast<size_t>(s) * part_stride + row;
-      L += part_l[o] * exp2f(part_m[o] - M);
-      z = fmaxf(z, part_z[o]);
-    }
-    const float l = (M + log2f(L)) * 0.6931471805599453f;
-    lse[row] = l;
-    if (labels[row] != ignore_index) {
+    const int c = pos[row];  // compact position, -1 for ignored rows
+    float l = 0.f;
+    if (c >= 0) {
+      float M = -INFINITY;
+      for (int s = 0; s < splits; ++s) M = fmaxf(M, part_m[static_cast<size_t>(s) * part_stride + c]);
+      float L = 0.f, z = -INFINITY;
+      for (int s = 0; s < splits; ++s) {
+        const size_t o = static_cast<size_t>(s) * part_stride + c;
+        L += part_l[o] * exp2f(part_m[o] - M);
+        z = fmaxf(z, part_z[o]);
+      }
+      l = (M + log2f(L)) * 0.6931471805599453f;
       loss = l - z;
       cnt = 1;
     }
+    lse[row] = l;
   }
   s_loss[threadIdx.x] = loss;
   s_cnt[threadIdx.x] = cnt;
@@ -86,21 +221,6 @@ __global__ void __launch_bounds__(256) loss_finalize_kernel(const float* __restr
     // 0/0 -> NaN exactly like total_loss / total_elements in ce_chunked_output_loss.py:83
     loss_out[1] = static_cast<float>(sum) / static_cast<float>(n);
     n_valid[0] = n;
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------
-// dX accumulator (fp32) -> bf16
-// ---------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) cast_f32_bf16_kernel(const float4* __restrict__ src, uint2* __restrict__ dst,
-                                                            size_t n4) {
-  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n4;
-       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
-    const float4 v = src[i];
-    uint2 o;
-    o.x = pack_bf16x2(v.x, v.y);
-    o.y = pack_bf16x2(v.z, v.w);
-    dst[i] = o;
   }
 }
 

@@ -11,6 +11,7 @@
 #include <cuda_runtime.h>
 #include <cstdint>
 
+#include "aux_kernels.cuh"
 #include "ptx.cuh"
 
 namespace ssi {
@@ -44,6 +45,10 @@ struct GemmParams {
   int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
   unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
+  // Device-side schedule (row compaction): when set, token-dependent sizes are read from *dplan at kernel start
+  const DevPlan* dplan;
+  int m_from_plan;  // tiles_m (and for EPI_LSE the split schedule and partial stride) come from dplan
+  int k_from_plan;  // k_blocks = dplan->k_blocks_tok (the K loop runs over compacted token rows)
   // ---- EPI_LSE / EPI_GRAD
   const int64_t* labels;
   long long ignore_index;
@@ -66,8 +71,32 @@ struct TileItem {
   int m, n0, ncount;
 };
 
+struct Sched {
+  int tiles_m, tiles_n, group_m, k_blocks, vtiles_per_split, vtiles_total, part_stride;
+};
+
 template <int EPI>
-__device__ __forceinline__ TileItem decode_item(const GemmParams& p, int item) {
+__device__ __forceinline__ Sched make_sched(const GemmParams& p) {
+  Sched s;
+  s.tiles_m = p.tiles_m, s.tiles_n = p.tiles_n, s.group_m = p.group_m, s.k_blocks = p.k_blocks;
+  s.vtiles_per_split = p.vtiles_per_split, s.vtiles_total = p.vtiles_total, s.part_stride = p.part_stride;
+  if (p.dplan != nullptr) {
+    if (p.m_from_plan) {
+      s.tiles_m = p.dplan->tiles_m;
+      if constexpr (EPI == EPI_LSE) {
+        s.tiles_n = p.dplan->splits;
+        s.vtiles_per_split = p.dplan->vtiles_per_split;
+        s.part_stride = p.dplan->part_stride;
+        s.group_m = max(s.tiles_m, 1);
+      }
+    }
+    if (p.k_from_plan) s.k_blocks = p.dplan->k_blocks_tok;
+  }
+  return s;
+}
+
+template <int EPI>
+__device__ __forceinline__ TileItem decode_item(const Sched& p, int item) {
   const int per_group = p.group_m * p.tiles_n;
   const int g = item / per_group;
   const int r = item - g * per_group;
@@ -111,7 +140,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int total_items = p.tiles_m * p.tiles_n;
+  const Sched sc = make_sched<EPI>(p);
+  const int total_items = sc.tiles_m * sc.tiles_n;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -143,10 +173,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int stage = 0;
       uint32_t phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-        const TileItem it = decode_item<EPI>(p, item);
+        const TileItem it = decode_item<EPI>(sc, item);
         for (int t = 0; t < it.ncount; ++t) {
           const int nt = it.n0 + t;
-          for (int kb = 0; kb < p.k_blocks; ++kb) {
+          for (int kb = 0; kb < sc.k_blocks; ++kb) {
             mbar_wait(empty_bar(stage), phase ^ 1u);
             const uint32_t fb = full_bar(stage);
             mbar_expect_tx(fb, STAGE_BYTES);
@@ -187,12 +217,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-        const TileItem it = decode_item<EPI>(p, item);
+        const TileItem it = decode_item<EPI>(sc, item);
         for (int t = 0; t < it.ncount; ++t) {
           mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * BN;
-          for (int kb = 0; kb < p.k_blocks; ++kb) {
+          for (int kb = 0; kb < sc.k_blocks; ++kb) {
             mbar_wait(full_bar(stage), phase);
             tc_fence_after();
             const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
@@ -228,6 +258,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     (void)issuer;
     (void)chunk_ctr;
 
+    const bool zero_acc = (sc.k_blocks == 0);  // empty contraction (no valid rows): the result is exactly zero
+    (void)zero_acc;
     float gscale = 0.f;
     if constexpr (EPI == EPI_GRAD) {
       const long long nv = *p.n_valid;
@@ -235,7 +267,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     }
 
     for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
-      const TileItem it = decode_item<EPI>(p, item);
+      const TileItem it = decode_item<EPI>(sc, item);
       const int row = it.m * BM + row_in_tile;  // global row of this thread
 
       // per-item row state
@@ -351,6 +383,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             for (int h = 0; h < 2; ++h) {
               float v[32];
               tmem_ld32(taddr + c * 64 + h * 32, v);
+              if (zero_acc) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] = 0.f;
+              }
 #pragma unroll
               for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
             }
@@ -385,7 +421,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               float v[32];
               tmem_ld32(taddr + c * 32, v);
 #pragma unroll
-              for (int j = 0; j < 32; ++j) w[j] = __float_as_uint(v[j]);
+              for (int j = 0; j < 32; ++j) w[j] = zero_acc ? 0u : __float_as_uint(v[j]);
             }
             if (c == BN / 32 - 1) {
               tc_fence_before();
@@ -419,8 +455,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 
       if constexpr (EPI == EPI_LSE) {
         // item.n0 / vtiles_per_split is the split index
-        const int split = it.n0 / p.vtiles_per_split;
-        const size_t o = static_cast<size_t>(split) * p.part_stride + row;
+        const int split = it.n0 / sc.vtiles_per_split;
+        const size_t o = static_cast<size_t>(split) * sc.part_stride + row;
         p.part_m[o] = m_run;
         p.part_l[o] = l_run;
         p.part_z[o] = z_lab;
