@@ -41,6 +41,8 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="c5", help="SURVEY.md §8d configuration (c1..c5)")
+    ap.add_argument("--mode", default=None, choices=["single_pass", "recompute"],
+                    help="gradient mode of the fused loss (default: the library default, single_pass)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -211,7 +213,8 @@ def run_ours(args):
         dist.all_reduce(nv)
     n_valid_global = int(nv.item())
 
-    path = PathStep(W, process_group=pg)
+    path = PathStep(W, process_group=pg, mode=args.mode)
+    mode = path.loss_fn.mode
 
     def step():
         path.zero_grad(set_to_none=True)  # ssi/trainer.py:410
@@ -292,7 +295,8 @@ def run_ours(args):
     alg = {"lse_fwd": 2.0 * n_valid_local * V * D, "dlogits": 0.0, "dW": 2.0 * n_valid_local * V * D,
            "dX": 2.0 * n_valid_local * V * D}
     n_local = Bl * cfg.seq
-    executed = {k: 2.0 * n_local * V * D for k in ("lse_fwd", "dlogits", "dW", "dX")}
+    # executed flop: compacted rows are padded to 128-row tiles; recompute mode runs the logits contraction twice
+    executed = {k: 2.0 * n_valid_local * V * D for k in ("lse_fwd", "dlogits", "dW", "dX")}
     kern = {}
     for k, (ms, cnt) in classes.items():
         per_step = ms / args.steps
@@ -324,7 +328,7 @@ def run_ours(args):
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(cfg), "rows_per_rank": n_local, "valid_rows_global": n_valid_global,
-                   "parallelism": f"dp{world}", "l2": "inputs (X, W, dlogits blocks) are several times larger than "
+                   "parallelism": f"dp{world}", "mode": mode, "l2": "inputs (X, W, dlogits blocks) are several times larger than "
                    "the 126 MB L2, no explicit flush", "loss_batch_rank0": loss_batch},
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
         "step_algorithmic_tflops_per_gpu": step_tflops,

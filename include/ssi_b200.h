@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 100
+#define SSI_B200_ABI_VERSION 101
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -45,6 +45,11 @@ const char* ssi_b200_last_error(void);
 /* Number of tcgen05 / helper kernels launched by this process through the library so far
  * (used by bench.py for its gpu_launches claim). */
 int64_t ssi_b200_launch_count(void);
+
+/* Tuning knobs (also read once from the environment as SSI_B200_<NAME>): "g_cap_mib" = size cap of the bf16
+ * logits/dlogits block scratch in MiB (default 4096), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx",
+ * "store_hint". Workspace sizes depend on g_cap_mib: query them again after changing it. */
+int ssi_b200_set_option(const char* name, int64_t value);
 
 /* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. Workspaces must be 256-byte
  * aligned. */
@@ -86,6 +91,35 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
                            void* stream);
 
 /*
+ * Single-pass mode (the default for training): forward ALSO forms the gradients, one bounded ROW chunk at a
+ * time, so each logits tile is computed once (6 N V D flop executed instead of the 8 N V D of fwd + recompute
+ * bwd).  Per chunk: the logits tiles are rounded to bf16 -- exactly the dtype the reference's logits have
+ * (tied_linear.py:25) -- and stored into one reused block S [rows_cap, Vpad] inside `ws` (never the full
+ * [N, V] matrix); the log-sum-exp runs on those rounded values (ce_chunked_output_loss.py:41); S is rewritten
+ * in place into dlogits = (softmax - onehot) * grad_hint / n_valid_total (bf16, like autograd's); then
+ *   dW_acc (+)= dlogits^T * X_chunk   fp32 [V, D], summed over ALL tokens before any rounding
+ *   dX_chunk  = dlogits * W           bf16
+ *   grad_hint     [1] fp32 device scalar: the upstream gradient the caller expects backward to receive
+ *                     (ssi/trainer.py:393: num_tokens_iter); any value works, see apply_grad
+ *   n_valid_total [1] int64 device scalar or NULL (= use this call's own n_valid)
+ *   lse/loss_out/n_valid  as ssi_b200_lmhead_ce_fwd
+ *   dX     [N, D] bf16 out (zeros for ignored rows);  dW_acc [V, D] fp32 out (overwritten)
+ */
+int ssi_b200_single_pass_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* bytes);
+int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                float* dW_acc, void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * Backward of single-pass mode: ratio = grad_out / grad_hint (exactly 1 when the hint was right);
+ *   dX *= ratio in place (skipped on the device when ratio == 1; dX may be NULL)
+ *   dW  = bf16((accumulate_dW ? dW : 0) + ratio * dW_acc)     -- one rounding of the whole-batch fp32 sum
+ */
+int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
+                                  int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW, void* stream);
+
+/*
  * Tied-embedding gradient: dW[ids[i], :] += dH[i, :] for i in [0, N), ids in [0, V) (ids < 0 or >= V are
  * skipped).  Rows are grouped by a stable radix sort of the ids and reduced in fp32 by a warp-level
  * segmented reduction in sorted order (deterministic: no floating-point atomics), one read-modify-write
@@ -107,7 +141,8 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
  * profile_end every launch made through this library is bracketed by CUDA events on its own stream.
  * profile_end waits for those events and fills ms_by_class[8] / launches_by_class[8] (either may be NULL):
  *   0 = K1 logits + online-LSE (fwd), 1 = K2a dlogits recompute, 2 = K2b dW contraction, 3 = K2c dX contraction,
- *   4 = K3 embedding scatter (sort + segmented reduce, one entry per call), 5 = small helper kernels, 6-7 unused.
+ *   4 = K3 embedding scatter (sort + segmented reduce, one entry per call), 5 = small helper kernels,
+ *   6 = single-pass softmax-grad pass (S -> dlogits in place, HBM-bound), 7 unused.
  * This pair is the only part of the ABI that synchronises (profile_end) or allocates (events, lazily).
  */
 int ssi_b200_profile_begin(void);

@@ -23,7 +23,8 @@ thread_local char g_err[512] = "";
 std::atomic<long long> g_launches{0};
 
 // ---- optional per-kernel-class timing with CUDA events on the launching stream (bench.py's roofline leg)
-enum ProfCat { CAT_LSE = 0, CAT_DLOGITS = 1, CAT_DW = 2, CAT_DX = 3, CAT_SCATTER = 4, CAT_AUX = 5, CAT_COUNT = 8 };
+enum ProfCat { CAT_LSE = 0, CAT_DLOGITS = 1, CAT_DW = 2, CAT_DX = 3, CAT_SCATTER = 4, CAT_AUX = 5, CAT_SOFTMAX = 6,
+               CAT_COUNT = 8 };
 struct ProfRec {
   int cat;
   cudaEvent_t a, b;
@@ -185,7 +186,7 @@ struct CompactWs {  // shared head of the forward and backward workspaces
 };
 CompactWs plan_compact(int64_t N, int64_t n_pad, int64_t D, size_t o) {
   CompactWs c;
-  c.off_plan = o, o += 256;
+  c.off_plan = o, o += ssi::PLAN_AREA_BYTES;
   c.off_pos = o, o += align_up(static_cast<size_t>(N) * sizeof(int), 256);
   c.off_idx = o, o += align_up(static_cast<size_t>(n_pad) * sizeof(int), 256);
   c.off_labels_c = o, o += align_up(static_cast<size_t>(n_pad) * sizeof(int64_t), 256);
@@ -228,7 +229,7 @@ struct Tune {
   int group_m_grad = 16, group_m_dw = 16, group_m_dx = 16;
   int store_hint = 0;  // 1 = evict-first L2 policy on the dlogits / dW / dX tile stores
 };
-const Tune& tune() {
+Tune& tune() {
   static Tune t = [] {
     Tune x;
     if (const char* e = getenv("SSI_B200_G_CAP_MIB")) x.g_cap_elems = atoll(e) * (int64_t(1) << 19);
@@ -286,6 +287,48 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   return b;
 }
 
+// Single-pass ("stash") mode: forward also forms the gradients, one ROW chunk at a time, so the logits are
+// computed once (6 N V D executed instead of 8 N V D).  Scratch: one bf16 block S/G [rows_cap, Vpad].
+struct SpPlan {
+  int64_t n_pad, vpad;
+  int tiles_m, vtiles_total, combine_blocks, t_max, chunks_max;
+  CompactWs cw;
+  size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_dxc, off_s, bytes;
+};
+
+int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
+  SpPlan f;
+  f.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
+  f.tiles_m = static_cast<int>(f.n_pad / ssi::BM);
+  f.vtiles_total = static_cast<int>(ceil_div(V, ssi::BN));
+  f.vpad = static_cast<int64_t>(f.vtiles_total) * ssi::BN;
+  f.combine_blocks = static_cast<int>(ceil_div(N, ssi::COMBINE_THREADS));
+  int64_t t_max = tune().g_cap_elems / f.vpad / ssi::BM;
+  if (t_max < 1) t_max = 1;
+  if (t_max > f.tiles_m) t_max = f.tiles_m;
+  f.t_max = static_cast<int>(t_max);
+  f.chunks_max = static_cast<int>(ceil_div(f.tiles_m, t_max)) + (t_max < f.tiles_m ? 1 : 0);
+  if (f.chunks_max > ssi::MAX_ROW_CHUNKS)
+    return fail(-1, "single-pass mode needs %d row chunks (> %d): raise SSI_B200_G_CAP_MIB", f.chunks_max,
+                ssi::MAX_ROW_CHUNKS);
+  f.cw = plan_compact(N, f.n_pad, D, 0);
+  size_t o = f.cw.end;
+  const size_t items = f.t_max > ssi::MAX_LSE_ITEMS ? f.t_max : ssi::MAX_LSE_ITEMS;
+  const size_t part = align_up(items * ssi::BM * sizeof(float), 256);
+  f.off_m = o, o += part;
+  f.off_l = o, o += part;
+  f.off_z = o, o += part;
+  f.off_lse_c = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
+  f.off_loss_c = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
+  f.off_bl = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(float), 256);
+  f.off_bc = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(int), 256);
+  f.off_dxc = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
+  f.off_s = o, o += align_up(static_cast<size_t>(f.t_max) * ssi::BM * f.vpad * 2, 1024);
+  f.bytes = o;
+  *out = f;
+  return 0;
+}
+
 struct ScatPlan {
   int blocks, nwarps, passes;
   size_t off_k0, off_v0, off_k1, off_v1, off_hist, off_partial, off_info, bytes;
@@ -328,6 +371,21 @@ extern "C" {
 int ssi_b200_version(void) { return SSI_B200_ABI_VERSION; }
 
 const char* ssi_b200_last_error(void) { return g_err; }
+
+int ssi_b200_set_option(const char* name, int64_t value) {
+  SSI_CHECK_ARG(name, "null option name");
+  Tune& t = tune();
+  if (!strcmp(name, "g_cap_mib")) {
+    SSI_CHECK_ARG(value >= 1, "g_cap_mib must be >= 1");
+    t.g_cap_elems = value * (int64_t(1) << 19);
+  } else if (!strcmp(name, "g_tiles")) t.g_tiles = value;
+  else if (!strcmp(name, "group_m_grad")) t.group_m_grad = static_cast<int>(value);
+  else if (!strcmp(name, "group_m_dw")) t.group_m_dw = static_cast<int>(value);
+  else if (!strcmp(name, "group_m_dx")) t.group_m_dx = static_cast<int>(value);
+  else if (!strcmp(name, "store_hint")) t.store_hint = static_cast<int>(value);
+  else return fail(-1, "unknown option '%s'", name);
+  return 0;
+}
 
 int64_t ssi_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
@@ -512,6 +570,168 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
                                                          reinterpret_cast<uint2*>(dX));
     SSI_LAUNCH_OK("dx_finalize");
   }
+  return 0;
+}
+
+int ssi_b200_single_pass_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* bytes) {
+  SSI_CHECK_ARG(bytes, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64 && D % 64 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
+                (long long)V, (long long)D);
+  SpPlan f;
+  if (int r = plan_single_pass(N, V, D, &f)) return r;
+  *bytes = f.bytes;
+  return 0;
+}
+
+int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
+  if (int r = check_common(X, W, N, V, D)) return r;
+  SSI_CHECK_ARG(labels && grad_hint && lse && loss_out && n_valid && dX && dW_acc && ws, "null pointer argument");
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0,
+                "dX / dW_acc must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  SpPlan f;
+  if (int r = plan_single_pass(N, V, D, &f)) return r;
+  SSI_CHECK_ARG(ws_bytes >= f.bytes, "single-pass workspace too small: %zu < %zu", ws_bytes, f.bytes);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 255) == 0, "workspace must be 256-byte aligned");
+  char* wsb = static_cast<char*>(ws);
+  ssi::DevPlan* dplan = reinterpret_cast<ssi::DevPlan*>(wsb + f.cw.off_plan);
+  int* pos = reinterpret_cast<int*>(wsb + f.cw.off_pos);
+  int* idx = reinterpret_cast<int*>(wsb + f.cw.off_idx);
+  int64_t* labels_c = reinterpret_cast<int64_t*>(wsb + f.cw.off_labels_c);
+  void* Xc = wsb + f.cw.off_xc;
+  float* part_m = reinterpret_cast<float*>(wsb + f.off_m);
+  float* part_l = reinterpret_cast<float*>(wsb + f.off_l);
+  float* part_z = reinterpret_cast<float*>(wsb + f.off_z);
+  float* lse_c = reinterpret_cast<float*>(wsb + f.off_lse_c);
+  float* loss_c = reinterpret_cast<float*>(wsb + f.off_loss_c);
+  float* blk_loss = reinterpret_cast<float*>(wsb + f.off_bl);
+  int* blk_cnt = reinterpret_cast<int*>(wsb + f.off_bc);
+  void* dXc = wsb + f.off_dxc;
+  void* S = wsb + f.off_s;
+  const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
+  const int64_t rows_cap = static_cast<int64_t>(f.t_max) * ssi::BM;
+  const int64_t* nvt = n_valid_total ? n_valid_total : n_valid;
+
+  {
+    ProfScope ps(CAT_AUX, st);
+    ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(f.n_pad),
+                                                  ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms,
+                                                  f.t_max, f.chunks_max, d_tiles, n_valid);
+    SSI_LAUNCH_OK("compact_scan");
+    ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
+                                                         static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
+                                                         nullptr);
+    SSI_LAUNCH_OK("gather_rows");
+  }
+
+  CUtensorMap tmX_k, tmX_mn, tmW_k, tmW_mn, tmS_k, tmS_mn, tmdW, tmdXc;
+  if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
+  if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  if (int r = make_tmap(&tmW_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, 64)) return r;
+  if (int r = make_tmap(&tmS_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, S, f.vpad, rows_cap, f.vpad * 2, 64, ssi::BM))
+    return r;
+  if (int r = make_tmap(&tmS_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, S, f.vpad, rows_cap, f.vpad * 2, 64, 64))
+    return r;
+  if (int r = make_tmap(&tmdW, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dW_acc, D, V, D * 4, 32, ssi::BM)) return r;
+  if (int r = make_tmap(&tmdXc, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dXc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
+
+  for (int ch = 0; ch < f.chunks_max; ++ch) {
+    const ssi::DevPlan* cplan = dplan + 1 + ch;
+    // ---- K1: logits tiles of the chunk -> bf16 block S + online log-sum-exp partials
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmX_k, p.tmB = tmW_k, p.tmC = tmS_k;
+      p.dplan = cplan, p.m_from_plan = 1, p.plan_rows = ssi::PR_A_ROWS | ssi::PR_LABEL_ROWS;
+      p.tiles_m = f.t_max, p.tiles_n = 1, p.k_blocks = static_cast<int>(D / ssi::BK);
+      p.group_m = f.t_max;
+      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
+      p.labels = labels_c, p.ignore_index = ignore_index;
+      p.n_rows = static_cast<int>(f.n_pad), p.vocab = static_cast<int>(V), p.col0 = 0;
+      p.vtiles_per_split = f.vtiles_total, p.vtiles_total = f.vtiles_total;
+      p.part_m = part_m, p.part_l = part_l, p.part_z = part_z;
+      p.part_stride = static_cast<int>(rows_cap);
+      if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
+        return r;
+    }
+    {
+      ProfScope ps(CAT_AUX, st);
+      ssi::chunk_combine_kernel<<<64, 256, 0, st>>>(part_m, part_l, part_z, cplan, lse_c, loss_c);
+      SSI_LAUNCH_OK("chunk_combine");
+    }
+    // ---- S -> G in place (softmax - onehot) * grad_hint / n_valid_total
+    {
+      ProfScope ps(CAT_SOFTMAX, st);
+      ssi::softmax_grad_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(S), static_cast<int>(f.vpad / 8),
+                                                            cplan, lse_c, labels_c, static_cast<int>(V), grad_hint,
+                                                            nvt);
+      SSI_LAUNCH_OK("softmax_grad");
+    }
+    // ---- dW_acc (+)= G^T X_c[chunk]   (M = vocabulary rows, N = D, K = the chunk's token rows)
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmS_mn, p.tmB = tmX_mn, p.tmC = tmdW;
+      p.dplan = cplan, p.k_from_plan = 1, p.plan_rows = ssi::PR_B_K;
+      p.tiles_m = static_cast<int>(ceil_div(V, ssi::BM));
+      p.tiles_n = d_tiles;
+      p.k_blocks = static_cast<int>(rows_cap / ssi::BK);
+      p.group_m = tune().group_m_dw;
+      p.c_reduce = (ch > 0) ? 1 : 0;
+      if (int r = launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
+    }
+    // ---- dXc[chunk] = G W   (M = the chunk's token rows, N = D, K = padded vocabulary)
+    {
+      ssi::GemmParams p;
+      memset(&p, 0, sizeof(p));
+      p.tmA = tmS_k, p.tmB = tmW_mn, p.tmC = tmdXc;
+      p.dplan = cplan, p.m_from_plan = 1, p.plan_rows = ssi::PR_C_ROWS;
+      p.tiles_m = f.t_max, p.tiles_n = d_tiles;
+      p.k_blocks = f.vtiles_total * (ssi::BN / ssi::BK);
+      p.group_m = tune().group_m_dx;
+      if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
+    }
+  }
+  ProfScope ps_aux(CAT_AUX, st);
+  ssi::stash_finish_kernel<<<f.combine_blocks, ssi::COMBINE_THREADS, 0, st>>>(lse_c, loss_c, pos,
+                                                                              static_cast<int>(N), lse, blk_loss,
+                                                                              blk_cnt);
+  SSI_LAUNCH_OK("stash_finish");
+  ssi::loss_finalize_kernel<<<1, 256, 0, st>>>(blk_loss, blk_cnt, f.combine_blocks, loss_out, n_valid);
+  SSI_LAUNCH_OK("loss_finalize");
+  ssi::dx_scatter_bf16_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(dXc), pos, static_cast<int>(N),
+                                                           static_cast<int>(D / 8), static_cast<uint4*>(dX));
+  SSI_LAUNCH_OK("dx_scatter");
+  return 0;
+}
+
+int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
+                                  int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW, void* stream) {
+  SSI_CHECK_ARG(dW_acc && grad_out && grad_hint && dW, "null pointer argument");
+  SSI_CHECK_ARG(N >= 0 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
+                (long long)V, (long long)D);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0 &&
+                    (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
+                "dX / dW_acc / dW must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_AUX, st);
+  if (dX && N > 0) {
+    ssi::apply_dx_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(dX), static_cast<size_t>(N) * D / 8,
+                                                      grad_out, grad_hint);
+    SSI_LAUNCH_OK("apply_dx");
+  }
+  ssi::apply_dw_kernel<<<di->sms * 16, 256, 0, st>>>(reinterpret_cast<const float4*>(dW_acc),
+                                                     static_cast<size_t>(V) * D / 4, grad_out, grad_hint,
+                                                     accumulate_dW ? 1 : 0, static_cast<uint2*>(dW));
+  SSI_LAUNCH_OK("apply_dw");
   return 0;
 }
 

@@ -23,17 +23,49 @@ struct DevPlan {
   int vtiles_per_split;  // K1: 256-column tiles per split
   int k_blocks_tok;      // K2b: K loop over tokens = tiles_m * 2 (64-row blocks)
   int part_stride;       // K1 partial arrays: floats per split = tiles_m * 128
-  int pad0, pad1;
+  int row0;              // first compact row of this plan (0 for the whole-problem plan; chunk plans: chunk start)
+  int pad1;
 };
+constexpr int MAX_ROW_CHUNKS = 120;  // plan area = (1 + MAX_ROW_CHUNKS) DevPlans (single-pass mode)
+constexpr int PLAN_AREA_BYTES = 4096;
 constexpr int MAX_LSE_ITEMS = 8192;  // cap on tiles_m * splits (bounds the partial arrays)
+
+// K1 split count: smallest s whose static-schedule makespan (waves x tiles per split) is within 1% of the best
+__device__ inline void choose_splits(int tiles_m, int vtiles_total, int sms, int& splits, int& per_split) {
+  int best_s = 1;
+  if (tiles_m > 0) {
+    const int max_s = min(vtiles_total, 148);
+    long long best = -1;
+    for (int pass = 0; pass < 2; ++pass) {
+      for (int s2 = 1; s2 <= max_s; ++s2) {
+        if (s2 > 1 && static_cast<long long>(s2) * tiles_m > MAX_LSE_ITEMS) break;
+        const int pr = (vtiles_total + s2 - 1) / s2;
+        if ((vtiles_total + pr - 1) / pr != s2) continue;
+        const long long items = static_cast<long long>(tiles_m) * s2;
+        const long long c = ((items + sms - 1) / sms) * pr;
+        if (pass == 0) {
+          if (best < 0 || c < best) best = c;
+        } else if (c * 100 <= best * 101) {
+          best_s = s2;
+          break;
+        }
+      }
+    }
+  }
+  splits = best_s;
+  per_split = (vtiles_total + best_s - 1) / best_s;
+}
 
 // One block: stable compaction of the valid rows. pos[r] = compact position or -1, idx[c] = original row,
 // labels_c[c] = label (ignore_index beyond n_valid up to n_pad), then the device-side plan.
 __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __restrict__ labels, int n, int n_pad,
                                                             long long ignore_index, int* __restrict__ pos,
                                                             int* __restrict__ idx, int64_t* __restrict__ labels_c,
-                                                            DevPlan* __restrict__ plan, int vtiles_total, int sms) {
+                                                            DevPlan* __restrict__ plan, int vtiles_total, int sms,
+                                                            int chunk_t_max = 0, int chunks_max = 0,
+                                                            int d_tiles = 0, int64_t* n_valid_out = nullptr) {
   __shared__ int s_sum[1024];
+  __shared__ int s_chunk_t;
   const int per = (n + 1023) / 1024;
   const int b = threadIdx.x * per;
   const int e = min(b + per, n);
@@ -68,31 +100,42 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
     d.tiles_m = (n_valid + 127) / 128;
     d.k_blocks_tok = d.tiles_m * 2;
     d.part_stride = d.tiles_m * 128;
-    // K1 split count: smallest s whose static-schedule makespan is within 1% of the best
-    int best_s = 1;
-    if (d.tiles_m > 0) {
-      const int max_s = min(vtiles_total, 148);
-      long long best = -1;
-      for (int pass = 0; pass < 2; ++pass) {
-        for (int s2 = 1; s2 <= max_s; ++s2) {
-          if (s2 > 1 && static_cast<long long>(s2) * d.tiles_m > MAX_LSE_ITEMS) break;
-          const int pr = (vtiles_total + s2 - 1) / s2;
-          if ((vtiles_total + pr - 1) / pr != s2) continue;
-          const long long items = static_cast<long long>(d.tiles_m) * s2;
-          const long long c = ((items + sms - 1) / sms) * pr;
-          if (pass == 0) {
-            if (best < 0 || c < best) best = c;
-          } else if (c * 100 <= best * 101) {
-            best_s = s2;
-            break;
-          }
-        }
+    choose_splits(d.tiles_m, vtiles_total, sms, d.splits, d.vtiles_per_split);
+    d.row0 = d.pad1 = 0;
+    *plan = d;
+    if (n_valid_out) *n_valid_out = n_valid;
+    // Single-pass mode: m-tiles per row chunk.  The dX contraction of a chunk has t * d_tiles output tiles on
+    // `sms` persistent CTAs, so t is chosen to waste the fewest waves; a per-chunk charge prefers fewer chunks.
+    int best_t = max(chunk_t_max, 1);
+    if (chunks_max > 0 && d.tiles_m > 0) {
+      float best_cost = -1.f;
+      for (int t = 1; t <= chunk_t_max; ++t) {
+        const int full = d.tiles_m / t, rem = d.tiles_m % t;
+        const int nch = full + (rem ? 1 : 0);
+        if (nch > chunks_max) continue;
+        float cost = static_cast<float>(full) * ((t * d_tiles + sms - 1) / sms) + 0.3f * nch;
+        if (rem) cost += (rem * d_tiles + sms - 1) / sms;
+        if (best_cost < 0.f || cost <= best_cost) best_cost = cost, best_t = t;
       }
     }
-    d.splits = best_s;
-    d.vtiles_per_split = (vtiles_total + best_s - 1) / best_s;
-    d.pad0 = d.pad1 = 0;
-    *plan = d;
+    s_chunk_t = best_t;
+  }
+  if (chunks_max > 0) {
+    __syncthreads();
+    const int t = s_chunk_t;
+    const int tiles_all = (n_valid + 127) / 128;
+    for (int c = threadIdx.x; c < chunks_max; c += 1024) {
+      DevPlan d;
+      const int m0 = min(c * t, tiles_all);
+      d.tiles_m = min(t, tiles_all - m0);
+      d.row0 = m0 * 128;
+      d.n_valid = max(0, min(n_valid - d.row0, d.tiles_m * 128));
+      d.k_blocks_tok = d.tiles_m * 2;
+      d.part_stride = d.tiles_m * 128;
+      choose_splits(d.tiles_m, vtiles_total, sms, d.splits, d.vtiles_per_split);
+      d.pad1 = 0;
+      plan[1 + c] = d;
+    }
   }
 }
 
@@ -221,6 +264,202 @@ __global__ void __launch_bounds__(256) loss_finalize_kernel(const float* __restr
     // 0/0 -> NaN exactly like total_loss / total_elements in ce_chunked_output_loss.py:83
     loss_out[1] = static_cast<float>(sum) / static_cast<float>(n);
     n_valid[0] = n;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Single-pass ("stash") mode helpers.  Per row chunk: K1 stores the bf16 logits tile block S and the split
+// partials; chunk_combine_kernel folds the partials into lse_c / loss_c for the chunk's compact rows;
+// softmax_grad_kernel rewrites S in place into dlogits G (HBM-bound, 2 B read + 2 B written per logit).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) chunk_combine_kernel(const float* __restrict__ part_m,
+                                                            const float* __restrict__ part_l,
+                                                            const float* __restrict__ part_z,
+                                                            const DevPlan* __restrict__ plan,
+                                                            float* __restrict__ lse_c, float* __restrict__ loss_c) {
+  const int rows = plan->tiles_m * 128, nv = plan->n_valid, row0 = plan->row0;
+  const int splits = plan->splits, part_stride = plan->part_stride;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+    float l = 0.f, loss = 0.f;
+    if (r < nv) {
+      float M = -INFINITY;
+      for (int s = 0; s < splits; ++s) M = fmaxf(M, part_m[static_cast<size_t>(s) * part_stride + r]);
+      float L = 0.f, z = -INFINITY;
+      for (int s = 0; s < splits; ++s) {
+        const size_t o = static_cast<size_t>(s) * part_stride + r;
+        L += part_l[o] * exp2f(part_m[o] - M);
+        z = fmaxf(z, part_z[o]);
+      }
+      l = (M + log2f(L)) * 0.6931471805599453f;
+      loss = l - z;
+    }
+    lse_c[row0 + r] = l;
+    loss_c[row0 + r] = loss;
+  }
+}
+
+__device__ __forceinline__ float bf16lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+// G[r, v] = (exp(S[r, v] - lse[r]) - [v == label[r]]) * grad_hint / n_valid_total, bf16, in place; padding
+// columns (v >= V) and padding rows (r >= n_valid of the chunk) become exact zeros.  One block per row at a
+// time, 16-byte accesses, 4 loads in flight per thread.
+__global__ void __launch_bounds__(256) softmax_grad_kernel(uint4* __restrict__ S, int row_u4,
+                                                           const DevPlan* __restrict__ plan,
+                                                           const float* __restrict__ lse_c,
+                                                           const int64_t* __restrict__ labels_c, int V,
+                                                           const float* __restrict__ grad_hint,
+                                                           const int64_t* __restrict__ n_valid_total) {
+  const int rows = plan->tiles_m * 128, nv = plan->n_valid, row0 = plan->row0;
+  const long long nvt = *n_valid_total;
+  const float gscale = (nvt > 0) ? (*grad_hint / static_cast<float>(nvt)) : 0.f;
+  constexpr float kLog2e = 1.4426950408889634f;
+  for (int r = blockIdx.x; r < rows; r += gridDim.x) {
+    uint4* row = S + static_cast<size_t>(r) * row_u4;
+    if (r >= nv) {
+      for (int j = threadIdx.x; j < row_u4; j += 256) row[j] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const float lse2 = lse_c[row0 + r] * kLog2e;
+    const int label = static_cast<int>(labels_c[row0 + r]);
+    for (int j0 = threadIdx.x; j0 < row_u4; j0 += 4 * 256) {
+      uint4 u[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int j = j0 + k * 256;
+        if (j < row_u4) u[k] = row[j];
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int j = j0 + k * 256;
+        if (j >= row_u4) continue;
+        const int c0 = j * 8;
+        uint32_t w[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
+        float g[8];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          g[2 * e] = fast_exp2(fmaf(bf16lo(w[e]), kLog2e, -lse2)) * gscale;
+          g[2 * e + 1] = fast_exp2(fmaf(bf16hi(w[e]), kLog2e, -lse2)) * gscale;
+        }
+        if (label >= c0 && label < c0 + 8) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (c0 + e == label) g[e] -= gscale;
+        }
+        if (c0 + 8 > V) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (c0 + e >= V) g[e] = 0.f;
+        }
+        uint4 o;
+        o.x = pack_bf16x2(g[0], g[1]);
+        o.y = pack_bf16x2(g[2], g[3]);
+        o.z = pack_bf16x2(g[4], g[5]);
+        o.w = pack_bf16x2(g[6], g[7]);
+        row[j] = o;
+      }
+    }
+  }
+}
+
+// lse[row] / per-block loss partials over ORIGINAL rows from the compact lse_c / loss_c (fixed order).
+__global__ void __launch_bounds__(COMBINE_THREADS) stash_finish_kernel(const float* __restrict__ lse_c,
+                                                                       const float* __restrict__ loss_c,
+                                                                       const int* __restrict__ pos, int n_rows,
+                                                                       float* __restrict__ lse,
+                                                                       float* __restrict__ blk_loss,
+                                                                       int* __restrict__ blk_cnt) {
+  __shared__ float s_loss[COMBINE_THREADS];
+  __shared__ int s_cnt[COMBINE_THREADS];
+  const int row = blockIdx.x * COMBINE_THREADS + threadIdx.x;
+  float loss = 0.f;
+  int cnt = 0;
+  if (row < n_rows) {
+    const int c = pos[row];
+    float l = 0.f;
+    if (c >= 0) {
+      l = lse_c[c];
+      loss = loss_c[c];
+      cnt = 1;
+    }
+    lse[row] = l;
+  }
+  s_loss[threadIdx.x] = loss;
+  s_cnt[threadIdx.x] = cnt;
+  __syncthreads();
+  for (int off = COMBINE_THREADS / 2; off > 0; off >>= 1) {
+    if (threadIdx.x < off) {
+      s_loss[threadIdx.x] += s_loss[threadIdx.x + off];
+      s_cnt[threadIdx.x] += s_cnt[threadIdx.x + off];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    blk_loss[blockIdx.x] = s_loss[0];
+    blk_cnt[blockIdx.x] = s_cnt[0];
+  }
+}
+
+// dX[r, :] = dXc[pos[r], :] for valid rows, zeros for ignored rows (bf16 rows, 16-byte accesses).
+__global__ void __launch_bounds__(256) dx_scatter_bf16_kernel(const uint4* __restrict__ dXc,
+                                                              const int* __restrict__ pos, int n, int row_u4,
+                                                              uint4* __restrict__ dX) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n; r += warps) {
+    const int c = pos[r];
+    uint4* dst = dX + static_cast<size_t>(r) * row_u4;
+    if (c >= 0) {
+      const uint4* src = dXc + static_cast<size_t>(c) * row_u4;
+      for (int j = lane; j < row_u4; j += 32) dst[j] = src[j];
+    } else {
+      for (int j = lane; j < row_u4; j += 32) dst[j] = make_uint4(0, 0, 0, 0);
+    }
+  }
+}
+
+// Backward of single-pass mode: the gradients were formed in forward for an upstream gradient `grad_hint`;
+// ratio = grad_out / grad_hint rescales them (exactly 1 when the caller announced the right hint).
+__device__ __forceinline__ float grad_ratio(const float* grad_out, const float* grad_hint) {
+  const float g = *grad_out, h = *grad_hint;
+  return (g == h) ? 1.f : g / h;
+}
+
+__global__ void __launch_bounds__(256) apply_dx_kernel(uint4* __restrict__ dX, size_t n_u4,
+                                                       const float* __restrict__ grad_out,
+                                                       const float* __restrict__ grad_hint) {
+  const float ratio = grad_ratio(grad_out, grad_hint);
+  if (ratio == 1.f) return;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_u4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const uint4 u = dX[i];
+    uint4 o;
+    o.x = pack_bf16x2(bf16lo(u.x) * ratio, bf16hi(u.x) * ratio);
+    o.y = pack_bf16x2(bf16lo(u.y) * ratio, bf16hi(u.y) * ratio);
+    o.z = pack_bf16x2(bf16lo(u.z) * ratio, bf16hi(u.z) * ratio);
+    o.w = pack_bf16x2(bf16lo(u.w) * ratio, bf16hi(u.w) * ratio);
+    dX[i] = o;
+  }
+}
+
+// dW = bf16((accumulate ? dW : 0) + ratio * acc): the fp32 accumulator over ALL tokens is rounded once.
+__global__ void __launch_bounds__(256) apply_dw_kernel(const float4* __restrict__ acc, size_t n_f4,
+                                                       const float* __restrict__ grad_out,
+                                                       const float* __restrict__ grad_hint, int accumulate,
+                                                       uint2* __restrict__ dW) {
+  const float ratio = grad_ratio(grad_out, grad_hint);
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_f4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float4 a = acc[i];
+    a.x *= ratio, a.y *= ratio, a.z *= ratio, a.w *= ratio;
+    if (accumulate) {
+      const uint2 old = dW[i];
+      a.x += bf16lo(old.x), a.y += bf16hi(old.x), a.z += bf16lo(old.y), a.w += bf16hi(old.y);
+    }
+    uint2 o;
+    o.x = pack_bf16x2(a.x, a.y);
+    o.y = pack_bf16x2(a.z, a.w);
+    dW[i] = o;
   }
 }
 

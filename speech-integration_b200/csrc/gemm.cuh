@@ -35,7 +35,11 @@ constexpr int TMEM_COLS = 512;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
-enum Epi { EPI_LSE = 0, EPI_GRAD = 1, EPI_BF16 = 2, EPI_F32 = 3 };
+enum Epi { EPI_LSE = 0, EPI_GRAD = 1, EPI_BF16 = 2, EPI_F32 = 3, EPI_LSE_STASH = 4 };
+template <int EPI>
+__host__ __device__ constexpr bool is_lse_epi() { return EPI == EPI_LSE || EPI == EPI_LSE_STASH; }
+// GemmParams::plan_rows bits: add dplan->row0 (first compact row of a row chunk) to ...
+enum PlanRows { PR_A_ROWS = 1, PR_B_K = 2, PR_C_ROWS = 4, PR_LABEL_ROWS = 8 };
 
 struct GemmParams {
   CUtensorMap tmA;
@@ -49,6 +53,7 @@ struct GemmParams {
   const DevPlan* dplan;
   int m_from_plan;  // tiles_m (and for EPI_LSE the split schedule and partial stride) come from dplan
   int k_from_plan;  // k_blocks = dplan->k_blocks_tok (the K loop runs over compacted token rows)
+  int plan_rows;    // PlanRows bits (single-pass mode: the plan describes one row chunk)
   // ---- EPI_LSE / EPI_GRAD
   const int64_t* labels;
   long long ignore_index;
@@ -73,6 +78,7 @@ struct TileItem {
 
 struct Sched {
   int tiles_m, tiles_n, group_m, k_blocks, vtiles_per_split, vtiles_total, part_stride;
+  int a_row_off, b_k_off, c_row_off, label_off;
 };
 
 template <int EPI>
@@ -80,10 +86,16 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
   Sched s;
   s.tiles_m = p.tiles_m, s.tiles_n = p.tiles_n, s.group_m = p.group_m, s.k_blocks = p.k_blocks;
   s.vtiles_per_split = p.vtiles_per_split, s.vtiles_total = p.vtiles_total, s.part_stride = p.part_stride;
+  s.a_row_off = s.b_k_off = s.c_row_off = s.label_off = 0;
   if (p.dplan != nullptr) {
+    const int row0 = p.dplan->row0;
+    if (p.plan_rows & PR_A_ROWS) s.a_row_off = row0;
+    if (p.plan_rows & PR_B_K) s.b_k_off = row0;
+    if (p.plan_rows & PR_C_ROWS) s.c_row_off = row0;
+    if (p.plan_rows & PR_LABEL_ROWS) s.label_off = row0;
     if (p.m_from_plan) {
       s.tiles_m = p.dplan->tiles_m;
-      if constexpr (EPI == EPI_LSE) {
+      if constexpr (is_lse_epi<EPI>()) {
         s.tiles_n = p.dplan->splits;
         s.vtiles_per_split = p.dplan->vtiles_per_split;
         s.part_stride = p.dplan->part_stride;
@@ -92,6 +104,8 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
     }
     if (p.k_from_plan) s.k_blocks = p.dplan->k_blocks_tok;
   }
+  // accumulating an empty contraction (an empty row chunk) is a no-op
+  if (s.k_blocks == 0 && p.c_reduce) s.tiles_m = 0;
   return s;
 }
 
@@ -105,7 +119,7 @@ __device__ __forceinline__ TileItem decode_item(const Sched& p, int item) {
   TileItem it;
   it.m = m0 + r % gm;
   const int n = r / gm;
-  if constexpr (EPI == EPI_LSE) {
+  if constexpr (is_lse_epi<EPI>()) {
     it.n0 = n * p.vtiles_per_split;
     it.ncount = min(p.vtiles_per_split, p.vtiles_total - it.n0);
   } else {
@@ -146,7 +160,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
     tma_prefetch_desc(&p.tmB);
-    if constexpr (EPI == EPI_BF16 || EPI == EPI_F32 || EPI == EPI_GRAD) tma_prefetch_desc(&p.tmC);
+    if constexpr (EPI != EPI_LSE) tma_prefetch_desc(&p.tmC);
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
@@ -183,7 +197,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
             const uint32_t sB = sA + A_STAGE_BYTES;
             if constexpr (!A_MN) {
-              tma_load_2d(sA, &p.tmA, p.a_k0 + kb * BK, p.a_r0 + it.m * BM, fb);
+              tma_load_2d(sA, &p.tmA, p.a_k0 + kb * BK, p.a_r0 + sc.a_row_off + it.m * BM, fb);
             } else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j)
@@ -194,7 +208,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             } else {
 #pragma unroll
               for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(sB + j * MN_BOX_BYTES, &p.tmB, p.b_r0 + nt * BN + 64 * j, p.b_k0 + kb * BK, fb);
+                tma_load_2d(sB + j * MN_BOX_BYTES, &p.tmB, p.b_r0 + nt * BN + 64 * j, p.b_k0 + sc.b_k_off + kb * BK, fb);
             }
             if (++stage == STAGES) {
               stage = 0;
@@ -275,9 +289,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       bool valid = false;
       float m_run = -INFINITY, l_run = 0.f, z_lab = -INFINITY;  // EPI_LSE
       float lse2 = 0.f;                                         // EPI_GRAD
-      if constexpr (EPI == EPI_LSE || EPI == EPI_GRAD) {
-        if (row < p.n_rows) {
-          label = p.labels[row];
+      if constexpr (is_lse_epi<EPI>() || EPI == EPI_GRAD) {
+        if (sc.label_off + row < p.n_rows) {
+          label = p.labels[sc.label_off + row];
           valid = (label != p.ignore_index);
         }
         if constexpr (EPI == EPI_GRAD) {
@@ -329,6 +343,75 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           tc_fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
+        } else if constexpr (EPI == EPI_LSE_STASH) {
+          // Single-pass mode: the logits tile is rounded to bf16 (the reference's logits dtype,
+          // tied_linear.py:25) and stored into the row chunk's block S; the online log-sum-exp runs on the
+          // ROUNDED values, like ce_chunked_output_loss.py:41 upcasting bf16 logits.
+          const int cbase = p.col0 + nt * BN;
+#pragma unroll 1
+          for (int c = 0; c < BN / 64; ++c) {
+            uint32_t w[32];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float v[32];
+              tmem_ld32(taddr + c * 64 + h * 32, v);
+              const int ch0 = cbase + c * 64 + h * 32;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t pk = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                w[h * 16 + j] = pk;
+                v[2 * j] = bf16lo(pk);
+                v[2 * j + 1] = bf16hi(pk);
+              }
+              if (ch0 < p.vocab) {
+                if (ch0 + 32 > p.vocab) {
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (ch0 + j >= p.vocab) v[j] = -INFINITY;
+                }
+                if (valid && label >= ch0 && label < ch0 + 32) {
+                  const int jl = static_cast<int>(label - ch0);
+#pragma unroll
+                  for (int j = 0; j < 32; ++j)
+                    if (j == jl) z_lab = v[j];
+                }
+                float cmax = v[0];
+#pragma unroll
+                for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, v[j]);
+                const float m_new = fmaxf(m_run, cmax * LOG2E);
+                float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+                for (int j = 0; j < 32; j += 4) {
+                  s0 += fast_exp2(fmaf(v[j], LOG2E, -m_new));
+                  s1 += fast_exp2(fmaf(v[j + 1], LOG2E, -m_new));
+                  s2 += fast_exp2(fmaf(v[j + 2], LOG2E, -m_new));
+                  s3 += fast_exp2(fmaf(v[j + 3], LOG2E, -m_new));
+                }
+                l_run = l_run * fast_exp2(m_run - m_new) + ((s0 + s1) + (s2 + s3));
+                m_run = m_new;
+              }
+            }
+            if (c == BN / 64 - 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(tempty_bar(acc));
+            }
+            const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
+            if (issuer) tma_wait_group_read<1>();
+            named_bar_sync(1, EPI_THREADS);
+            stage_row_128B(buf, row_in_tile, w);
+            fence_proxy_async_smem();
+            named_bar_sync(1, EPI_THREADS);
+            if (issuer) {
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + it.m * BM;
+              if (p.store_policy)
+                tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
+              else
+                tma_store_2d(&p.tmC, buf, cc, cr);
+              tma_commit_group();
+            }
+            ++chunk_ctr;
+          }
         } else if constexpr (EPI == EPI_GRAD) {
           const int cbase = p.col0 + nt * BN;  // global vocab index of tile column 0
 #pragma unroll 1
@@ -402,7 +485,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer) {
-              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + it.m * BM;
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + it.m * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -435,7 +518,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer) {
-              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + it.m * BM;
+              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + sc.c_row_off + it.m * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -453,7 +536,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         }
       }
 
-      if constexpr (EPI == EPI_LSE) {
+      if constexpr (is_lse_epi<EPI>()) {
         // item.n0 / vtiles_per_split is the split index
         const int split = it.n0 / sc.vtiles_per_split;
         const size_t o = static_cast<size_t>(split) * sc.part_stride + row;

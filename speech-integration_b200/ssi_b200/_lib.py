@@ -11,13 +11,14 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 100
+ABI_VERSION = 101
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
     "ssi_b200_version": (c_int, []),
     "ssi_b200_last_error": (c_char_p, []),
     "ssi_b200_launch_count": (c_int64, []),
+    "ssi_b200_set_option": (c_int, [c_char_p, c_int64]),
     "ssi_b200_workspace_bytes": (
         c_int,
         [c_int64, c_int64, c_int64, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)],
@@ -32,6 +33,16 @@ SYMBOLS = {
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p,
          c_void_p, c_int, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_single_pass_workspace_bytes": (c_int, [c_int64, c_int64, c_int64, POINTER(c_size_t)]),
+    "ssi_b200_lmhead_ce_fwd_grad": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_lmhead_ce_apply_grad": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p],
     ),
     "ssi_b200_embedding_grad_scatter": (
         c_int,
@@ -93,11 +104,21 @@ def workspace_bytes(N: int, V: int, D: int, which: str = "all") -> tuple[int, in
     return f.value, b.value, s.value
 
 
+def single_pass_workspace_bytes(N: int, V: int, D: int) -> int:
+    b = c_size_t(0)
+    check(load().ssi_b200_single_pass_workspace_bytes(N, V, D, ctypes.byref(b)), "single_pass_workspace_bytes")
+    return b.value
+
+
+def set_option(name: str, value: int) -> None:
+    check(load().ssi_b200_set_option(name.encode(), int(value)), f"set_option({name})")
+
+
 def launch_count() -> int:
     return int(load().ssi_b200_launch_count())
 
 
-PROFILE_CLASSES = ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux", "_6", "_7")
+PROFILE_CLASSES = ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux", "softmax_grad", "_7")
 
 
 def profile_begin() -> None:
@@ -109,7 +130,7 @@ def profile_end() -> dict[str, tuple[float, int]]:
     ms = (ctypes.c_double * 8)()
     cnt = (ctypes.c_int64 * 8)()
     check(load().ssi_b200_profile_end(ctypes.cast(ms, c_void_p), ctypes.cast(cnt, c_void_p)), "profile_end")
-    return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(6)}
+    return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(7)}
 
 
 def plan_info(N: int, V: int, D: int) -> dict[str, int]:

@@ -8,6 +8,7 @@ the final normed HIDDEN states in those positions and this module does projectio
 """
 from __future__ import annotations
 
+import os
 from typing import List, Sequence, Union
 
 import torch
@@ -58,11 +59,72 @@ class _FusedLinearCE(torch.autograd.Function):
         return dX, dW, None, None, None, None
 
 
+_ONES: dict = {}
+
+
+def _one(device: torch.device) -> torch.Tensor:
+    t = _ONES.get(device)
+    if t is None:
+        t = torch.ones(1, dtype=torch.float32, device=device)
+        _ONES[device] = t
+    return t
+
+
+class _FusedLinearCESinglePass(torch.autograd.Function):
+    """Single-pass mode: when a gradient is needed, forward also forms dX and the fp32 dW sum (each logits tile
+    is computed once; a bounded bf16 block of logits/dlogits is the only scratch). Backward only rescales by
+    ``grad_out / grad_hint`` (1 when the trainer announced its multiplier) and rounds dW once into ``.grad``."""
+
+    @staticmethod
+    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint):
+        ctx.holder = holder
+        ctx.with_grad = bool(ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
+        if ctx.with_grad:
+            hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
+            loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(X, W, labels, hint, n_valid_override,
+                                                                        ignore_index)
+            ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
+        else:
+            loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
+        if holder is not None:
+            holder.last_loss_sum = loss_out[0:1]
+            holder.last_n_valid = n_valid
+        if n_valid_override is None:
+            return loss_out[1]
+        return loss_out[0] / n_valid_override[0].to(torch.float32)
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        if ctx.dW_acc is None:
+            raise RuntimeError("ssi_b200: single-pass backward called twice (the stashed gradients were consumed)")
+        g = grad_out.detach().to(torch.float32).reshape(1).contiguous()
+        holder = ctx.holder
+        dX, dW_acc, hint = ctx.dX, ctx.dW_acc, ctx.hint
+        ctx.dX = ctx.dW_acc = None
+        wparam = holder.weight_param() if holder is not None else None
+        if wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr:
+            acc = wparam.grad is not None
+            if not acc:
+                wparam.grad = torch.empty_like(wparam)
+            ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc)
+            return dX, None, None, None, None, None, None
+        _, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint)
+        return dX, dW, None, None, None, None, None
+
+
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                                ignore_index: int = -100, n_valid_total: torch.Tensor | None = None,
-                               _holder=None) -> torch.Tensor:
-    """Functional form: ``hidden [N, D]`` bf16, ``weight [V, D]`` bf16, ``labels [N]`` int64 -> fp32 0-dim loss."""
-    return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
+                               _holder=None, mode: str = "single_pass",
+                               grad_hint: torch.Tensor | None = None) -> torch.Tensor:
+    """Functional form: ``hidden [N, D]`` bf16, ``weight [V, D]`` bf16, ``labels [N]`` int64 -> fp32 0-dim loss.
+
+    ``mode``: ``"single_pass"`` (default; gradients formed during forward, 6 N V D flop) or ``"recompute"``
+    (forward keeps only the per-row logsumexp, backward recomputes the logits tiles, 8 N V D flop, no stash)."""
+    if mode == "recompute":
+        return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
+    if mode != "single_pass":
+        raise ValueError(f"ssi_b200: unknown mode {mode!r} (expected 'single_pass' or 'recompute')")
+    return _FusedLinearCESinglePass.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, grad_hint)
 
 
 class FusedLinearCrossEntropyLoss(nn.Module):
@@ -77,10 +139,17 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         ignore_index: label value that contributes nothing (default -100).
         accumulate_into_grad: write dW directly into ``tied_module.weight.grad`` instead of returning it to
             autograd (saves a ``[V, D]`` temporary and an AccumulateGrad pass).
+        mode: ``"single_pass"`` (default) or ``"recompute"``, see :func:`fused_linear_cross_entropy`;
+            overridable with the environment variable ``SSI_B200_MODE``.
+
+    Attribute ``grad_hint`` (fp32 device scalar or None = 1.0): the multiplier the caller will apply to the
+    loss before ``backward()`` (ssi/trainer.py:393 uses ``num_tokens_iter``). Purely an optimisation: with the
+    right hint single-pass gradients are rounded to bf16 once; any other upstream gradient is still exact up to
+    one extra bf16 rounding of dX.
     """
 
     def __init__(self, tied_module: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
-                 accumulate_into_grad: bool = True):
+                 accumulate_into_grad: bool = True, mode: str | None = None):
         super().__init__()
         if not hasattr(tied_module, "weight"):
             raise AttributeError(
@@ -91,6 +160,10 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         self.num_output_chunks = num_output_chunks
         self.ignore_index = ignore_index
         self.accumulate_into_grad = accumulate_into_grad
+        self.mode = mode or os.environ.get("SSI_B200_MODE", "single_pass")
+        if self.mode not in ("single_pass", "recompute"):
+            raise ValueError(f"ssi_b200: unknown mode {self.mode!r} (expected 'single_pass' or 'recompute')")
+        self.grad_hint: torch.Tensor | None = None
         self.n_valid_total: torch.Tensor | None = None  # set by ssi_b200.dist for data parallelism
         self.last_loss_sum: torch.Tensor | None = None
         self.last_n_valid: torch.Tensor | None = None
@@ -107,7 +180,7 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         """Sum-reduced CE of one chunk of hidden states (mirrors ce_chunked_output_loss.py:35-43, which takes
         logits): returned so that ``training.compile_loss``-style wrappers that call it keep working."""
         loss = fused_linear_cross_entropy(hidden.reshape(-1, hidden.size(-1)), self._tied.weight,
-                                          labels.reshape(-1), self.ignore_index, None, self)
+                                          labels.reshape(-1), self.ignore_index, None, self, self.mode, self.grad_hint)
         return loss * self.last_n_valid[0].to(torch.float32)
 
     def forward(self, hidden: Union[torch.Tensor, Sequence[torch.Tensor]], labels: torch.Tensor) -> torch.Tensor:
@@ -126,7 +199,8 @@ class FusedLinearCrossEntropyLoss(nn.Module):
             lab = lab.contiguous()
         if lab.numel() != X.size(0):
             raise ValueError(f"labels ({tuple(labels.shape)}) do not match hidden rows ({X.size(0)})")
-        return fused_linear_cross_entropy(X, W, lab, self.ignore_index, self.n_valid_total, self)
+        return fused_linear_cross_entropy(X, W, lab, self.ignore_index, self.n_valid_total, self, self.mode,
+                                          self.grad_hint)
 
 
 def make_torchtune_subclass():

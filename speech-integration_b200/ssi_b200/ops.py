@@ -112,6 +112,61 @@ def lmhead_ce_bwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, lse: t
     return dX, dW
 
 
+def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, grad_hint: torch.Tensor,
+                       n_valid_total: torch.Tensor | None = None, ignore_index: int = -100):
+    """Single-pass mode: fused projection + CE forward that also forms the gradients (each logits tile is
+    computed once). Returns ``(loss_out, lse, n_valid, dX, dW_acc)``; ``dX`` bf16 ``[N, D]`` and ``dW_acc`` fp32
+    ``[V, D]`` are the gradients for an upstream gradient of ``grad_hint`` (fp32 device scalar);
+    :func:`lmhead_ce_apply_grad` rescales them for the gradient autograd actually delivers.
+    """
+    dev = _require_cuda(X, W, labels, grad_hint)
+    N, V, D = _check_xw(X, W)
+    if labels.dtype != torch.int64 or labels.numel() != N or not labels.is_contiguous():
+        raise ValueError("ssi_b200: labels must be a contiguous int64 tensor with one entry per row of X")
+    if grad_hint.dtype != torch.float32 or grad_hint.numel() != 1:
+        raise ValueError("ssi_b200: grad_hint must be a single fp32 value on the device")
+    if n_valid_total is not None and (n_valid_total.dtype != torch.int64 or n_valid_total.numel() != 1
+                                      or n_valid_total.device != dev):
+        raise ValueError("ssi_b200: n_valid_total must be a single int64 value on the device")
+    lib = _lib.load()
+    ws = _workspace("single_pass", _lib.single_pass_workspace_bytes(N, V, D), dev)
+    lse = torch.empty(N, dtype=torch.float32, device=dev)
+    loss_out = torch.empty(2, dtype=torch.float32, device=dev)
+    n_valid = torch.empty(1, dtype=torch.int64, device=dev)
+    dX = torch.empty_like(X)
+    dW_acc = torch.empty(V, D, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_lmhead_ce_fwd_grad(
+            X.data_ptr(), W.data_ptr(), labels.data_ptr(), grad_hint.data_ptr(),
+            n_valid_total.data_ptr() if n_valid_total is not None else None, N, V, D, int(ignore_index),
+            lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), dX.data_ptr(), dW_acc.data_ptr(),
+            ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "lmhead_ce_fwd_grad")
+    return loss_out, lse, n_valid, dX, dW_acc
+
+
+def lmhead_ce_apply_grad(dX: torch.Tensor, dW_acc: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
+                         dW: torch.Tensor | None = None, accumulate_dW: bool = False):
+    """Backward of single-pass mode: ``dX *= grad_out / grad_hint`` in place (a no-op on the device when the
+    ratio is 1) and ``dW = bf16((accumulate ? dW : 0) + ratio * dW_acc)``. Returns ``(dX, dW)``."""
+    dev = _require_cuda(dX, dW_acc, grad_out, grad_hint)
+    N, D = dX.shape
+    V = dW_acc.size(0)
+    if dW is None:
+        if accumulate_dW:
+            raise ValueError("ssi_b200: accumulate_dW needs an existing dW buffer")
+        dW = torch.empty(V, D, dtype=torch.bfloat16, device=dev)
+    elif tuple(dW.shape) != (V, D) or dW.dtype != torch.bfloat16 or not dW.is_contiguous() or dW.device != dev:
+        raise ValueError("ssi_b200: dW must be a contiguous bf16 [V, D] tensor on the same device")
+    lib = _lib.load()
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_lmhead_ce_apply_grad(dX.data_ptr(), dW_acc.data_ptr(), grad_out.data_ptr(),
+                                               grad_hint.data_ptr(), N, V, D, dW.data_ptr(),
+                                               1 if accumulate_dW else 0, _stream(dev))
+    _lib.check(rc, "lmhead_ce_apply_grad")
+    return dX, dW
+
+
 def embedding_grad_scatter(dH: torch.Tensor, ids: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
     """``dW[ids[i]] += dH[i]`` in place (sorted-id warp-segmented reduction, deterministic). Returns ``dW``.
 

@@ -22,12 +22,12 @@ from .loss import FusedLinearCrossEntropyLoss
 
 class PathStep:
     def __init__(self, weight: nn.Parameter | torch.Tensor, ignore_index: int = -100, num_output_chunks: int = 8,
-                 process_group=None):
+                 process_group=None, mode: str | None = None):
         if not isinstance(weight, nn.Parameter):
             weight = nn.Parameter(weight)
         self.emb = nn.Embedding(weight.size(0), weight.size(1), device="meta", dtype=weight.dtype)
         self.emb.weight = weight
-        self.loss_fn = FusedLinearCrossEntropyLoss(self.emb, num_output_chunks, ignore_index)
+        self.loss_fn = FusedLinearCrossEntropyLoss(self.emb, num_output_chunks, ignore_index, mode=mode)
         self.ignore_index = ignore_index
         self.pg = process_group
         self.world = 1
@@ -67,6 +67,8 @@ class PathStep:
             gcounts = ddist.global_counts(counts, self.pg)
             self.loss_fn.n_valid_total = gcounts[1:2]
         n_iter = gcounts[0].to(torch.float32)
+        # announce the multiplier of ssi/trainer.py:393 so single-pass mode rounds its gradients once
+        self.loss_fn.grad_hint = n_iter.reshape(1)
         loss = self.loss_fn(hidden, shifted)
         loss_batch = loss * n_iter
         loss_batch.backward()

@@ -1,0 +1,142 @@
+"""GPU parity of SINGLE-PASS mode (ssi_b200_lmhead_ce_fwd_grad / _apply_grad through the C ABI): forward also
+forms dX and the fp32 dW sum from a bounded bf16 logits block, each logits tile computed once.
+
+Same oracle and tolerances as test_gpu_parity.py: loss rel. err <= 1e-3; dX, dW rel-Frobenius <= 4e-3 and per
+element |err| <= 2^-7 |ref| + 2^-8 max|ref| against the fp32 oracle.  The per-row logsumexp is taken on
+bf16-rounded logits (the reference's logits dtype), so it is compared with the oracle run in bf16 as well.
+"""
+import pytest
+import torch
+
+from oracle import reference_path as oracle
+from test_gpu_parity import CASES, LOSS_RTOL, _case, assert_grad_close
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture
+def small_blocks():
+    """Force several row chunks: cap the logits block at 1 MiB for the duration of a test."""
+    from ssi_b200 import _lib
+
+    _lib.set_option("g_cap_mib", 1)
+    yield
+    _lib.set_option("g_cap_mib", 4096)
+
+
+def _run(inp, D, upstream, hint=None):
+    from ssi_b200 import ops
+
+    X = inp["X"].reshape(-1, D).cuda()
+    W = inp["W"].cuda()
+    lab = inp["shifted"].reshape(-1).cuda()
+    h = torch.tensor([upstream if hint is None else hint], dtype=torch.float32, device="cuda")
+    loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(X, W, lab, h)
+    g = torch.tensor([upstream], dtype=torch.float32, device="cuda")
+    dX, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, h)
+    torch.cuda.synchronize()
+    return loss_out, lse, n_valid, dX, dW, dW_acc
+
+
+def _check(inp, D, out, upstream):
+    loss_out, lse, n_valid, dX, dW, _ = out
+    ref_loss = oracle.lmhead_ce(inp["X"].float(), inp["W"].float(), inp["shifted"])
+    assert n_valid.item() == oracle.count_valid(inp["shifted"])
+    assert abs(loss_out[1].item() - ref_loss.item()) <= LOSS_RTOL * abs(ref_loss.item())
+    # lse on bf16-rounded logits, as the reference computes it (tied_linear.py:25 -> ce_chunked_output_loss.py:41)
+    logits_bf16 = (inp["X"].reshape(-1, D).float() @ inp["W"].float().t()).to(torch.bfloat16).float()
+    ref_lse = torch.logsumexp(logits_bf16, dim=-1)
+    valid = inp["shifted"].reshape(-1) != -100
+    assert torch.allclose(lse.cpu()[valid], ref_lse[valid], rtol=1e-4, atol=2e-3)
+    assert (lse.cpu()[~valid] == 0).all()
+    _, rdX, rdW = oracle.lmhead_ce_fwd_bwd(inp["X"], inp["W"], inp["shifted"], upstream)
+    assert_grad_close(dX, rdX.reshape(-1, D), "dX")
+    assert_grad_close(dW, rdW, "dW")
+    assert (dX.float().cpu()[~valid] == 0).all()
+
+
+@pytest.mark.parametrize("cfg,B,S,V,D", CASES)
+def test_single_pass_matches_oracle(cfg, B, S, V, D):
+    inp = _case(cfg, B, S, V, D, seed=1)
+    upstream = float(oracle.count_valid(inp["labels"]))
+    _check(inp, D, _run(inp, D, upstream), upstream)
+
+
+@pytest.mark.parametrize("cfg,B,S,V,D", [("c3", 4, 300, 4098, 256), ("c2", 8, 256, 5002, 128), ("c4", 3, 700, 9000, 64)])
+def test_single_pass_many_row_chunks(small_blocks, cfg, B, S, V, D):
+    from ssi_b200 import _lib
+
+    inp = _case(cfg, B, S, V, D, seed=2)
+    upstream = float(oracle.count_valid(inp["labels"]))
+    out = _run(inp, D, upstream)
+    _check(inp, D, out, upstream)
+    # same inputs with one big block: the chunking only changes the fp32 summation order of dW
+    _lib.set_option("g_cap_mib", 4096)
+    one = _run(inp, D, upstream)
+    assert_grad_close(out[3], one[3], "dX(chunked vs one block)")
+    assert torch.allclose(out[5], one[5], rtol=1e-4, atol=1e-6 * float(one[5].abs().max()))
+
+
+def test_wrong_hint_is_rescaled_and_accumulate():
+    cfg, B, S, V, D = CASES[2]
+    inp = _case(cfg, B, S, V, D, seed=3)
+    upstream = float(oracle.count_valid(inp["labels"]))
+    from ssi_b200 import ops
+
+    out = _run(inp, D, upstream, hint=1.0)  # hint 1.0, real upstream = token count -> ratio path
+    _check(inp, D, out, upstream)
+    # accumulate into an existing gradient buffer
+    _, _, _, dX, dW, dW_acc = out
+    _, _, rdW = oracle.lmhead_ce_fwd_bwd(inp["X"], inp["W"], inp["shifted"], upstream)
+    base = (torch.randn(V, D) * rdW.abs().max()).to(torch.bfloat16)
+    dW2 = base.clone().cuda()
+    g = torch.tensor([upstream], dtype=torch.float32, device="cuda")
+    ops.lmhead_ce_apply_grad(dX.clone(), dW_acc, g, torch.ones(1, device="cuda"), dW=dW2, accumulate_dW=True)
+    torch.cuda.synchronize()
+    assert_grad_close(dW2, rdW + base.float(), "dW(accumulate)")
+
+
+def test_single_pass_deterministic_and_all_ignored():
+    from ssi_b200 import ops
+
+    cfg, B, S, V, D = CASES[3]
+    inp = _case(cfg, B, S, V, D, seed=4)
+    a = _run(inp, D, 17.0)
+    b = _run(inp, D, 17.0)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    X = torch.randn(128, 64).to(torch.bfloat16).cuda()
+    W = torch.randn(512, 64).to(torch.bfloat16).cuda()
+    lab = torch.full((128,), -100, dtype=torch.int64).cuda()
+    one = torch.ones(1, device="cuda")
+    loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(X, W, lab, one)
+    assert n_valid.item() == 0 and torch.isnan(loss_out[1]).item()
+    dX, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, one, one)
+    assert dX.float().abs().max().item() == 0 and dW.float().abs().max().item() == 0
+
+
+def test_module_modes_agree():
+    """FusedLinearCrossEntropyLoss in single_pass and recompute mode: same loss (to bf16-logit rounding) and
+    gradients within the oracle tolerance of each other, through autograd with the trainer's multiplier."""
+    from torch import nn
+
+    from ssi_b200.loss import FusedLinearCrossEntropyLoss
+
+    cfg, B, S, V, D = CASES[5]
+    inp = _case(cfg, B, S, V, D, seed=5)
+    res = {}
+    for mode in ("single_pass", "recompute"):
+        emb = nn.Embedding(V, D, dtype=torch.bfloat16, device="cuda")
+        with torch.no_grad():
+            emb.weight.copy_(inp["W"].cuda())
+        loss_fn = FusedLinearCrossEntropyLoss(emb, mode=mode)
+        h = inp["X"].cuda().requires_grad_(True)
+        n_iter = torch.tensor(float(oracle.count_valid(inp["labels"])), device="cuda")
+        loss_fn.grad_hint = n_iter.reshape(1)
+        loss = loss_fn([c for c in h.chunk(8, dim=1)], inp["shifted"].cuda())
+        (loss * n_iter).backward()
+        torch.cuda.synchronize()
+        res[mode] = (loss.item(), h.grad.clone(), emb.weight.grad.clone())
+    assert abs(res["single_pass"][0] - res["recompute"][0]) <= 1e-3 * abs(res["recompute"][0])
+    assert_grad_close(res["single_pass"][1], res["recompute"][1], "dX(single vs recompute)")
+    assert_grad_close(res["single_pass"][2], res["recompute"][2], "dW(single vs recompute)")

@@ -14,6 +14,6 @@ try:
     k = j["kernels"]
     print(" ".join(sys.argv[1:]), "| ms/step %.2f tok/s %.0f frac_burst %.3f clk %s %s |" % (
         j["ms_per_step"], j["value"], j["step_frac_of_bf16_peak"]["burst"], j["clocks"]["sm_mhz"], j["clocks"]["reasons"]),
-        " ".join("%s %.2f" % (n, k[n]["ms_per_step"]) for n in ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux")))
+        " ".join("%s %.2f" % (n, k[n]["ms_per_step"]) for n in ("lse_fwd", "dlogits", "softmax_grad", "dW", "dX", "scatter", "aux") if n in k))
 except Exception as e:
     print("FAILED", sys.argv[1:], e, out.stdout[-500:], out.stderr[-1500:])
