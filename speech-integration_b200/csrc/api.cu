@@ -156,24 +156,56 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
   return 0;
 }
 
-template <int EPI, bool A_MN, bool B_MN>
-int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat,
-                int grid_override = 0) {
-  auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN>;
+int cta_group();  // tuning knob, defined below
+
+template <int EPI, bool A_MN, bool B_MN, int CG>
+int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int grid_override) {
+  auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN, CG>;
   static bool attr_set = false;  // per instantiation
+  static int max_workers = 0;    // CTAs (CG 1) or CTA pairs (CG 2) that can be co-resident
   if (!attr_set) {
     SSI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::GEMM_SMEM_BYTES));
+    max_workers = sms / CG;
+    if (CG == 2) {
+      cudaLaunchConfig_t qc = {};
+      qc.gridDim = dim3(sms / 2 * 2), qc.blockDim = dim3(ssi::GEMM_THREADS);
+      qc.dynamicSmemBytes = ssi::GEMM_SMEM_BYTES;
+      cudaLaunchAttribute qa[1];
+      qa[0].id = cudaLaunchAttributeClusterDimension;
+      qa[0].val.clusterDim.x = 2, qa[0].val.clusterDim.y = 1, qa[0].val.clusterDim.z = 1;
+      qc.attrs = qa, qc.numAttrs = 1;
+      int n = 0;
+      SSI_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &qc));
+      if (n < 1) return fail(-5, "%s: no CTA pair can be resident (cudaOccupancyMaxActiveClusters = %d)", name, n);
+      if (n < max_workers) max_workers = n;
+    }
     attr_set = true;
   }
-  const int items = p.tiles_m * p.tiles_n;  // host-side upper bound when the schedule is device-side
+  const int tiles_m = (CG == 2) ? (p.tiles_m + 1) / 2 : p.tiles_m;
+  const int items = tiles_m * p.tiles_n;  // host-side upper bound when the schedule is device-side
   if (items <= 0 && grid_override <= 0) return 0;
-  const int grid = grid_override > 0 ? grid_override : (items < sms ? items : sms);
+  int workers = grid_override > 0 ? max_workers : (items < max_workers ? items : max_workers);
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(workers * CG), cfg.blockDim = dim3(ssi::GEMM_THREADS);
+  cfg.dynamicSmemBytes = ssi::GEMM_SMEM_BYTES, cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CG, at[0].val.clusterDim.y = 1, at[0].val.clusterDim.z = 1;
+  cfg.attrs = at, cfg.numAttrs = 1;
   {
     ProfScope ps(cat, st);
-    kern<<<grid, ssi::GEMM_THREADS, ssi::GEMM_SMEM_BYTES, st>>>(p);
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, p);
+    if (e != cudaSuccess) return fail(static_cast<int>(e), "launch %s: %s", name, cudaGetErrorString(e));
   }
   SSI_LAUNCH_OK(name);
   return 0;
+}
+
+template <int EPI, bool A_MN, bool B_MN>
+int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat,
+                int grid_override = 0) {
+  if (cta_group() == 2) return launch_gemm_cg<EPI, A_MN, B_MN, 2>(p, sms, st, name, cat, grid_override);
+  return launch_gemm_cg<EPI, A_MN, B_MN, 1>(p, sms, st, name, cat, grid_override);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -226,8 +258,11 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
 struct Tune {
   int64_t g_cap_elems = int64_t(1) << 31;  // dlogits block scratch cap: 4 GiB of bf16
   int64_t g_tiles = 0;                     // force the block width (256-column tiles); 0 = auto
-  int group_m_grad = 16, group_m_dw = 16, group_m_dx = 16;
+  int group_m_grad = 16, group_m_dw = 1, group_m_dx = 1;  // m-tiles per raster group (1 = n-fastest)
   int store_hint = 0;  // 1 = evict-first L2 policy on the dlogits / dW / dX tile stores
+  int k1_hints = 0, dw_hints = 0, dx_hints = 0;  // operand L2 policies: 10 * A + B; 1 evict-first, 2 evict-last
+  int lockstep = 64;   // k-blocks between lockstep sync points of the dW / dX contractions (0 = off)
+  int cta_group = 2;   // 2 = CTA pairs (tcgen05 cta_group::2, 256x256 tiles), 1 = single-CTA 128x256 tiles
 };
 Tune& tune() {
   static Tune t = [] {
@@ -238,9 +273,23 @@ Tune& tune() {
     if (const char* e = getenv("SSI_B200_GROUP_M_DW")) x.group_m_dw = atoi(e);
     if (const char* e = getenv("SSI_B200_GROUP_M_DX")) x.group_m_dx = atoi(e);
     if (const char* e = getenv("SSI_B200_STORE_HINT")) x.store_hint = atoi(e);
+    if (const char* e = getenv("SSI_B200_CTA_GROUP")) x.cta_group = atoi(e) == 1 ? 1 : 2;
+    if (const char* e = getenv("SSI_B200_K1_HINTS")) x.k1_hints = atoi(e);
+    if (const char* e = getenv("SSI_B200_LOCKSTEP")) x.lockstep = atoi(e);
+    if (const char* e = getenv("SSI_B200_DW_HINTS")) x.dw_hints = atoi(e);
+    if (const char* e = getenv("SSI_B200_DX_HINTS")) x.dx_hints = atoi(e);
     return x;
   }();
   return t;
+}
+
+int cta_group() { return tune().cta_group; }
+unsigned long long policy_of(int code) {
+  return code == 1 ? ssi::kEvictFirst : code == 2 ? ssi::kEvictLast : code == 3 ? ssi::kEvictNormal : 0ull;
+}
+void set_hints(ssi::GemmParams& p, int hints) {
+  p.a_policy = policy_of(hints / 10);
+  p.b_policy = policy_of(hints % 10);
 }
 
 struct BwdPlan {
@@ -293,8 +342,9 @@ struct SpPlan {
   int64_t n_pad, vpad;
   int tiles_m, vtiles_total, combine_blocks, t_max, chunks_max;
   CompactWs cw;
-  size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_dxc, off_s, bytes;
+  size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_dxc, off_s, bytes;
 };
+constexpr size_t SYNC_AREA_BYTES = 4096;
 
 int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   SpPlan f;
@@ -322,6 +372,7 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   f.off_loss_c = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
   f.off_bl = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(float), 256);
   f.off_bc = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(int), 256);
+  f.off_sync = o, o += SYNC_AREA_BYTES;
   f.off_dxc = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
   f.off_s = o, o += align_up(static_cast<size_t>(f.t_max) * ssi::BM * f.vpad * 2, 1024);
   f.bytes = o;
@@ -383,6 +434,11 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "group_m_dw")) t.group_m_dw = static_cast<int>(value);
   else if (!strcmp(name, "group_m_dx")) t.group_m_dx = static_cast<int>(value);
   else if (!strcmp(name, "store_hint")) t.store_hint = static_cast<int>(value);
+  else if (!strcmp(name, "cta_group")) t.cta_group = (value == 1) ? 1 : 2;
+  else if (!strcmp(name, "k1_hints")) t.k1_hints = static_cast<int>(value);
+  else if (!strcmp(name, "lockstep")) t.lockstep = static_cast<int>(value);
+  else if (!strcmp(name, "dw_hints")) t.dw_hints = static_cast<int>(value);
+  else if (!strcmp(name, "dx_hints")) t.dx_hints = static_cast<int>(value);
   else return fail(-1, "unknown option '%s'", name);
   return 0;
 }
@@ -434,7 +490,7 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   ssi::GemmParams p;
   memset(&p, 0, sizeof(p));
   if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
-  if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN / cta_group())) return r;
   p.dplan = dplan;
   p.m_from_plan = 1;
   p.tiles_m = f.tiles_m;  // upper bounds; the kernel takes tiles_m / splits from *dplan
@@ -503,7 +559,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
   CUtensorMap tmX_k, tmX_mn, tmW_k, tmW_mn, tmG_st, tmG_k, tmG_mn, tmdW, tmdX;
   if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, b.n_pad, D * 2, 64, ssi::BM)) return r;
   if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, b.n_pad, D * 2, 64, 64)) return r;
-  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN / cta_group())) return r;
   if (int r = make_tmap(&tmW_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, 64)) return r;
   if (int r = make_tmap(&tmG_st, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, G, b.vc, b.n_pad, b.vc * 2, 64, ssi::BM))
     return r;
@@ -542,7 +598,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.tiles_m = static_cast<int>(ceil_div(vrows, ssi::BM));
       p.tiles_n = d_tiles;
       p.k_blocks = static_cast<int>(b.n_pad / ssi::BK);
-      p.group_m = tune().group_m_dw;
+      p.group_m = tune().group_m_grad;
       p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.c_r0 = v0;
       p.c_reduce = accumulate_dW ? 1 : 0;
@@ -556,7 +612,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.dplan = dplan, p.m_from_plan = 1;
       p.tiles_m = b.tiles_m, p.tiles_n = d_tiles;
       p.k_blocks = vtn * (ssi::BN / ssi::BK);
-      p.group_m = tune().group_m_dx;
+      p.group_m = tune().group_m_grad;
       p.b_k0 = v0;
       p.c_reduce = (blk > 0) ? 1 : 0;
       if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
@@ -616,6 +672,9 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
   const int64_t rows_cap = static_cast<int64_t>(f.t_max) * ssi::BM;
   const int64_t* nvt = n_valid_total ? n_valid_total : n_valid;
+  unsigned int* sync_area = reinterpret_cast<unsigned int*>(wsb + f.off_sync);
+  const int lockstep = tune().lockstep;
+  if (lockstep > 0) SSI_CUDA(cudaMemsetAsync(sync_area, 0, SYNC_AREA_BYTES, st));
 
   {
     ProfScope ps(CAT_AUX, st);
@@ -632,7 +691,7 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
   CUtensorMap tmX_k, tmX_mn, tmW_k, tmW_mn, tmS_k, tmS_mn, tmdW, tmdXc;
   if (int r = make_tmap(&tmX_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
   if (int r = make_tmap(&tmX_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xc, D, f.n_pad, D * 2, 64, 64)) return r;
-  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN)) return r;
+  if (int r = make_tmap(&tmW_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, ssi::BN / cta_group())) return r;
   if (int r = make_tmap(&tmW_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, W, D, V, D * 2, 64, 64)) return r;
   if (int r = make_tmap(&tmS_k, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, S, f.vpad, rows_cap, f.vpad * 2, 64, ssi::BM))
     return r;
@@ -657,6 +716,7 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.vtiles_per_split = f.vtiles_total, p.vtiles_total = f.vtiles_total;
       p.part_m = part_m, p.part_l = part_l, p.part_z = part_z;
       p.part_stride = static_cast<int>(rows_cap);
+      set_hints(p, tune().k1_hints);
       if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
         return r;
     }
@@ -684,6 +744,8 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.k_blocks = static_cast<int>(rows_cap / ssi::BK);
       p.group_m = tune().group_m_dw;
       p.c_reduce = (ch > 0) ? 1 : 0;
+      set_hints(p, tune().dw_hints);
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_every = lockstep;
       if (int r = launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
     }
     // ---- dXc[chunk] = G W   (M = the chunk's token rows, N = D, K = padded vocabulary)
@@ -695,6 +757,8 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.tiles_m = f.t_max, p.tiles_n = d_tiles;
       p.k_blocks = f.vtiles_total * (ssi::BN / ssi::BK);
       p.group_m = tune().group_m_dx;
+      set_hints(p, tune().dx_hints);
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch + 1, p.sync_every = lockstep;
       if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
     }
   }
@@ -853,7 +917,7 @@ int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64
     if (int r = make_tmap(&p.tmA, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, A, M, K, M * 2, 64, 64)) return r;
   }
   if (!b_mn_major) {
-    if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, K, N, K * 2, 64, ssi::BN)) return r;
+    if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, K, N, K * 2, 64, ssi::BN / cta_group())) return r;
   } else {
     if (int r = make_tmap(&p.tmB, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, B, N, K, N * 2, 64, 64)) return r;
   }

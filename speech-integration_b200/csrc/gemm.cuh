@@ -20,15 +20,24 @@ constexpr int BM = 128;
 constexpr int BN = 256;
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
-constexpr int STAGES = 4;
 constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
-constexpr int B_STAGE_BYTES = BN * BK * 2;  // 32 KiB
-constexpr int STAGE_BYTES = A_STAGE_BYTES + B_STAGE_BYTES;
+// CG = CTAs per MMA (tcgen05 cta_group). CG 1: one CTA owns a 128x256 tile, stage = A 16 KiB + B 32 KiB, 4 stages.
+// CG 2: a CTA pair (one TPC) owns a 256x256 tile; each CTA stages its own 128 rows of A and HALF of B (128 of
+// the 256 columns), so a stage is 32 KiB per CTA (6 stages) and each SM pulls a third less operand data
+// through L2 / shared memory per flop.
+template <int CG> struct StageCfg {
+  static constexpr int B_BYTES = (BN / CG) * BK * 2;
+  static constexpr int BYTES = A_STAGE_BYTES + B_BYTES;
+  static constexpr int STAGES = (CG == 1) ? 4 : 6;
+};
+constexpr int MAX_STAGES = 6;
+constexpr int PIPE_BYTES = 4 * (A_STAGE_BYTES + BN * BK * 2);  // 192 KiB either way
+static_assert(StageCfg<1>::STAGES * StageCfg<1>::BYTES == PIPE_BYTES && StageCfg<2>::STAGES * StageCfg<2>::BYTES == PIPE_BYTES, "");
 constexpr int MN_BOX_BYTES = 64 * BK * 2;  // one {64 MN, 64 K} TMA box of an MN-major operand = 8 KiB
 constexpr int EPI_BUF_BYTES = 128 * 128;   // 128 rows x 128 B staging tile for TMA stores
 constexpr int NUM_EPI_BUFS = 2;
 constexpr int SMEM_BAR_BYTES = 256;
-constexpr int GEMM_SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + NUM_EPI_BUFS * EPI_BUF_BYTES + SMEM_BAR_BYTES;
+constexpr int GEMM_SMEM_BYTES = 1024 + PIPE_BYTES + NUM_EPI_BUFS * EPI_BUF_BYTES + SMEM_BAR_BYTES;
 constexpr int GEMM_THREADS = 192;
 constexpr int EPI_THREADS = 128;
 constexpr int TMEM_COLS = 512;
@@ -49,6 +58,12 @@ struct GemmParams {
   int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
   unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
+  unsigned long long a_policy, b_policy;  // L2 cache policy of the A / B operand loads (0 = default)
+  // Lockstep throttle (EPI_BF16 / EPI_F32 only, uniform K loops): every `sync_every` k-blocks the producers of
+  // all co-running tiles meet at a split-phase counter barrier, so the tiles of one wave stream the same
+  // K window of their shared operands through L2 together instead of drifting apart.  nullptr = off.
+  unsigned int* sync_ctr;
+  int sync_every;
   // Device-side schedule (row compaction): when set, token-dependent sizes are read from *dplan at kernel start
   const DevPlan* dplan;
   int m_from_plan;  // tiles_m (and for EPI_LSE the split schedule and partial stride) come from dplan
@@ -138,23 +153,45 @@ __device__ __forceinline__ void stage_row_128B(uint32_t buf, int row, const uint
     st_shared_v4(base + ((j ^ sw) << 4), w[4 * j], w[4 * j + 1], w[4 * j + 2], w[4 * j + 3]);
 }
 
-template <int EPI, bool A_MN, bool B_MN>
+// epilogue warp -> MMA issuer: "this accumulator buffer has been read" (CG 2: the barrier lives in the leader CTA)
+template <int CG>
+__device__ __forceinline__ void release_acc(uint32_t bar) {
+  if constexpr (CG == 2)
+    mbar_arrive_cluster(bar, 0);
+  else
+    mbar_arrive(bar);
+}
+
+template <int EPI, bool A_MN, bool B_MN, int CG = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
+  constexpr int STAGES = StageCfg<CG>::STAGES;
+  constexpr int STAGE_BYTES = StageCfg<CG>::BYTES;
+  constexpr int BN_CTA = BN / CG;  // B columns staged by this CTA
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_stage0 = smem_base;
-  const uint32_t smem_epi0 = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t smem_epi0 = smem_base + PIPE_BYTES;
   const uint32_t smem_bar0 = smem_epi0 + NUM_EPI_BUFS * EPI_BUF_BYTES;
-  // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then the TMEM base address slot
+  // barriers: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2], then the TMEM base address slot.
+  // CG 2: full[] and tmem_empty[] are only used in the leader CTA (rank 0) of the pair; empty[] and
+  // tmem_full[] exist in both and are arrived on by the leader's multicast tcgen05.commit.
   auto full_bar = [&](int s) { return smem_bar0 + 8u * s; };
-  auto empty_bar = [&](int s) { return smem_bar0 + 8u * (STAGES + s); };
-  auto tfull_bar = [&](int s) { return smem_bar0 + 8u * (2 * STAGES + s); };
-  auto tempty_bar = [&](int s) { return smem_bar0 + 8u * (2 * STAGES + 2 + s); };
-  const uint32_t tmem_slot = smem_bar0 + 8u * (2 * STAGES + 4);
+  auto empty_bar = [&](int s) { return smem_bar0 + 8u * (MAX_STAGES + s); };
+  auto tfull_bar = [&](int s) { return smem_bar0 + 8u * (2 * MAX_STAGES + s); };
+  auto tempty_bar = [&](int s) { return smem_bar0 + 8u * (2 * MAX_STAGES + 2 + s); };
+  const uint32_t tmem_slot = smem_bar0 + 8u * (2 * MAX_STAGES + 4);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const Sched sc = make_sched<EPI>(p);
+  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const int worker = (CG == 2) ? (blockIdx.x >> 1) : blockIdx.x;       // CTA (pair) index
+  const int workers = (CG == 2) ? (gridDim.x >> 1) : gridDim.x;
+  Sched sc = make_sched<EPI>(p);
+  const int tiles_m_real = sc.tiles_m;  // in 128-row tiles
+  if constexpr (CG == 2) {
+    sc.tiles_m = (sc.tiles_m + 1) >> 1;  // the schedule runs over 256-row tile pairs
+    sc.group_m = max(1, sc.group_m >> 1);
+  }
   const int total_items = sc.tiles_m * sc.tiles_n;
 
   if (warp == 0 && lane == 0) {
@@ -167,48 +204,80 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     }
     for (int s = 0; s < 2; ++s) {
       mbar_init(tfull_bar(s), 1);
-      mbar_init(tempty_bar(s), 4);
+      mbar_init(tempty_bar(s), 4 * CG);
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc<1>(tmem_slot, TMEM_COLS);
-    tmem_relinquish<1>();
+    tmem_alloc<CG>(tmem_slot, TMEM_COLS);
+    tmem_relinquish<CG>();
   }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) {
+    cluster_arrive();
+    cluster_wait();
+  } else {
+    __syncthreads();
+  }
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
   if (warp == 0) {
-    // ===================================================== TMA producer
+    // ===================================================== TMA producer (one per CTA)
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+      // lockstep throttle: only the leader producers take part (the peer follows through the shared pipeline)
+      const bool throttle = !is_lse_epi<EPI>() && EPI != EPI_GRAD && p.sync_ctr != nullptr && p.sync_every > 0 &&
+                            cta_rank == 0 && workers > 1;
+      const int sync_T = throttle ? p.sync_every : 0x7fffffff;
+      const int sync_pts = throttle ? (sc.k_blocks - 1) / sync_T : 0;  // points at kb = T, 2T, ... < k_blocks
+      unsigned int sync_base = 0;                                       // arrivals of all earlier rounds
+      for (int item = worker; item < total_items; item += workers) {
         const TileItem it = decode_item<EPI>(sc, item);
+        const int m_tile = (CG == 2) ? (2 * it.m + static_cast<int>(cta_rank)) : it.m;
+        const unsigned int round_workers = static_cast<unsigned int>(min(workers, total_items - (item - worker)));
         for (int t = 0; t < it.ncount; ++t) {
           const int nt = it.n0 + t;
+          const int b_row = p.b_r0 + nt * BN + static_cast<int>(cta_rank) * BN_CTA;
+          int next_arrive = sync_T, next_wait = 0x7fffffff, sync_j = 0;
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
+            if (throttle) {
+              if (kb == next_arrive) {
+                atomicAdd(p.sync_ctr, 1u);
+                next_wait = min(kb + sync_T / 2, sc.k_blocks - 1);
+                next_arrive = (sync_j + 1 < sync_pts) ? kb + sync_T : 0x7fffffff;
+              }
+              if (kb == next_wait) {
+                const unsigned int target = sync_base + static_cast<unsigned int>(sync_j + 1) * round_workers;
+                while (ld_acquire_gpu(p.sync_ctr) < target) {
+                }
+                ++sync_j;
+                next_wait = 0x7fffffff;
+              }
+            }
             mbar_wait(empty_bar(stage), phase ^ 1u);
-            const uint32_t fb = full_bar(stage);
-            mbar_expect_tx(fb, STAGE_BYTES);
+            // CG 2: both CTAs signal the LEADER's full barrier; only the leader posts the expected bytes
+            const uint32_t fb = (CG == 2) ? (full_bar(stage) & 0xFEFFFFFFu) : full_bar(stage);
+            if (CG == 1 || cta_rank == 0) mbar_expect_tx(full_bar(stage), CG * STAGE_BYTES);
             const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
             const uint32_t sB = sA + A_STAGE_BYTES;
             if constexpr (!A_MN) {
-              tma_load_2d(sA, &p.tmA, p.a_k0 + kb * BK, p.a_r0 + sc.a_row_off + it.m * BM, fb);
+              tma_load_2d_g<CG>(sA, &p.tmA, p.a_k0 + kb * BK, p.a_r0 + sc.a_row_off + m_tile * BM, fb, p.a_policy);
             } else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j)
-                tma_load_2d(sA + j * MN_BOX_BYTES, &p.tmA, p.a_r0 + it.m * BM + 64 * j, p.a_k0 + kb * BK, fb);
+                tma_load_2d_g<CG>(sA + j * MN_BOX_BYTES, &p.tmA, p.a_r0 + m_tile * BM + 64 * j, p.a_k0 + kb * BK, fb,
+                                  p.a_policy);
             }
             if constexpr (!B_MN) {
-              tma_load_2d(sB, &p.tmB, p.b_k0 + kb * BK, p.b_r0 + nt * BN, fb);
+              tma_load_2d_g<CG>(sB, &p.tmB, p.b_k0 + kb * BK, b_row, fb, p.b_policy);
             } else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tma_load_2d(sB + j * MN_BOX_BYTES, &p.tmB, p.b_r0 + nt * BN + 64 * j, p.b_k0 + sc.b_k_off + kb * BK, fb);
+              for (int j = 0; j < BN_CTA / 64; ++j)
+                tma_load_2d_g<CG>(sB + j * MN_BOX_BYTES, &p.tmB, b_row + 64 * j, p.b_k0 + sc.b_k_off + kb * BK, fb,
+                                  p.b_policy);
             }
             if (++stage == STAGES) {
               stage = 0;
@@ -216,12 +285,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             }
           }
         }
+        sync_base += static_cast<unsigned int>(sync_pts) * round_workers;
       }
     }
   } else if (warp == 1) {
-    // ===================================================== MMA issuer (single thread)
-    if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
+    // ===================================================== MMA issuer (single thread; CG 2: leader CTA only)
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * CG, BN, A_MN ? 1 : 0, B_MN ? 1 : 0);
       constexpr uint32_t A_LBO = A_MN ? MN_BOX_BYTES : 16;
       constexpr uint32_t B_LBO = B_MN ? MN_BOX_BYTES : 16;
       constexpr uint32_t A_KADV = A_MN ? (UMMA_K * 128) : (UMMA_K * 2);  // bytes per UMMA_K step
@@ -230,10 +300,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+      for (int item = worker; item < total_items; item += workers) {
         const TileItem it = decode_item<EPI>(sc, item);
         for (int t = 0; t < it.ncount; ++t) {
-          mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+          if constexpr (CG == 2)
+            mbar_wait_cluster(tempty_bar(acc), acc_phase ^ 1u);
+          else
+            mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
           tc_fence_after();
           const uint32_t d_tmem = tmem_base + acc * BN;
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
@@ -245,15 +318,21 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t adesc = make_smem_desc(sA + k * A_KADV, A_LBO, 1024);
               const uint64_t bdesc = make_smem_desc(sB + k * B_KADV, B_LBO, 1024);
-              umma_bf16<1>(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_bf16<CG>(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
             }
-            umma_commit(empty_bar(stage));
+            if constexpr (CG == 2)
+              umma_commit_cg2(empty_bar(stage), 3);
+            else
+              umma_commit(empty_bar(stage));
             if (++stage == STAGES) {
               stage = 0;
               phase ^= 1u;
             }
           }
-          umma_commit(tfull_bar(acc));
+          if constexpr (CG == 2)
+            umma_commit_cg2(tfull_bar(acc), 3);
+          else
+            umma_commit(tfull_bar(acc));
           if (++acc == 2) {
             acc = 0;
             acc_phase ^= 1u;
@@ -280,9 +359,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       gscale = (nv > 0) ? (*p.grad_out / static_cast<float>(nv)) : 0.f;
     }
 
-    for (int item = blockIdx.x; item < total_items; item += gridDim.x) {
+    for (int item = worker; item < total_items; item += workers) {
       const TileItem it = decode_item<EPI>(sc, item);
-      const int row = it.m * BM + row_in_tile;  // global row of this thread
+      const int m_tile = (CG == 2) ? (2 * it.m + static_cast<int>(cta_rank)) : it.m;
+      const bool m_ok = (CG == 1) || (m_tile < tiles_m_real);  // odd tile count: the pair's 2nd tile is a phantom
+      const int row = m_tile * BM + row_in_tile;  // row of this thread (relative to the plan's row0)
 
       // per-item row state
       long long label = p.ignore_index;
@@ -342,7 +423,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) release_acc<CG>(tempty_bar(acc));
         } else if constexpr (EPI == EPI_LSE_STASH) {
           // Single-pass mode: the logits tile is rounded to bf16 (the reference's logits dtype,
           // tied_linear.py:25) and stored into the row chunk's block S; the online log-sum-exp runs on the
@@ -394,7 +475,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             if (c == BN / 64 - 1) {
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(tempty_bar(acc));
+              if (lane == 0) release_acc<CG>(tempty_bar(acc));
             }
             const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
             if (issuer) tma_wait_group_read<1>();
@@ -402,8 +483,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             stage_row_128B(buf, row_in_tile, w);
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
-            if (issuer) {
-              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + it.m * BM;
+            if (issuer && m_ok) {
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (p.store_policy)
                 tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
               else
@@ -441,7 +522,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             if (c == BN / 64 - 1) {  // accumulator fully read: release it to the MMA warp
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(tempty_bar(acc));
+              if (lane == 0) release_acc<CG>(tempty_bar(acc));
             }
             const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
             if (issuer) tma_wait_group_read<1>();
@@ -449,11 +530,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             stage_row_128B(buf, row_in_tile, w);
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
-            if (issuer) {
+            if (issuer && m_ok) {
               if (p.store_policy)
-                tma_store_2d_hint(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM, p.store_policy);
+                tma_store_2d_hint(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + m_tile * BM, p.store_policy);
               else
-                tma_store_2d(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + it.m * BM);
+                tma_store_2d(&p.tmC, buf, p.c_c0 + nt * BN + c * 64, p.c_r0 + m_tile * BM);
               tma_commit_group();
             }
             ++chunk_ctr;
@@ -476,7 +557,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             if (c == BN / 64 - 1) {
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(tempty_bar(acc));
+              if (lane == 0) release_acc<CG>(tempty_bar(acc));
             }
             const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
             if (issuer) tma_wait_group_read<1>();
@@ -484,8 +565,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             stage_row_128B(buf, row_in_tile, w);
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
-            if (issuer) {
-              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + it.m * BM;
+            if (issuer && m_ok) {
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -509,7 +590,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             if (c == BN / 32 - 1) {
               tc_fence_before();
               __syncwarp();
-              if (lane == 0) mbar_arrive(tempty_bar(acc));
+              if (lane == 0) release_acc<CG>(tempty_bar(acc));
             }
             const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
             if (issuer) tma_wait_group_read<1>();
@@ -517,8 +598,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             stage_row_128B(buf, row_in_tile, w);
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
-            if (issuer) {
-              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + sc.c_row_off + it.m * BM;
+            if (issuer && m_ok) {
+              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -539,10 +620,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       if constexpr (is_lse_epi<EPI>()) {
         // item.n0 / vtiles_per_split is the split index
         const int split = it.n0 / sc.vtiles_per_split;
-        const size_t o = static_cast<size_t>(split) * sc.part_stride + row;
-        p.part_m[o] = m_run;
-        p.part_l[o] = l_run;
-        p.part_z[o] = z_lab;
+        if (m_ok) {
+          const size_t o = static_cast<size_t>(split) * sc.part_stride + row;
+          p.part_m[o] = m_run;
+          p.part_l[o] = l_run;
+          p.part_z[o] = z_lab;
+        }
       }
     }
     if constexpr (EPI != EPI_LSE) {
@@ -550,12 +633,17 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     }
   }
 
-  // ---- teardown
+  // ---- teardown (CG 2: neither CTA may leave while its peer can still touch its smem / barriers / TMEM)
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) {
+    cluster_arrive();
+    cluster_wait();
+  } else {
+    __syncthreads();
+  }
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc<1>(tmem_base, TMEM_COLS);
+    tmem_dealloc<CG>(tmem_base, TMEM_COLS);
   }
 }
 

@@ -84,6 +84,12 @@ __device__ __forceinline__ void mbar_wait_cluster(uint32_t bar, uint32_t parity)
   }
 }
 
+__device__ __forceinline__ unsigned int ld_acquire_gpu(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
 // ------------------------------------------------------------------ named barriers / fences
 __device__ __forceinline__ void named_bar_sync(uint32_t id, uint32_t nthreads) {
   asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
@@ -122,6 +128,28 @@ __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const void* tmap, 
       "[%2];" ::"r"(dst),
       "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_cg2_hint(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar,
+                                                     uint64_t pol) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.L2::cache_hint [%0], "
+      "[%1, {%3, %4}], [%2], %5;" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "l"(pol)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_2d_hint(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar,
+                                                 uint64_t pol);
+// pol = 0: default L2 policy
+template <int CG>
+__device__ __forceinline__ void tma_load_2d_g(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar,
+                                              uint64_t pol = 0) {
+  if constexpr (CG == 2) {
+    if (pol) tma_load_2d_cg2_hint(dst, tmap, c0, c1, bar, pol);
+    else tma_load_2d_cg2(dst, tmap, c0, c1, bar);
+  } else {
+    if (pol) tma_load_2d_hint(dst, tmap, c0, c1, bar, pol);
+    else tma_load_2d(dst, tmap, c0, c1, bar);
+  }
 }
 // shared -> global tile store / reduce-add (bulk async group)
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
