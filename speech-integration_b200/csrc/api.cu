@@ -256,7 +256,7 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
 
 // Tuning knobs (environment, read once): for experiments from bench.py without rebuilding.
 struct Tune {
-  int64_t g_cap_elems = int64_t(1) << 31;  // dlogits block scratch cap: 4 GiB of bf16
+  int64_t g_cap_elems = int64_t(1) << 31;  // logits / dlogits block scratch cap: 4 GiB of bf16
   int64_t g_tiles = 0;                     // force the block width (256-column tiles); 0 = auto
   int group_m_grad = 16, group_m_dw = 1, group_m_dx = 1;  // m-tiles per raster group (1 = n-fastest)
   int store_hint = 0;  // 1 = evict-first L2 policy on the dlogits / dW / dX tile stores
@@ -479,7 +479,8 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   {
     ProfScope ps(CAT_AUX, st);
     ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(f.n_pad),
-                                                  ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms);
+                                                  ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms,
+                                                  0, 0, 0, nullptr, cta_group());
     SSI_LAUNCH_OK("compact_scan");
     ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
@@ -548,7 +549,8 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
   {
     ProfScope ps(CAT_AUX, st);
     ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(b.n_pad),
-                                                  ignore_index, pos, idx, labels_c, dplan, b.vtiles_total, di->sms);
+                                                  ignore_index, pos, idx, labels_c, dplan, b.vtiles_total, di->sms,
+                                                  0, 0, 0, nullptr, cta_group());
     SSI_LAUNCH_OK("compact_scan");
     ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xc), lse, lse_c);
@@ -680,7 +682,7 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
     ProfScope ps(CAT_AUX, st);
     ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(f.n_pad),
                                                   ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms,
-                                                  f.t_max, f.chunks_max, d_tiles, n_valid);
+                                                  f.t_max, f.chunks_max, d_tiles, n_valid, cta_group());
     SSI_LAUNCH_OK("compact_scan");
     ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,

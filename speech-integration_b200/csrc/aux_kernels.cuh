@@ -31,8 +31,11 @@ constexpr int PLAN_AREA_BYTES = 4096;
 constexpr int MAX_LSE_ITEMS = 8192;  // cap on tiles_m * splits (bounds the partial arrays)
 
 // K1 split count: smallest s whose static-schedule makespan (waves x tiles per split) is within 1% of the best
-__device__ inline void choose_splits(int tiles_m, int vtiles_total, int sms, int& splits, int& per_split) {
+// `cg` = CTAs per work item (1, or 2 for CTA pairs owning two m-tiles); `sms / cg` items run concurrently.
+__device__ inline void choose_splits(int tiles_m, int vtiles_total, int sms, int cg, int& splits, int& per_split) {
   int best_s = 1;
+  const int units_m = (tiles_m + cg - 1) / cg;
+  sms = max(sms / cg, 1);
   if (tiles_m > 0) {
     const int max_s = min(vtiles_total, 148);
     long long best = -1;
@@ -41,7 +44,7 @@ __device__ inline void choose_splits(int tiles_m, int vtiles_total, int sms, int
         if (s2 > 1 && static_cast<long long>(s2) * tiles_m > MAX_LSE_ITEMS) break;
         const int pr = (vtiles_total + s2 - 1) / s2;
         if ((vtiles_total + pr - 1) / pr != s2) continue;
-        const long long items = static_cast<long long>(tiles_m) * s2;
+        const long long items = static_cast<long long>(units_m) * s2;
         const long long c = ((items + sms - 1) / sms) * pr;
         if (pass == 0) {
           if (best < 0 || c < best) best = c;
@@ -63,7 +66,8 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
                                                             int* __restrict__ idx, int64_t* __restrict__ labels_c,
                                                             DevPlan* __restrict__ plan, int vtiles_total, int sms,
                                                             int chunk_t_max = 0, int chunks_max = 0,
-                                                            int d_tiles = 0, int64_t* n_valid_out = nullptr) {
+                                                            int d_tiles = 0, int64_t* n_valid_out = nullptr,
+                                                            int cg = 1) {
   __shared__ int s_sum[1024];
   __shared__ int s_chunk_t;
   const int per = (n + 1023) / 1024;
@@ -100,7 +104,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
     d.tiles_m = (n_valid + 127) / 128;
     d.k_blocks_tok = d.tiles_m * 2;
     d.part_stride = d.tiles_m * 128;
-    choose_splits(d.tiles_m, vtiles_total, sms, d.splits, d.vtiles_per_split);
+    choose_splits(d.tiles_m, vtiles_total, sms, cg, d.splits, d.vtiles_per_split);
     d.row0 = d.pad1 = 0;
     *plan = d;
     if (n_valid_out) *n_valid_out = n_valid;
@@ -113,8 +117,9 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
         const int full = d.tiles_m / t, rem = d.tiles_m % t;
         const int nch = full + (rem ? 1 : 0);
         if (nch > chunks_max) continue;
-        float cost = static_cast<float>(full) * ((t * d_tiles + sms - 1) / sms) + 0.3f * nch;
-        if (rem) cost += (rem * d_tiles + sms - 1) / sms;
+        const int wk = max(sms / cg, 1);  // concurrent work items (CTAs or CTA pairs)
+        float cost = static_cast<float>(full) * ((((t + cg - 1) / cg) * d_tiles + wk - 1) / wk) + 0.3f * nch;
+        if (rem) cost += (((rem + cg - 1) / cg) * d_tiles + wk - 1) / wk;
         if (best_cost < 0.f || cost <= best_cost) best_cost = cost, best_t = t;
       }
     }
@@ -132,7 +137,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
       d.n_valid = max(0, min(n_valid - d.row0, d.tiles_m * 128));
       d.k_blocks_tok = d.tiles_m * 2;
       d.part_stride = d.tiles_m * 128;
-      choose_splits(d.tiles_m, vtiles_total, sms, d.splits, d.vtiles_per_split);
+      choose_splits(d.tiles_m, vtiles_total, sms, cg, d.splits, d.vtiles_per_split);
       d.pad1 = 0;
       plan[1 + c] = d;
     }
