@@ -4,8 +4,10 @@
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c5]
 
 One "step" = one pass of the hot path over one batch of synthetic input: label shift + token
-counts, K1 fused projection + online-LSE CE forward, K2 recompute backward (dX, dW), K3 tied-embedding scatter-add
-and, for N > 1, the NCCL all-reduce of the token counts and of the tied gradient.  The default workload is
+counts, the fused projection + CE forward and backward (default single-pass mode: per row chunk K1 logits tiles ->
+bf16 block + online LSE, softmax-grad in place, dW_acc += G^T X, dX = G W, then rescale/round in backward;
+--mode recompute: K1 online-LSE forward, K2 recompute backward), K3 tied-embedding scatter-add and, for N > 1, the
+NCCL all-reduce of the token counts and of the tied gradient.  The default workload is
 BASELINE.json configs[4] / SURVEY c5 — HuBERT 5000-DSU vocabulary (V = 133,258, the "@133k vocab" the metric is
 quoted on), global batch 64 x 2048 — sharded by sequences over the ranks (strong scaling: the global batch is
 fixed; at N = 1 the whole batch runs on one GPU).

@@ -79,12 +79,13 @@ class TiedEmbeddingB200(nn.Embedding):
 
 
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
-            replace_embedding: bool = True) -> FusedLinearCrossEntropyLoss:
+            replace_embedding: bool = True, mode: str | None = None) -> FusedLinearCrossEntropyLoss:
     """Mirror of ``Trainer._setup_loss`` (ssi/trainer.py:299-304) for the fused path.
 
     Replaces ``model.output`` by a hidden passthrough, optionally swaps ``model.tok_embeddings`` for
     :class:`TiedEmbeddingB200` (sharing the same Parameter), calls ``model.set_num_output_chunks`` when the model
-    has it, and returns the loss module to use as ``loss_fn``.
+    has it, and returns the loss module to use as ``loss_fn``. ``mode``: ``"single_pass"`` (default) or
+    ``"recompute"``, see :func:`ssi_b200.loss.fused_linear_cross_entropy`.
     """
     emb = model.tok_embeddings
     if replace_embedding and isinstance(emb, nn.Embedding) and not isinstance(emb, TiedEmbeddingB200):
@@ -92,7 +93,7 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
         model.tok_embeddings = emb
     model.output = HiddenPassthroughOutput(emb)
     cls = make_torchtune_subclass() or FusedLinearCrossEntropyLoss
-    loss_fn = cls(emb, num_output_chunks=num_output_chunks, ignore_index=ignore_index)
+    loss_fn = cls(emb, num_output_chunks=num_output_chunks, ignore_index=ignore_index, mode=mode)
     if hasattr(model, "set_num_output_chunks"):
         model.set_num_output_chunks(loss_fn.num_output_chunks)
     return loss_fn
