@@ -158,9 +158,9 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
 
 int cta_group();  // tuning knob, defined below
 
-template <int EPI, bool A_MN, bool B_MN, int CG>
+template <int EPI, bool A_MN, bool B_MN, int CG, int NW = 1>
 int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int grid_override) {
-  auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN, CG>;
+  auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN, CG, NW>;
   static bool attr_set = false;  // per instantiation
   static int max_workers = 0;    // CTAs (CG 1) or CTA pairs (CG 2) that can be co-resident
   if (!attr_set) {
@@ -182,7 +182,7 @@ int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const cha
     attr_set = true;
   }
   const int tiles_m = (CG == 2) ? (p.tiles_m + 1) / 2 : p.tiles_m;
-  const int items = tiles_m * p.tiles_n;  // host-side upper bound when the schedule is device-side
+  const int items = tiles_m * ((p.tiles_n + NW - 1) / NW);  // host-side upper bound when the schedule is device-side
   if (items <= 0 && grid_override <= 0) return 0;
   int workers = grid_override > 0 ? max_workers : (items < max_workers ? items : max_workers);
   cudaLaunchConfig_t cfg = {};
@@ -206,6 +206,13 @@ int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* 
                 int grid_override = 0) {
   if (cta_group() == 2) return launch_gemm_cg<EPI, A_MN, B_MN, 2>(p, sms, st, name, cat, grid_override);
   return launch_gemm_cg<EPI, A_MN, B_MN, 1>(p, sms, st, name, cat, grid_override);
+}
+
+// Long-K contractions (single-pass dW / dX): 256x512 tiles per CTA pair when `wide` == 2 ("wide_dw" / "wide_dx").
+template <int EPI, bool A_MN, bool B_MN>
+int launch_gemm_wide(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int wide) {
+  if (cta_group() == 2 && wide == 2) return launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(p, sms, st, name, cat, 0);
+  return launch_gemm<EPI, A_MN, B_MN>(p, sms, st, name, cat);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -263,6 +270,7 @@ struct Tune {
   int k1_hints = 0, dw_hints = 0, dx_hints = 0;  // operand L2 policies: 10 * A + B; 1 evict-first, 2 evict-last
   int lockstep = 64;   // k-blocks between lockstep sync points of the dW / dX contractions (0 = off)
   int cta_group = 2;   // 2 = CTA pairs (tcgen05 cta_group::2, 256x256 tiles), 1 = single-CTA 128x256 tiles
+  int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
 };
 Tune& tune() {
   static Tune t = [] {
@@ -278,6 +286,8 @@ Tune& tune() {
     if (const char* e = getenv("SSI_B200_LOCKSTEP")) x.lockstep = atoi(e);
     if (const char* e = getenv("SSI_B200_DW_HINTS")) x.dw_hints = atoi(e);
     if (const char* e = getenv("SSI_B200_DX_HINTS")) x.dx_hints = atoi(e);
+    if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
+    if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
     return x;
   }();
   return t;
@@ -439,6 +449,8 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "lockstep")) t.lockstep = static_cast<int>(value);
   else if (!strcmp(name, "dw_hints")) t.dw_hints = static_cast<int>(value);
   else if (!strcmp(name, "dx_hints")) t.dx_hints = static_cast<int>(value);
+  else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
+  else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
   else return fail(-1, "unknown option '%s'", name);
   return 0;
 }
@@ -682,7 +694,9 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
     ProfScope ps(CAT_AUX, st);
     ssi::compact_scan_kernel<<<1, 1024, 0, st>>>(labels, static_cast<int>(N), static_cast<int>(f.n_pad),
                                                   ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms,
-                                                  f.t_max, f.chunks_max, d_tiles, n_valid, cta_group());
+                                                  f.t_max, f.chunks_max,
+                                                  (cta_group() == 2 && tune().wide_dx == 2) ? (d_tiles + 1) / 2 : d_tiles,
+                                                  n_valid, cta_group());
     SSI_LAUNCH_OK("compact_scan");
     ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
@@ -748,7 +762,8 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.c_reduce = (ch > 0) ? 1 : 0;
       set_hints(p, tune().dw_hints);
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_every = lockstep;
-      if (int r = launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
+      if (int r = launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
+        return r;
     }
     // ---- dXc[chunk] = G W   (M = the chunk's token rows, N = D, K = padded vocabulary)
     {
@@ -761,7 +776,8 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.group_m = tune().group_m_dx;
       set_hints(p, tune().dx_hints);
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch + 1, p.sync_every = lockstep;
-      if (int r = launch_gemm<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
+      if (int r = launch_gemm_wide<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX, tune().wide_dx))
+        return r;
     }
   }
   ProfScope ps_aux(CAT_AUX, st);
@@ -930,8 +946,10 @@ int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64
   p.group_m = 8;
   p.c_reduce = accumulate ? 1 : 0;
   if (!a_mn_major && !b_mn_major) return launch_gemm<ssi::EPI_F32, false, false>(p, di->sms, st, "debug_gemm_kk", CAT_AUX);
-  if (a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, true, true>(p, di->sms, st, "debug_gemm_mm", CAT_AUX);
-  if (!a_mn_major && b_mn_major) return launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "debug_gemm_km", CAT_AUX);
+  if (a_mn_major && b_mn_major)
+    return launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "debug_gemm_mm", CAT_AUX, tune().wide_dw);
+  if (!a_mn_major && b_mn_major)
+    return launch_gemm_wide<ssi::EPI_F32, false, true>(p, di->sms, st, "debug_gemm_km", CAT_AUX, tune().wide_dx);
   return fail(-1, "unsupported operand majors (a_mn=%d, b_mn=%d)", a_mn_major, b_mn_major);
 }
 

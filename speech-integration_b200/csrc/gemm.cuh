@@ -25,14 +25,22 @@ constexpr int A_STAGE_BYTES = BM * BK * 2;  // 16 KiB
 // CG 2: a CTA pair (one TPC) owns a 256x256 tile; each CTA stages its own 128 rows of A and HALF of B (128 of
 // the 256 columns), so a stage is 32 KiB per CTA (6 stages) and each SM pulls a third less operand data
 // through L2 / shared memory per flop.
-template <int CG> struct StageCfg {
-  static constexpr int B_BYTES = (BN / CG) * BK * 2;
+// NW = n-tiles per work item (CG 2 only).  NW 2: the pair owns a 256x512 tile -- BOTH 256-column accumulators of
+// the 512 TMEM columns belong to one tile and share every A stage, so a stage is A 16 KiB + 2 x 16 KiB of B per
+// CTA (4 stages) and each SM pulls a quarter less operand data through L2 per flop than with 256x256 tiles.  The
+// accumulator is then single-buffered (the epilogue no longer overlaps the next tile's MMAs), which only suits
+// the long-K contractions (dW, dX).
+template <int CG, int NW = 1> struct StageCfg {
+  static_assert(NW == 1 || (NW == 2 && CG == 2), "wide tiles need a CTA pair");
+  static constexpr int B_HALF_BYTES = (BN / CG) * BK * 2;
+  static constexpr int B_BYTES = NW * B_HALF_BYTES;
   static constexpr int BYTES = A_STAGE_BYTES + B_BYTES;
-  static constexpr int STAGES = (CG == 1) ? 4 : 6;
+  static constexpr int STAGES = (CG == 1) ? 4 : (NW == 2 ? 4 : 6);
 };
 constexpr int MAX_STAGES = 6;
 constexpr int PIPE_BYTES = 4 * (A_STAGE_BYTES + BN * BK * 2);  // 192 KiB either way
-static_assert(StageCfg<1>::STAGES * StageCfg<1>::BYTES == PIPE_BYTES && StageCfg<2>::STAGES * StageCfg<2>::BYTES == PIPE_BYTES, "");
+static_assert(StageCfg<1>::STAGES * StageCfg<1>::BYTES == PIPE_BYTES && StageCfg<2>::STAGES * StageCfg<2>::BYTES == PIPE_BYTES &&
+              StageCfg<2, 2>::STAGES * StageCfg<2, 2>::BYTES == PIPE_BYTES, "");
 constexpr int MN_BOX_BYTES = 64 * BK * 2;  // one {64 MN, 64 K} TMA box of an MN-major operand = 8 KiB
 constexpr int EPI_BUF_BYTES = 128 * 128;   // 128 rows x 128 B staging tile for TMA stores
 constexpr int NUM_EPI_BUFS = 2;
@@ -162,11 +170,14 @@ __device__ __forceinline__ void release_acc(uint32_t bar) {
     mbar_arrive(bar);
 }
 
-template <int EPI, bool A_MN, bool B_MN, int CG = 1>
+template <int EPI, bool A_MN, bool B_MN, int CG = 1, int NW = 1>
 __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_constant__ GemmParams p) {
-  constexpr int STAGES = StageCfg<CG>::STAGES;
-  constexpr int STAGE_BYTES = StageCfg<CG>::BYTES;
-  constexpr int BN_CTA = BN / CG;  // B columns staged by this CTA
+  static_assert(NW == 1 || EPI == EPI_BF16 || EPI == EPI_F32, "wide tiles: plain store epilogues only");
+  constexpr int STAGES = StageCfg<CG, NW>::STAGES;
+  constexpr int STAGE_BYTES = StageCfg<CG, NW>::BYTES;
+  constexpr int BN_CTA = BN / CG;  // B columns of ONE 256-column n-tile staged by this CTA
+  constexpr int B_HALF_BYTES = StageCfg<CG, NW>::B_HALF_BYTES;
+  constexpr int BNW = BN * NW;     // output columns per work item
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t smem_stage0 = smem_base;
@@ -192,6 +203,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     sc.tiles_m = (sc.tiles_m + 1) >> 1;  // the schedule runs over 256-row tile pairs
     sc.group_m = max(1, sc.group_m >> 1);
   }
+  if constexpr (NW == 2) sc.tiles_n = (sc.tiles_n + 1) >> 1;  // ... and over 512-column tile pairs
   const int total_items = sc.tiles_m * sc.tiles_n;
 
   if (warp == 0 && lane == 0) {
@@ -240,7 +252,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         const unsigned int round_workers = static_cast<unsigned int>(min(workers, total_items - (item - worker)));
         for (int t = 0; t < it.ncount; ++t) {
           const int nt = it.n0 + t;
-          const int b_row = p.b_r0 + nt * BN + static_cast<int>(cta_rank) * BN_CTA;
+          const int b_row = p.b_r0 + nt * BNW + static_cast<int>(cta_rank) * BN_CTA;
           int next_arrive = sync_T, next_wait = 0x7fffffff, sync_j = 0;
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
             if (throttle) {
@@ -271,13 +283,16 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
                 tma_load_2d_g<CG>(sA + j * MN_BOX_BYTES, &p.tmA, p.a_r0 + m_tile * BM + 64 * j, p.a_k0 + kb * BK, fb,
                                   p.a_policy);
             }
-            if constexpr (!B_MN) {
-              tma_load_2d_g<CG>(sB, &p.tmB, p.b_k0 + kb * BK, b_row, fb, p.b_policy);
-            } else {
 #pragma unroll
-              for (int j = 0; j < BN_CTA / 64; ++j)
-                tma_load_2d_g<CG>(sB + j * MN_BOX_BYTES, &p.tmB, b_row + 64 * j, p.b_k0 + sc.b_k_off + kb * BK, fb,
-                                  p.b_policy);
+            for (int h = 0; h < NW; ++h) {
+              if constexpr (!B_MN) {
+                tma_load_2d_g<CG>(sB + h * B_HALF_BYTES, &p.tmB, p.b_k0 + kb * BK, b_row + h * BN, fb, p.b_policy);
+              } else {
+#pragma unroll
+                for (int j = 0; j < BN_CTA / 64; ++j)
+                  tma_load_2d_g<CG>(sB + h * B_HALF_BYTES + j * MN_BOX_BYTES, &p.tmB, b_row + h * BN + 64 * j,
+                                    p.b_k0 + sc.b_k_off + kb * BK, fb, p.b_policy);
+              }
             }
             if (++stage == STAGES) {
               stage = 0;
@@ -308,7 +323,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           else
             mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
           tc_fence_after();
-          const uint32_t d_tmem = tmem_base + acc * BN;
+          const uint32_t d_tmem = tmem_base + (NW == 2 ? 0 : acc * BN);
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
             mbar_wait(full_bar(stage), phase);
             tc_fence_after();
@@ -317,8 +332,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
             for (int k = 0; k < BK / UMMA_K; ++k) {
               const uint64_t adesc = make_smem_desc(sA + k * A_KADV, A_LBO, 1024);
-              const uint64_t bdesc = make_smem_desc(sB + k * B_KADV, B_LBO, 1024);
-              umma_bf16<CG>(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+#pragma unroll
+              for (int h = 0; h < NW; ++h) {
+                const uint64_t bdesc = make_smem_desc(sB + h * B_HALF_BYTES + k * B_KADV, B_LBO, 1024);
+                umma_bf16<CG>(d_tmem + h * BN, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              }
             }
             if constexpr (CG == 2)
               umma_commit_cg2(empty_bar(stage), 3);
@@ -333,7 +351,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             umma_commit_cg2(tfull_bar(acc), 3);
           else
             umma_commit(tfull_bar(acc));
-          if (++acc == 2) {
+          if (NW == 2 || ++acc == 2) {  // wide tiles: one accumulator set, the phase flips every tile
             acc = 0;
             acc_phase ^= 1u;
           }
@@ -384,7 +402,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
         const int nt = it.n0 + t;
         mbar_wait(tfull_bar(acc), acc_phase);
         tc_fence_after();
-        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + acc * BN;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + (NW == 2 ? 0 : acc * BN);
 
         if constexpr (EPI == EPI_LSE) {
           const int cbase = p.col0 + nt * BN;
@@ -541,7 +559,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         } else if constexpr (EPI == EPI_BF16) {
 #pragma unroll 1
-          for (int c = 0; c < BN / 64; ++c) {
+          for (int c = 0; c < BNW / 64; ++c) {
             uint32_t w[32];
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -554,7 +572,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
               for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
             }
-            if (c == BN / 64 - 1) {
+            if (c == BNW / 64 - 1) {
               tc_fence_before();
               __syncwarp();
               if (lane == 0) release_acc<CG>(tempty_bar(acc));
@@ -566,7 +584,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
-              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
+              const int cc = p.c_c0 + nt * BNW + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -579,7 +597,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         } else {  // EPI_F32
 #pragma unroll 1
-          for (int c = 0; c < BN / 32; ++c) {
+          for (int c = 0; c < BNW / 32; ++c) {
             uint32_t w[32];
             {
               float v[32];
@@ -587,7 +605,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
               for (int j = 0; j < 32; ++j) w[j] = zero_acc ? 0u : __float_as_uint(v[j]);
             }
-            if (c == BN / 32 - 1) {
+            if (c == BNW / 32 - 1) {
               tc_fence_before();
               __syncwarp();
               if (lane == 0) release_acc<CG>(tempty_bar(acc));
@@ -599,7 +617,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
-              const int cc = p.c_c0 + nt * BN + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
+              const int cc = p.c_c0 + nt * BNW + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (p.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -611,7 +629,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             ++chunk_ctr;
           }
         }
-        if (++acc == 2) {
+        if (NW == 2 || ++acc == 2) {
           acc = 0;
           acc_phase ^= 1u;
         }

@@ -17,8 +17,25 @@ def _mk(shape, seed):
 
 @pytest.mark.parametrize("M,N,K", SHAPES)
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (True, True), (False, True)])
-def test_debug_gemm(M, N, K, a_mn, b_mn):
-    from ssi_b200 import ops
+@pytest.mark.parametrize("wide", [2, 1])
+def test_debug_gemm(M, N, K, a_mn, b_mn, wide):
+    """wide = 2: the long-K contractions run 256x512 tiles per CTA pair (both TMEM accumulators on one tile);
+    wide = 1: 256x256 tiles with a double-buffered accumulator.  (K,K) always uses 256x256."""
+    from ssi_b200 import _lib, ops
+
+    if wide == 1 and not a_mn and not b_mn:
+        pytest.skip("(K,K) has no wide variant")
+    _lib.load()
+    _lib.set_option("wide_dw", wide)
+    _lib.set_option("wide_dx", wide)
+    try:
+        _run_debug_gemm(ops, M, N, K, a_mn, b_mn)
+    finally:
+        _lib.set_option("wide_dw", 2)
+        _lib.set_option("wide_dx", 2)
+
+
+def _run_debug_gemm(ops, M, N, K, a_mn, b_mn):
 
     A = _mk((K, M) if a_mn else (M, K), 1)
     B = _mk((K, N) if b_mn else (N, K), 2)
