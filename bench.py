@@ -45,6 +45,9 @@ def parse_args():
     ap.add_argument("--config", default="c5", help="SURVEY.md §8d configuration (c1..c5)")
     ap.add_argument("--mode", default=None, choices=["single_pass", "recompute"],
                     help="gradient mode of the fused loss (default: the library default, single_pass)")
+    ap.add_argument("--exchange", default=None, choices=["peer", "nccl"],
+                    help="N > 1: how the tied gradient is summed over ranks (default: peer-memory reduce behind "
+                         "the last dX contraction; nccl = bf16 all_reduce after the step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     return ap.parse_args()
@@ -215,7 +218,7 @@ def run_ours(args):
         dist.all_reduce(nv)
     n_valid_global = int(nv.item())
 
-    path = PathStep(W, process_group=pg, mode=args.mode)
+    path = PathStep(W, process_group=pg, mode=args.mode, exchange=args.exchange)
     mode = path.loss_fn.mode
 
     def step():
@@ -297,6 +300,11 @@ def run_ours(args):
                       "every step (LossReader, read one step behind)", "loss_last": e2e_losses[-1]}
         del hx, hd
 
+    mismatch = path.loss_fn.grad_hint_mismatch
+    if mismatch is not None and bool(mismatch.any().item()):
+        raise SystemExit("bench.py: the peer exchange ran with a multiplier that backward did not confirm")
+    exchange = path.exchange
+    path.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -340,7 +348,7 @@ def run_ours(args):
         "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(cfg), "rows_per_rank": n_local, "valid_rows_global": n_valid_global,
-                   "parallelism": f"dp{world}", "mode": mode, "l2": "inputs (X, W, dlogits blocks) are several times larger than "
+                   "parallelism": f"dp{world}", "mode": mode, "exchange": exchange, "l2": "inputs (X, W, dlogits blocks) are several times larger than "
                    "the 126 MB L2, no explicit flush", "loss_batch_rank0": loss_batch},
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
         "step_algorithmic_tflops_per_gpu": step_tflops,

@@ -23,6 +23,8 @@
  *   ssi_b200_embedding_grad_scatter <- backward of nn.Embedding built at tt/torchtune/models/llama3_2/
  *                               _component_builders.py:114 and called at tt/torchtune/modules/transformer.py:628
  *   ssi_b200_label_shift_count <- ssi/loss.py:16 (label shift) + ssi/trainer.py:391 (token count)
+ *   ssi_b200_dp_*            <- no reference counterpart (the reference trains on one GPU); the exchange step of
+ *                               SURVEY.md 8(e), semantics of tt/recipes/full_finetune_distributed.py:844-851,867
  */
 #ifndef SSI_B200_H_
 #define SSI_B200_H_
@@ -34,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 101
+#define SSI_B200_ABI_VERSION 102
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -111,10 +113,19 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
                                 int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                 float* dW_acc, void* ws, size_t ws_bytes, void* stream);
 
+/* Same, plus `dw_ready_event` (a cudaEvent_t, may be NULL): recorded on `stream` right after the LAST dW
+ * contraction, i.e. as soon as dW_acc is final and while the last dX contraction is still to run, so that a
+ * caller can start the data-parallel exchange of the tied gradient on another stream behind it. */
+int ssi_b200_lmhead_ce_fwd_grad_ev(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                   const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                   int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, void* dw_ready_event);
+
 /*
  * Backward of single-pass mode: ratio = grad_out / grad_hint (exactly 1 when the hint was right);
  *   dX *= ratio in place (skipped on the device when ratio == 1; dX may be NULL)
  *   dW  = bf16((accumulate_dW ? dW : 0) + ratio * dW_acc)     -- one rounding of the whole-batch fp32 sum
+ *        (dW may be NULL: the data-parallel exchange below then does this step for the summed gradient)
  */
 int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
                                   int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW, void* stream);
@@ -127,6 +138,37 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
  */
 int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
                                     void* ws, size_t ws_bytes, void* stream);
+
+/* The same scatter-add into an fp32 [V, D] buffer (data-parallel mode: the embedding gradient joins the fp32
+ * dW_acc of single-pass mode before the exchange, so the summed tied gradient is rounded to bf16 exactly once). */
+int ssi_b200_embedding_grad_scatter_f32(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
+                                        float* dW_acc, void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * Data-parallel exchange of the tied LM-head / embedding gradient over NVLink peer memory (one process per GPU,
+ * one NVSwitch node; the reference is single-process, semantics follow tt/recipes/full_finetune_distributed.py:
+ * 844-851,867: gradients of the global mean).  Each rank owns one exchange buffer
+ *     [ctrl 4 KiB][dW_acc fp32 V x D][stage bf16 ceil(V / world) x D]
+ * that its peers map through CUDA IPC.  dp_buffer_bytes gives its size and the offset of dW_acc (pass that
+ * address as `dW_acc` of ssi_b200_lmhead_ce_fwd_grad[_ev] / ssi_b200_embedding_grad_scatter_f32).  dp_alloc /
+ * dp_open / dp_close / dp_free are SET-UP calls (they allocate and synchronise); `ipc_handle` is 64 bytes to
+ * be carried to the peers by the host (torch.distributed all_gather).
+ *
+ * dp_exchange (enqueue-only, like every other entry point):
+ *   dW = bf16((accumulate_dW ? dW : 0) + (grad_out / grad_hint) * sum over ranks in rank order of dW_acc_rank)
+ * on every rank, bit-identical across ranks and runs: rank r reduces vocabulary slice r in fp32 from its peers'
+ * buffers (P2P loads), rounds once, and all ranks then pull the finished bf16 slices.  The kernels use no
+ * shared memory, so they co-reside with the tensor-core CTAs of a dX contraction running on another stream.
+ *   peer_bufs  host array [world] of the exchange buffers as mapped in this process (entry `rank` = own buffer)
+ *   epoch      a counter the caller increments by one per exchange, starting at 1, identical on all ranks
+ */
+int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, size_t* bytes, size_t* dw_acc_offset);
+int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle);
+int ssi_b200_dp_open(const void* ipc_handle, void** ptr);
+int ssi_b200_dp_close(void* ptr);
+int ssi_b200_dp_free(void* ptr);
+int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, uint32_t epoch,
+                         const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW, void* stream);
 
 /*
  * labels_out[b, s] = labels[b, s+1] for s < S-1, ignore_index for s == S-1 (ssi/loss.py:16);
@@ -142,7 +184,7 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
  * profile_end waits for those events and fills ms_by_class[8] / launches_by_class[8] (either may be NULL):
  *   0 = K1 logits + online-LSE (fwd), 1 = K2a dlogits recompute, 2 = K2b dW contraction, 3 = K2c dX contraction,
  *   4 = K3 embedding scatter (sort + segmented reduce, one entry per call), 5 = small helper kernels,
- *   6 = single-pass softmax-grad pass (S -> dlogits in place, HBM-bound), 7 unused.
+ *   6 = single-pass softmax-grad pass (S -> dlogits in place, HBM-bound), 7 = data-parallel exchange.
  * This pair is the only part of the ABI that synchronises (profile_end) or allocates (events, lazily).
  */
 int ssi_b200_profile_begin(void);

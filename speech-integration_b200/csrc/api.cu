@@ -15,6 +15,7 @@
 
 #include "../../include/ssi_b200.h"
 #include "aux_kernels.cuh"
+#include "dp_exchange.cuh"
 #include "gemm.cuh"
 
 namespace {
@@ -24,7 +25,7 @@ std::atomic<long long> g_launches{0};
 
 // ---- optional per-kernel-class timing with CUDA events on the launching stream (bench.py's roofline leg)
 enum ProfCat { CAT_LSE = 0, CAT_DLOGITS = 1, CAT_DW = 2, CAT_DX = 3, CAT_SCATTER = 4, CAT_AUX = 5, CAT_SOFTMAX = 6,
-               CAT_COUNT = 8 };
+               CAT_EXCHANGE = 7, CAT_COUNT = 8 };
 struct ProfRec {
   int cat;
   cudaEvent_t a, b;
@@ -657,6 +658,14 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
                                 const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
                                 int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                 float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
+  return ssi_b200_lmhead_ce_fwd_grad_ev(X, W, labels, grad_hint, n_valid_total, N, V, D, ignore_index, lse, loss_out,
+                                        n_valid, dX, dW_acc, ws, ws_bytes, stream, nullptr);
+}
+
+int ssi_b200_lmhead_ce_fwd_grad_ev(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                   const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                   int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, void* dw_ready_event) {
   if (int r = check_common(X, W, N, V, D)) return r;
   SSI_CHECK_ARG(labels && grad_hint && lse && loss_out && n_valid && dX && dW_acc && ws, "null pointer argument");
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0,
@@ -759,11 +768,14 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
       p.tiles_n = d_tiles;
       p.k_blocks = static_cast<int>(rows_cap / ssi::BK);
       p.group_m = tune().group_m_dw;
-      p.c_reduce = (ch > 0) ? 1 : 0;
+      p.c_reduce = 0, p.c_reduce_plan = 1;  // the first NON-EMPTY round overwrites dW_acc, later rounds add
       set_hints(p, tune().dw_hints);
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
         return r;
+      // dW_acc is final after the last round's contraction (the real chunks occupy the last rounds): let the
+      // caller start the gradient exchange on another stream while this stream still runs the last dX
+      if (dw_ready_event && ch == f.chunks_max - 1) SSI_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(dw_ready_event), st));
     }
     // ---- dXc[chunk] = G W   (M = the chunk's token rows, N = D, K = padded vocabulary)
     {
@@ -795,7 +807,7 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
 
 int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
                                   int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW, void* stream) {
-  SSI_CHECK_ARG(dW_acc && grad_out && grad_hint && dW, "null pointer argument");
+  SSI_CHECK_ARG(grad_out && grad_hint && (dW_acc || !dW), "null pointer argument");
   SSI_CHECK_ARG(N >= 0 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0 &&
@@ -810,15 +822,20 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
                                                       grad_out, grad_hint);
     SSI_LAUNCH_OK("apply_dx");
   }
-  ssi::apply_dw_kernel<<<di->sms * 16, 256, 0, st>>>(reinterpret_cast<const float4*>(dW_acc),
-                                                     static_cast<size_t>(V) * D / 4, grad_out, grad_hint,
-                                                     accumulate_dW ? 1 : 0, static_cast<uint2*>(dW));
-  SSI_LAUNCH_OK("apply_dw");
+  if (dW) {
+    ssi::apply_dw_kernel<<<di->sms * 16, 256, 0, st>>>(reinterpret_cast<const float4*>(dW_acc),
+                                                       static_cast<size_t>(V) * D / 4, grad_out, grad_hint,
+                                                       accumulate_dW ? 1 : 0, static_cast<uint2*>(dW));
+    SSI_LAUNCH_OK("apply_dw");
+  }
   return 0;
 }
 
-int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
-                                    void* ws, size_t ws_bytes, void* stream) {
+}  // extern "C"
+namespace {
+template <typename OutT>
+int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, OutT* dW,
+                                void* ws, size_t ws_bytes, void* stream) {
   SSI_CHECK_ARG(dH && ids && dW && ws, "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
@@ -854,13 +871,123 @@ int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t 
   float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
   ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
   const int grid = static_cast<int>(ceil_div(s.nwarps, 8));
-  ssi::scatter_reduce_kernel<<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
-                                                   static_cast<uint32_t>(V), static_cast<int>(D),
-                                                   static_cast<__nv_bfloat16*>(dW), partial, info);
+  ssi::scatter_reduce_kernel<OutT><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
+                                                         static_cast<uint32_t>(V), static_cast<int>(D), dW, partial, info);
   SSI_LAUNCH_OK("scatter_reduce");
-  ssi::scatter_fixup_kernel<<<grid, 256, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
-                                                  static_cast<int>(D), static_cast<__nv_bfloat16*>(dW));
+  ssi::scatter_fixup_kernel<OutT><<<grid, 256, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
+                                                        static_cast<int>(D), dW);
   SSI_LAUNCH_OK("scatter_fixup");
+  return 0;
+}
+}  // namespace
+extern "C" {
+
+int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
+                                    void* ws, size_t ws_bytes, void* stream) {
+  return embedding_grad_scatter_impl(dH, ids, N, V, D, static_cast<__nv_bfloat16*>(dW), ws, ws_bytes, stream);
+}
+
+int ssi_b200_embedding_grad_scatter_f32(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
+                                        float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
+  return embedding_grad_scatter_impl(dH, ids, N, V, D, dW_acc, ws, ws_bytes, stream);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Data-parallel exchange of the tied gradient over NVLink peer memory (dp_exchange.cuh)
+// ---------------------------------------------------------------------------------------------------
+int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, size_t* bytes, size_t* dw_acc_offset) {
+  SSI_CHECK_ARG(bytes, "null pointer argument");
+  SSI_CHECK_ARG(V >= 1 && D >= 8 && D % 8 == 0, "bad shape V=%lld D=%lld", (long long)V, (long long)D);
+  SSI_CHECK_ARG(world >= 1 && world <= ssi::DP_MAX_WORLD, "world size %d not in [1, %d]", world, ssi::DP_MAX_WORLD);
+  const int64_t vs = ceil_div(V, world);
+  *bytes = ssi::DP_CTRL_BYTES + static_cast<size_t>(V) * D * 4 + static_cast<size_t>(vs) * D * 2;
+  if (dw_acc_offset) *dw_acc_offset = ssi::DP_CTRL_BYTES;
+  return 0;
+}
+
+int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle) {
+  SSI_CHECK_ARG(ptr && ipc_handle && bytes >= ssi::DP_CTRL_BYTES, "bad argument");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  void* p = nullptr;
+  SSI_CUDA(cudaMalloc(&p, bytes));
+  SSI_CUDA(cudaMemset(p, 0, ssi::DP_CTRL_BYTES));
+  cudaIpcMemHandle_t h;
+  cudaError_t e = cudaIpcGetMemHandle(&h, p);
+  if (e != cudaSuccess) {
+    cudaFree(p);
+    return fail(static_cast<int>(e), "cudaIpcGetMemHandle: %s", cudaGetErrorString(e));
+  }
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(ipc_handle, &h, sizeof(h));
+  *ptr = p;
+  return 0;
+}
+
+int ssi_b200_dp_open(const void* ipc_handle, void** ptr) {
+  SSI_CHECK_ARG(ipc_handle && ptr, "null pointer argument");
+  cudaIpcMemHandle_t h;
+  memcpy(&h, ipc_handle, sizeof(h));
+  SSI_CUDA(cudaIpcOpenMemHandle(ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return 0;
+}
+
+int ssi_b200_dp_close(void* ptr) {
+  SSI_CHECK_ARG(ptr, "null pointer argument");
+  SSI_CUDA(cudaIpcCloseMemHandle(ptr));
+  return 0;
+}
+
+int ssi_b200_dp_free(void* ptr) {
+  SSI_CHECK_ARG(ptr, "null pointer argument");
+  SSI_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, uint32_t epoch,
+                         const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW, void* stream) {
+  SSI_CHECK_ARG(peer_bufs && grad_out && grad_hint && dW, "null pointer argument");
+  SSI_CHECK_ARG(world >= 1 && world <= ssi::DP_MAX_WORLD && rank >= 0 && rank < world, "bad rank %d / world %d", rank,
+                world);
+  SSI_CHECK_ARG(V >= 1 && D >= 8 && D % 8 == 0, "bad shape V=%lld D=%lld", (long long)V, (long long)D);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ssi::DpPeers peers;
+  memset(&peers, 0, sizeof(peers));
+  for (int p = 0; p < world; ++p) {
+    SSI_CHECK_ARG(peer_bufs[p], "null exchange buffer for rank %d", p);
+    peers.buf[p] = static_cast<char*>(peer_bufs[p]);
+  }
+  const long long total_f4 = static_cast<long long>(V) * D / 4;
+  const long long slice_f4 = static_cast<long long>(ceil_div(V, world)) * D / 4;
+  const int grid = di->sms * 2;
+  uint2* out = static_cast<uint2*>(dW);
+  ProfScope ps(CAT_EXCHANGE, st);
+#define SSI_DP_CASE(W_)                                                                                          \
+  case W_:                                                                                                       \
+    ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, rank, slice_f4, total_f4, epoch, grad_out, \
+                                                                grad_hint, accumulate_dW ? 1 : 0, out);          \
+    SSI_LAUNCH_OK("dp_reduce");                                                                                  \
+    if (W_ > 1) {                                                                                                \
+      ssi::dp_gather_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, rank, slice_f4, total_f4, epoch, out);  \
+      SSI_LAUNCH_OK("dp_gather");                                                                                \
+    }                                                                                                            \
+    break;
+  switch (world) {
+    SSI_DP_CASE(1)
+    SSI_DP_CASE(2)
+    SSI_DP_CASE(3)
+    SSI_DP_CASE(4)
+    SSI_DP_CASE(5)
+    SSI_DP_CASE(6)
+    SSI_DP_CASE(7)
+    SSI_DP_CASE(8)
+    default:
+      return fail(-1, "unsupported world size %d", world);
+  }
+#undef SSI_DP_CASE
   return 0;
 }
 

@@ -24,7 +24,7 @@ struct DevPlan {
   int k_blocks_tok;      // K2b: K loop over tokens = tiles_m * 2 (64-row blocks)
   int part_stride;       // K1 partial arrays: floats per split = tiles_m * 128
   int row0;              // first compact row of this plan (0 for the whole-problem plan; chunk plans: chunk start)
-  int pad1;
+  int first;             // chunk plans: 1 = first non-empty round (its dW contraction overwrites dW_acc, later ones add)
 };
 constexpr int MAX_ROW_CHUNKS = 120;  // plan area = (1 + MAX_ROW_CHUNKS) DevPlans (single-pass mode)
 constexpr int PLAN_AREA_BYTES = 4096;
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
     d.k_blocks_tok = d.tiles_m * 2;
     d.part_stride = d.tiles_m * 128;
     choose_splits(d.tiles_m, vtiles_total, sms, cg, d.splits, d.vtiles_per_split);
-    d.row0 = d.pad1 = 0;
+    d.row0 = d.first = 0;
     *plan = d;
     if (n_valid_out) *n_valid_out = n_valid;
     // Single-pass mode: m-tiles per row chunk.  The dX contraction of a chunk has t * d_tiles output tiles on
@@ -127,18 +127,24 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
   }
   if (chunks_max > 0) {
     __syncthreads();
-    const int t = s_chunk_t;
+    const int t = max(s_chunk_t, 1);
     const int tiles_all = (n_valid + 127) / 128;
+    // The host launches `chunks_max` rounds; the real chunks occupy the LAST rounds (the empty ones come first),
+    // so that the final round's dW contraction is always the last work on dW_acc (the caller's "dW ready" event
+    // is recorded right after it).  With no valid row at all the final round still zero-fills dW_acc.
+    const int nch = max((tiles_all + t - 1) / t, 1);
+    const int lead = max(chunks_max - nch, 0);
     for (int c = threadIdx.x; c < chunks_max; c += 1024) {
       DevPlan d;
-      const int m0 = min(c * t, tiles_all);
+      const int cc = c - lead;
+      const int m0 = (cc < 0) ? tiles_all : min(cc * t, tiles_all);
       d.tiles_m = min(t, tiles_all - m0);
-      d.row0 = m0 * 128;
-      d.n_valid = max(0, min(n_valid - d.row0, d.tiles_m * 128));
+      d.row0 = (cc < 0) ? 0 : m0 * 128;
+      d.n_valid = max(0, min(n_valid - m0 * 128, d.tiles_m * 128));
       d.k_blocks_tok = d.tiles_m * 2;
       d.part_stride = d.tiles_m * 128;
       choose_splits(d.tiles_m, vtiles_total, sms, cg, d.splits, d.vtiles_per_split);
-      d.pad1 = 0;
+      d.first = (cc == 0) ? 1 : 0;
       plan[1 + c] = d;
     }
   }
@@ -638,10 +644,26 @@ __device__ __forceinline__ void rmw_row(__nv_bfloat16* __restrict__ dst, int dco
   }
 }
 
+// fp32 destination (data-parallel mode adds the embedding gradient to the fp32 dW sum before the exchange)
+__device__ __forceinline__ void rmw_row(float* __restrict__ dst, int dcols, uint32_t lane, const float (&acc)[8][8]) {
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    const int col = g * 256 + lane * 8;
+    if (col < dcols) {
+      float4* ptr = reinterpret_cast<float4*>(dst + col);
+      float4 a = ptr[0], b = ptr[1];
+      a.x += acc[g][0], a.y += acc[g][1], a.z += acc[g][2], a.w += acc[g][3];
+      b.x += acc[g][4], b.y += acc[g][5], b.z += acc[g][6], b.w += acc[g][7];
+      ptr[0] = a, ptr[1] = b;
+    }
+  }
+}
+
+template <typename OutT>
 __global__ void __launch_bounds__(256) scatter_reduce_kernel(const __nv_bfloat16* __restrict__ dH,
                                                              const uint32_t* __restrict__ skeys,
                                                              const uint32_t* __restrict__ srows, int n, uint32_t V,
-                                                             int D, __nv_bfloat16* __restrict__ dW,
+                                                             int D, OutT* __restrict__ dW,
                                                              float* __restrict__ partial,
                                                              ScatInfo* __restrict__ info) {
   const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -721,9 +743,10 @@ __global__ void __launch_bounds__(256) scatter_reduce_kernel(const __nv_bfloat16
 }
 
 // One warp per range whose last run continues into the next range(s): sum the chain of partials in order.
+template <typename OutT>
 __global__ void __launch_bounds__(256) scatter_fixup_kernel(const float* __restrict__ partial,
                                                             const ScatInfo* __restrict__ info, int nwarps, uint32_t V,
-                                                            int D, __nv_bfloat16* __restrict__ dW) {
+                                                            int D, OutT* __restrict__ dW) {
   const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint32_t lane = threadIdx.x & 31;
   if (wg >= nwarps) return;

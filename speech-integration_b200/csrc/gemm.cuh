@@ -65,6 +65,7 @@ struct GemmParams {
   int tiles_m, tiles_n, k_blocks, group_m;
   int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
+  int c_reduce_plan;  // 1 = take it from the chunk plan instead: reduce-add unless dplan->first
   unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
   unsigned long long a_policy, b_policy;  // L2 cache policy of the A / B operand loads (0 = default)
   // Lockstep throttle (EPI_BF16 / EPI_F32 only, uniform K loops): every `sync_every` k-blocks the producers of
@@ -102,6 +103,7 @@ struct TileItem {
 struct Sched {
   int tiles_m, tiles_n, group_m, k_blocks, vtiles_per_split, vtiles_total, part_stride;
   int a_row_off, b_k_off, c_row_off, label_off;
+  int c_reduce;
 };
 
 template <int EPI>
@@ -110,7 +112,9 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
   s.tiles_m = p.tiles_m, s.tiles_n = p.tiles_n, s.group_m = p.group_m, s.k_blocks = p.k_blocks;
   s.vtiles_per_split = p.vtiles_per_split, s.vtiles_total = p.vtiles_total, s.part_stride = p.part_stride;
   s.a_row_off = s.b_k_off = s.c_row_off = s.label_off = 0;
+  s.c_reduce = p.c_reduce;
   if (p.dplan != nullptr) {
+    if (p.c_reduce_plan) s.c_reduce = (p.dplan->first == 0) ? 1 : 0;
     const int row0 = p.dplan->row0;
     if (p.plan_rows & PR_A_ROWS) s.a_row_off = row0;
     if (p.plan_rows & PR_B_K) s.b_k_off = row0;
@@ -128,7 +132,7 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
     if (p.k_from_plan) s.k_blocks = p.dplan->k_blocks_tok;
   }
   // accumulating an empty contraction (an empty row chunk) is a no-op
-  if (s.k_blocks == 0 && p.c_reduce) s.tiles_m = 0;
+  if (s.k_blocks == 0 && s.c_reduce) s.tiles_m = 0;
   return s;
 }
 
@@ -585,7 +589,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
               const int cc = p.c_c0 + nt * BNW + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
-              if (p.c_reduce)
+              if (sc.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
                 tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
@@ -618,7 +622,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
               const int cc = p.c_c0 + nt * BNW + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
-              if (p.c_reduce)
+              if (sc.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
                 tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);

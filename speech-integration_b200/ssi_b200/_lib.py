@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 101
+ABI_VERSION = 102
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -40,6 +40,11 @@ SYMBOLS = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
+    "ssi_b200_lmhead_ce_fwd_grad_ev": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
+    ),
     "ssi_b200_lmhead_ce_apply_grad": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p],
@@ -47,6 +52,20 @@ SYMBOLS = {
     "ssi_b200_embedding_grad_scatter": (
         c_int,
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_embedding_grad_scatter_f32": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_dp_buffer_bytes": (c_int, [c_int64, c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t)]),
+    "ssi_b200_dp_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),
+    "ssi_b200_dp_open": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "ssi_b200_dp_close": (c_int, [c_void_p]),
+    "ssi_b200_dp_free": (c_int, [c_void_p]),
+    "ssi_b200_dp_exchange": (
+        c_int,
+        [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_int,
+         c_void_p],
     ),
     "ssi_b200_label_shift_count": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "ssi_b200_profile_begin": (c_int, []),
@@ -118,7 +137,7 @@ def launch_count() -> int:
     return int(load().ssi_b200_launch_count())
 
 
-PROFILE_CLASSES = ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux", "softmax_grad", "_7")
+PROFILE_CLASSES = ("lse_fwd", "dlogits", "dW", "dX", "scatter", "aux", "softmax_grad", "exchange")
 
 
 def profile_begin() -> None:
@@ -130,7 +149,7 @@ def profile_end() -> dict[str, tuple[float, int]]:
     ms = (ctypes.c_double * 8)()
     cnt = (ctypes.c_int64 * 8)()
     check(load().ssi_b200_profile_end(ctypes.cast(ms, c_void_p), ctypes.cast(cnt, c_void_p)), "profile_end")
-    return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(7)}
+    return {PROFILE_CLASSES[i]: (float(ms[i]), int(cnt[i])) for i in range(8)}
 
 
 def plan_info(N: int, V: int, D: int) -> dict[str, int]:

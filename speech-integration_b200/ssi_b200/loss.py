@@ -81,8 +81,9 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         ctx.with_grad = bool(ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
         if ctx.with_grad:
             hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
-            loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(X, W, labels, hint, n_valid_override,
-                                                                        ignore_index)
+            loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(
+                X, W, labels, hint, n_valid_override, ignore_index,
+                dW_acc=getattr(holder, "dw_acc_buffer", None), dw_ready_event=getattr(holder, "dw_ready_event", None))
             ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
         else:
             loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
@@ -102,6 +103,13 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         dX, dW_acc, hint = ctx.dX, ctx.dW_acc, ctx.hint
         ctx.dX = ctx.dW_acc = None
         wparam = holder.weight_param() if holder is not None else None
+        if holder is not None and getattr(holder, "defer_dw", False):
+            # data-parallel peer exchange (ssi_b200.peer / PathStep): the SUMMED fp32 dW is rounded into .grad by
+            # the exchange, which already runs behind the last dX contraction with the announced multiplier;
+            # here only dX is rescaled, and a wrong announcement is left visible instead of silently ignored.
+            ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
+            holder.grad_hint_mismatch = (g != hint)
+            return dX, None, None, None, None, None, None
         if wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr:
             acc = wparam.grad is not None
             if not acc:
@@ -167,6 +175,12 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         self.n_valid_total: torch.Tensor | None = None  # set by ssi_b200.dist for data parallelism
         self.last_loss_sum: torch.Tensor | None = None
         self.last_n_valid: torch.Tensor | None = None
+        # data-parallel peer exchange hooks (set by ssi_b200.step.PathStep): the fp32 accumulator to write into,
+        # the event to record once it is final, and "leave dW to the exchange" for backward
+        self.dw_acc_buffer: torch.Tensor | None = None
+        self.dw_ready_event: torch.cuda.Event | None = None
+        self.defer_dw: bool = False
+        self.grad_hint_mismatch: torch.Tensor | None = None
 
     @property
     def tied_module(self) -> nn.Module:

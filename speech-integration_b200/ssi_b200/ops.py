@@ -113,11 +113,15 @@ def lmhead_ce_bwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, lse: t
 
 
 def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, grad_hint: torch.Tensor,
-                       n_valid_total: torch.Tensor | None = None, ignore_index: int = -100):
+                       n_valid_total: torch.Tensor | None = None, ignore_index: int = -100,
+                       dW_acc: torch.Tensor | None = None, dw_ready_event: torch.cuda.Event | None = None):
     """Single-pass mode: fused projection + CE forward that also forms the gradients (each logits tile is
     computed once). Returns ``(loss_out, lse, n_valid, dX, dW_acc)``; ``dX`` bf16 ``[N, D]`` and ``dW_acc`` fp32
     ``[V, D]`` are the gradients for an upstream gradient of ``grad_hint`` (fp32 device scalar);
     :func:`lmhead_ce_apply_grad` rescales them for the gradient autograd actually delivers.
+
+    ``dW_acc``: optional existing fp32 ``[V, D]`` buffer to write into (data-parallel mode passes the view of its
+    peer-visible exchange buffer); ``dw_ready_event``: recorded right after the last dW contraction.
     """
     dev = _require_cuda(X, W, labels, grad_hint)
     N, V, D = _check_xw(X, W)
@@ -134,24 +138,40 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     loss_out = torch.empty(2, dtype=torch.float32, device=dev)
     n_valid = torch.empty(1, dtype=torch.int64, device=dev)
     dX = torch.empty_like(X)
-    dW_acc = torch.empty(V, D, dtype=torch.float32, device=dev)
+    if dW_acc is None:
+        dW_acc = torch.empty(V, D, dtype=torch.float32, device=dev)
+    elif (tuple(dW_acc.shape) != (V, D) or dW_acc.dtype != torch.float32 or not dW_acc.is_contiguous()
+          or dW_acc.device != dev):
+        raise ValueError("ssi_b200: dW_acc must be a contiguous fp32 [V, D] tensor on the same device")
+    ev = None
+    if dw_ready_event is not None:
+        ev = dw_ready_event.cuda_event
+        if not ev:
+            raise ValueError("ssi_b200: dw_ready_event has no CUDA handle yet (record it once before first use)")
     with torch.cuda.device(dev):
-        rc = lib.ssi_b200_lmhead_ce_fwd_grad(
+        rc = lib.ssi_b200_lmhead_ce_fwd_grad_ev(
             X.data_ptr(), W.data_ptr(), labels.data_ptr(), grad_hint.data_ptr(),
             n_valid_total.data_ptr() if n_valid_total is not None else None, N, V, D, int(ignore_index),
             lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), dX.data_ptr(), dW_acc.data_ptr(),
-            ws.data_ptr(), ws.numel(), _stream(dev))
+            ws.data_ptr(), ws.numel(), _stream(dev), ev)
     _lib.check(rc, "lmhead_ce_fwd_grad")
     return loss_out, lse, n_valid, dX, dW_acc
 
 
 def lmhead_ce_apply_grad(dX: torch.Tensor, dW_acc: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
-                         dW: torch.Tensor | None = None, accumulate_dW: bool = False):
+                         dW: torch.Tensor | None = None, accumulate_dW: bool = False, skip_dW: bool = False):
     """Backward of single-pass mode: ``dX *= grad_out / grad_hint`` in place (a no-op on the device when the
-    ratio is 1) and ``dW = bf16((accumulate ? dW : 0) + ratio * dW_acc)``. Returns ``(dX, dW)``."""
+    ratio is 1) and ``dW = bf16((accumulate ? dW : 0) + ratio * dW_acc)``. Returns ``(dX, dW)``.
+    ``skip_dW``: only rescale dX (data-parallel mode: the peer exchange rounds the SUMMED dW instead)."""
     dev = _require_cuda(dX, dW_acc, grad_out, grad_hint)
     N, D = dX.shape
     V = dW_acc.size(0)
+    if skip_dW:
+        with torch.cuda.device(dev):
+            rc = _lib.load().ssi_b200_lmhead_ce_apply_grad(dX.data_ptr(), dW_acc.data_ptr(), grad_out.data_ptr(),
+                                                           grad_hint.data_ptr(), N, V, D, None, 0, _stream(dev))
+        _lib.check(rc, "lmhead_ce_apply_grad")
+        return dX, None
     if dW is None:
         if accumulate_dW:
             raise ValueError("ssi_b200: accumulate_dW needs an existing dW buffer")
@@ -192,6 +212,30 @@ def embedding_grad_scatter(dH: torch.Tensor, ids: torch.Tensor, dW: torch.Tensor
                                                  ws.data_ptr(), ws.numel(), _stream(dev))
     _lib.check(rc, "embedding_grad_scatter")
     return dW
+
+
+def embedding_grad_scatter_f32(dH: torch.Tensor, ids: torch.Tensor, dW_acc: torch.Tensor) -> torch.Tensor:
+    """``dW_acc[ids[i]] += dH[i]`` into an fp32 ``[V, D]`` buffer (data-parallel mode: the embedding gradient joins
+    the fp32 LM-head sum before the peer exchange, so the tied gradient is rounded to bf16 once)."""
+    dev = _require_cuda(dH, ids, dW_acc)
+    if dH.dtype != torch.bfloat16 or dW_acc.dtype != torch.float32:
+        raise TypeError("ssi_b200: dH must be bfloat16 and dW_acc float32")
+    if dH.dim() != 2 or dW_acc.dim() != 2 or dH.size(1) != dW_acc.size(1):
+        raise ValueError("ssi_b200: expected dH [N, D] and dW_acc [V, D]")
+    if ids.dtype != torch.int64 or ids.numel() != dH.size(0):
+        raise ValueError("ssi_b200: ids must be int64 with one entry per row of dH")
+    if not (dH.is_contiguous() and dW_acc.is_contiguous() and ids.is_contiguous()):
+        raise ValueError("ssi_b200: dH, ids and dW_acc must be contiguous")
+    N, D = dH.shape
+    V = dW_acc.size(0)
+    lib = _lib.load()
+    _, _, sc_b = _lib.workspace_bytes(N, V, D, "scatter")
+    ws = _workspace("scatter", sc_b, dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_embedding_grad_scatter_f32(dH.data_ptr(), ids.data_ptr(), N, V, D, dW_acc.data_ptr(),
+                                                     ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "embedding_grad_scatter_f32")
+    return dW_acc
 
 
 def label_shift_count(labels: torch.Tensor, ignore_index: int = -100):

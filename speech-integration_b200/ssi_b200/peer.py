@@ -1,0 +1,115 @@
+"""Peer-memory exchange of the tied LM-head / embedding gradient for one process per GPU on one
+NVSwitch node.
+
+Each rank owns one exchange buffer (ctrl flags | fp32 ``dW_acc [V, D]`` | bf16 stage slice) allocated by the
+library and mapped into every peer through CUDA IPC (``ssi_b200_dp_alloc`` / ``ssi_b200_dp_open``); the handles
+travel through ``torch.distributed`` (any backend: NCCL on the GPUs, gloo in tests).  ``exchange()`` enqueues the
+two kernels of ``csrc/dp_exchange.cuh``: rank r sums vocabulary slice r of all ranks' fp32 ``dW_acc`` over NVLink
+P2P loads in rank order, rounds ONCE to bf16, and every rank then pulls the finished slices — the result is
+bit-identical on every rank and run to run, and the whole exchange co-resides with the tensor-core CTAs of the
+last dX contraction (no shared memory), so it hides behind math instead of following it.
+
+There is no reference counterpart (the reference trains on one GPU); semantics are those of torchtune's
+distributed recipe (tt/recipes/full_finetune_distributed.py:844-851,867): gradients of the global mean.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+MAX_WORLD = 8
+
+
+class _DevicePtr:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can view library-owned device memory."""
+
+    def __init__(self, ptr: int, shape: tuple[int, ...], typestr: str):
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False), "version": 3,
+                                         "strides": None}
+
+
+class TiedGradExchange:
+    """Owns this rank's exchange buffer and the mappings of its peers' buffers.
+
+    Attributes:
+        dw_acc: fp32 ``[V, D]`` tensor view of the peer-visible accumulator; hand it to the single-pass forward
+            (``FusedLinearCrossEntropyLoss.dw_acc_buffer``) and to ``ops.embedding_grad_scatter_f32``.
+    """
+
+    def __init__(self, V: int, D: int, group=None, device: torch.device | None = None):
+        if not dist.is_initialized():
+            raise RuntimeError("ssi_b200.peer: torch.distributed is not initialised")
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+        if self.world > MAX_WORLD:
+            raise RuntimeError(f"ssi_b200.peer: world size {self.world} > {MAX_WORLD} (one NVSwitch node)")
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self.V, self.D = int(V), int(D)
+        self.epoch = 0
+        lib = _lib.load()
+        nbytes, off = ctypes.c_size_t(0), ctypes.c_size_t(0)
+        _lib.check(lib.ssi_b200_dp_buffer_bytes(self.V, self.D, self.world, ctypes.byref(nbytes), ctypes.byref(off)),
+                   "dp_buffer_bytes")
+        self.nbytes, self._acc_off = nbytes.value, off.value
+        own = ctypes.c_void_p(0)
+        handle = (ctypes.c_ubyte * 64)()
+        with torch.cuda.device(self.device):
+            _lib.check(lib.ssi_b200_dp_alloc(self.nbytes, ctypes.byref(own), ctypes.cast(handle, ctypes.c_void_p)),
+                       "dp_alloc")
+        self._own = own.value
+        handles: list = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        self._peer_ptrs: list[int] = []
+        self._opened: list[int] = []
+        with torch.cuda.device(self.device):
+            for r in range(self.world):
+                if r == self.rank:
+                    self._peer_ptrs.append(self._own)
+                    continue
+                buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
+                p = ctypes.c_void_p(0)
+                _lib.check(lib.ssi_b200_dp_open(ctypes.cast(buf, ctypes.c_void_p), ctypes.byref(p)), "dp_open")
+                self._peer_ptrs.append(p.value)
+                self._opened.append(p.value)
+        self._ptr_array = (ctypes.c_void_p * self.world)(*self._peer_ptrs)
+        self.dw_acc = torch.as_tensor(_DevicePtr(self._own + self._acc_off, (self.V, self.D), "<f4"),
+                                      device=self.device)
+        # every rank must have mapped (and zero-initialised) its buffers before the first exchange touches them
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)
+
+    def exchange(self, dW: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
+                 accumulate: bool = False) -> torch.Tensor:
+        """Enqueue on the current stream: ``dW = bf16((accumulate ? dW : 0) + grad_out / grad_hint * sum_ranks
+        dw_acc)`` on every rank.  Every rank must call it the same number of times."""
+        if tuple(dW.shape) != (self.V, self.D) or dW.dtype != torch.bfloat16 or not dW.is_contiguous():
+            raise ValueError("ssi_b200.peer: dW must be a contiguous bf16 [V, D] tensor")
+        if dW.device != self.device:
+            raise ValueError("ssi_b200.peer: dW is on another device than the exchange buffer")
+        self.epoch += 1
+        with torch.cuda.device(self.device):
+            rc = _lib.load().ssi_b200_dp_exchange(self._ptr_array, self.rank, self.world, self.V, self.D,
+                                                  self.epoch & 0xFFFFFFFF, grad_out.data_ptr(), grad_hint.data_ptr(),
+                                                  dW.data_ptr(), 1 if accumulate else 0,
+                                                  torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(rc, "dp_exchange")
+        return dW
+
+    def close(self) -> None:
+        if self._own is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if dist.is_initialized():
+            dist.barrier(group=self.group)  # nobody may unmap while a peer can still read
+        lib = _lib.load()
+        self.dw_acc = None
+        with torch.cuda.device(self.device):
+            for p in self._opened:
+                lib.ssi_b200_dp_close(p)
+            lib.ssi_b200_dp_free(self._own)
+        self._opened, self._own = [], None

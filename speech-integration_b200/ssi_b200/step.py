@@ -21,8 +21,14 @@ from .loss import FusedLinearCrossEntropyLoss
 
 
 class PathStep:
+    """``exchange``: how the tied gradient is summed over ranks when a process group is given —
+    ``"peer"`` (default for single-pass mode): the library's own NVLink peer-memory reduce (ssi_b200.peer), started
+    on a side stream as soon as the last dW contraction is done, so it runs behind the last dX contraction;
+    the sum over ranks is taken in fp32 and rounded once.  ``"nccl"``: bf16 ``all_reduce`` after the step (the
+    plain baseline).  Environment override: ``SSI_B200_EXCHANGE``."""
+
     def __init__(self, weight: nn.Parameter | torch.Tensor, ignore_index: int = -100, num_output_chunks: int = 8,
-                 process_group=None, mode: str | None = None):
+                 process_group=None, mode: str | None = None, exchange: str | None = None):
         if not isinstance(weight, nn.Parameter):
             weight = nn.Parameter(weight)
         self.emb = nn.Embedding(weight.size(0), weight.size(1), device="meta", dtype=weight.dtype)
@@ -35,6 +41,28 @@ class PathStep:
             import torch.distributed as dist
 
             self.world = dist.get_world_size(process_group)
+        self.exchange = None
+        self.peer = None
+        if process_group is not None and (self.world > 1 or exchange == "peer"):
+            import os
+
+            self.exchange = exchange or os.environ.get("SSI_B200_EXCHANGE") or (
+                "peer" if self.loss_fn.mode == "single_pass" else "nccl")
+            if self.exchange not in ("peer", "nccl"):
+                raise ValueError(f"ssi_b200: unknown exchange {self.exchange!r} (expected 'peer' or 'nccl')")
+            if self.exchange == "peer":
+                if self.loss_fn.mode != "single_pass":
+                    raise ValueError("ssi_b200: exchange='peer' needs mode='single_pass'")
+                from .peer import TiedGradExchange
+
+                dev = weight.device
+                self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, dev)
+                self.side = torch.cuda.Stream(dev)
+                self.dw_ready = torch.cuda.Event()
+                self.dw_ready.record(torch.cuda.current_stream(dev))  # creates the CUDA handle
+                self.loss_fn.dw_acc_buffer = self.peer.dw_acc
+                self.loss_fn.dw_ready_event = self.dw_ready
+                self.loss_fn.defer_dw = True
 
     @property
     def weight(self) -> nn.Parameter:
@@ -71,11 +99,34 @@ class PathStep:
         self.loss_fn.grad_hint = n_iter.reshape(1)
         loss = self.loss_fn(hidden, shifted)
         loss_batch = loss * n_iter
-        loss_batch.backward()
         D = dH0.size(-1)
+        if self.peer is not None:
+            # The forward above recorded `dw_ready` right after the last dW contraction.  Side stream, behind the
+            # last dX contraction and the rest of the main stream: embedding gradient into the fp32 sum, then the
+            # peer reduce (fp32 over ranks, one rounding) straight into .grad.
+            main = torch.cuda.current_stream(hidden.device)
+            accumulate = self.weight.grad is not None
+            if not accumulate:
+                self.weight.grad = torch.empty_like(self.weight)
+            hint = self.loss_fn.grad_hint
+            self.side.wait_event(self.dw_ready)
+            with torch.cuda.stream(self.side):
+                ops.embedding_grad_scatter_f32(dH0.reshape(-1, D), tokens.reshape(-1), self.peer.dw_acc)
+                self.peer.exchange(self.weight.grad, hint, hint, accumulate=accumulate)
+            loss_batch.backward()  # dX rescale only (a device-side no-op: the multiplier was announced)
+            main.wait_stream(self.side)
+            return loss_batch.detach(), hidden.grad, counts
+        loss_batch.backward()
         ops.embedding_grad_scatter(dH0.reshape(-1, D), tokens.reshape(-1), self.weight.grad)
         if self.world > 1:
             from . import dist as ddist
 
             ddist.allreduce_tied_grad(self.weight.grad, self.pg)
         return loss_batch.detach(), hidden.grad, counts
+
+    def close(self) -> None:
+        """Release the peer exchange buffers (collective: every rank must call it)."""
+        if self.peer is not None:
+            self.loss_fn.dw_acc_buffer = None
+            self.peer.close()
+            self.peer = None
