@@ -113,13 +113,19 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
                                 int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                 float* dW_acc, void* ws, size_t ws_bytes, void* stream);
 
-/* Same, plus `dw_ready_event` (a cudaEvent_t, may be NULL): recorded on `stream` right after the LAST dW
- * contraction, i.e. as soon as dW_acc is final and while the last dX contraction is still to run, so that a
- * caller can start the data-parallel exchange of the tied gradient on another stream behind it. */
-int ssi_b200_lmhead_ce_fwd_grad_ev(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+/* Data-parallel variant of the above (see ssi_b200_dp_* below), three extra arguments:
+ *   accumulate_dW_acc  != 0: the caller initialised dW_acc (e.g. zeros + the embedding scatter-add) and every
+ *                      dW contraction ADDS to it; 0: the first one overwrites it as above
+ *   dw_acc_init_event  cudaEvent_t or NULL: `stream` waits for it right before the first dW contraction (the
+ *                      initialisation may run on another stream beside the first logits contraction)
+ *   dw_ready_event     cudaEvent_t or NULL: recorded on `stream` right after the LAST dW contraction, i.e. as soon
+ *                      as dW_acc is final and while the last dX contraction is still to run, so that the exchange
+ *                      of the tied gradient can start on another stream behind it. */
+int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
                                    const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
                                    int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
-                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, void* dw_ready_event);
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
+                                   void* dw_acc_init_event, void* dw_ready_event);
 
 /*
  * Backward of single-pass mode: ratio = grad_out / grad_hint (exactly 1 when the hint was right);
@@ -143,6 +149,13 @@ int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t 
  * dW_acc of single-pass mode before the exchange, so the summed tied gradient is rounded to bf16 exactly once). */
 int ssi_b200_embedding_grad_scatter_f32(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
                                         float* dW_acc, void* ws, size_t ws_bytes, void* stream);
+/* The two halves of the above as separate calls sharing `ws`: the radix sort of the ids (needs only the token ids,
+ * its kernels use shared memory) can run at the start of the step, so that the reduction (no shared memory) can
+ * later co-run with a tensor-core contraction on another stream.  Same N, V, D and workspace in both calls. */
+int ssi_b200_embedding_grad_sort(const int64_t* ids, int64_t N, int64_t V, int64_t D, void* ws, size_t ws_bytes,
+                                 void* stream);
+int ssi_b200_embedding_grad_scatter_sorted_f32(const void* dH, int64_t N, int64_t V, int64_t D, float* dW_acc,
+                                               void* ws, size_t ws_bytes, void* stream);
 
 /*
  * Data-parallel exchange of the tied LM-head / embedding gradient over NVLink peer memory (one process per GPU,

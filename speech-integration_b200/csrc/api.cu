@@ -658,14 +658,15 @@ int ssi_b200_lmhead_ce_fwd_grad(const void* X, const void* W, const int64_t* lab
                                 const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
                                 int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                 float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
-  return ssi_b200_lmhead_ce_fwd_grad_ev(X, W, labels, grad_hint, n_valid_total, N, V, D, ignore_index, lse, loss_out,
-                                        n_valid, dX, dW_acc, ws, ws_bytes, stream, nullptr);
+  return ssi_b200_lmhead_ce_fwd_grad_dp(X, W, labels, grad_hint, n_valid_total, N, V, D, ignore_index, lse, loss_out,
+                                        n_valid, dX, dW_acc, ws, ws_bytes, stream, 0, nullptr, nullptr);
 }
 
-int ssi_b200_lmhead_ce_fwd_grad_ev(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
                                    const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
                                    int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
-                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, void* dw_ready_event) {
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
+                                   void* dw_acc_init_event, void* dw_ready_event) {
   if (int r = check_common(X, W, N, V, D)) return r;
   SSI_CHECK_ARG(labels && grad_hint && lse && loss_out && n_valid && dX && dW_acc && ws, "null pointer argument");
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0,
@@ -768,7 +769,10 @@ int ssi_b200_lmhead_ce_fwd_grad_ev(const void* X, const void* W, const int64_t* 
       p.tiles_n = d_tiles;
       p.k_blocks = static_cast<int>(rows_cap / ssi::BK);
       p.group_m = tune().group_m_dw;
-      p.c_reduce = 0, p.c_reduce_plan = 1;  // the first NON-EMPTY round overwrites dW_acc, later rounds add
+      // the first NON-EMPTY round overwrites dW_acc and later rounds add -- or all add when the caller initialised it
+      p.c_reduce = accumulate_dW_acc ? 1 : 0, p.c_reduce_plan = accumulate_dW_acc ? 0 : 1;
+      if (ch == 0 && dw_acc_init_event)
+        SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(dw_acc_init_event), 0));
       set_hints(p, tune().dw_hints);
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
@@ -835,8 +839,9 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
 namespace {
 template <typename OutT>
 int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, OutT* dW,
-                                void* ws, size_t ws_bytes, void* stream) {
-  SSI_CHECK_ARG(dH && ids && dW && ws, "null pointer argument");
+                                void* ws, size_t ws_bytes, void* stream, int phases = 3) {
+  // phases: bit 0 = sort the ids (leaves the order in ws), bit 1 = segmented reduction of dH rows in that order
+  SSI_CHECK_ARG(ws && (!(phases & 1) || ids) && (!(phases & 2) || (dH && dW)), "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
   SSI_CHECK_ARG(N < (int64_t(1) << 31) && V < (int64_t(1) << 31), "N/V too large");
@@ -854,10 +859,16 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
   const int n = static_cast<int>(N);
 
   ProfScope ps_scat(CAT_SCATTER, st);
-  ssi::sort_prepare_kernel<<<static_cast<int>(ceil_div(N, 256)), 256, 0, st>>>(ids, n, V, k[0], v[0]);
-  SSI_LAUNCH_OK("sort_prepare");
+  if (phases & 1) {
+    ssi::sort_prepare_kernel<<<static_cast<int>(ceil_div(N, 256)), 256, 0, st>>>(ids, n, V, k[0], v[0]);
+    SSI_LAUNCH_OK("sort_prepare");
+  }
   int cur = 0;
   for (int pass = 0; pass < s.passes; ++pass) {
+    if (!(phases & 1)) {
+      cur ^= 1;
+      continue;
+    }
     const int shift = pass * 8;
     ssi::sort_hist_kernel<<<s.blocks, ssi::SORT_THREADS, 0, st>>>(k[cur], n, shift, hist, s.blocks);
     SSI_LAUNCH_OK("sort_hist");
@@ -868,6 +879,7 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
     SSI_LAUNCH_OK("sort_scatter");
     cur ^= 1;
   }
+  if (!(phases & 2)) return 0;
   float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
   ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
   const int grid = static_cast<int>(ceil_div(s.nwarps, 8));
@@ -890,6 +902,16 @@ int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t 
 int ssi_b200_embedding_grad_scatter_f32(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
                                         float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
   return embedding_grad_scatter_impl(dH, ids, N, V, D, dW_acc, ws, ws_bytes, stream);
+}
+
+int ssi_b200_embedding_grad_sort(const int64_t* ids, int64_t N, int64_t V, int64_t D, void* ws, size_t ws_bytes,
+                                 void* stream) {
+  return embedding_grad_scatter_impl<float>(nullptr, ids, N, V, D, nullptr, ws, ws_bytes, stream, 1);
+}
+
+int ssi_b200_embedding_grad_scatter_sorted_f32(const void* dH, int64_t N, int64_t V, int64_t D, float* dW_acc,
+                                               void* ws, size_t ws_bytes, void* stream) {
+  return embedding_grad_scatter_impl<float>(dH, nullptr, N, V, D, dW_acc, ws, ws_bytes, stream, 2);
 }
 
 // ---------------------------------------------------------------------------------------------------

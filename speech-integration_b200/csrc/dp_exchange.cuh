@@ -49,20 +49,20 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
   return v;
 }
+// Peer data is read exactly once per launch and only after the acquire on the peer's flag, and L1 is invalidated
+// at every launch boundary, so plain (weak) vector loads are safe; L1::no_allocate keeps the stream out of L1.
 __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {
   float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+  asm volatile("ld.global.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];"
                : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
-               : "l"(p)
-               : "memory");
+               : "l"(p));
   return v;
 }
 __device__ __forceinline__ uint4 ld_peer_u4(const uint4* p) {
   uint4 v;
-  asm volatile("ld.relaxed.sys.global.v4.u32 {%0, %1, %2, %3}, [%4];"
+  asm volatile("ld.global.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];"
                : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(p)
-               : "memory");
+               : "l"(p));
   return v;
 }
 

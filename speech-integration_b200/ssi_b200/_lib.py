@@ -40,10 +40,10 @@ SYMBOLS = {
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
-    "ssi_b200_lmhead_ce_fwd_grad_ev": (
+    "ssi_b200_lmhead_ce_fwd_grad_dp": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
-         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_void_p, c_void_p],
     ),
     "ssi_b200_lmhead_ce_apply_grad": (
         c_int,
@@ -56,6 +56,11 @@ SYMBOLS = {
     "ssi_b200_embedding_grad_scatter_f32": (
         c_int,
         [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_embedding_grad_sort": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, c_void_p]),
+    "ssi_b200_embedding_grad_scatter_sorted_f32": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
     "ssi_b200_dp_buffer_bytes": (c_int, [c_int64, c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t)]),
     "ssi_b200_dp_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),

@@ -83,7 +83,9 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
             hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
             loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(
                 X, W, labels, hint, n_valid_override, ignore_index,
-                dW_acc=getattr(holder, "dw_acc_buffer", None), dw_ready_event=getattr(holder, "dw_ready_event", None))
+                dW_acc=getattr(holder, "dw_acc_buffer", None), dw_ready_event=getattr(holder, "dw_ready_event", None),
+                accumulate_dW_acc=getattr(holder, "dw_acc_initialised", False),
+                dw_acc_init_event=getattr(holder, "dw_acc_init_event", None))
             ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
         else:
             loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
@@ -179,6 +181,8 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         # the event to record once it is final, and "leave dW to the exchange" for backward
         self.dw_acc_buffer: torch.Tensor | None = None
         self.dw_ready_event: torch.cuda.Event | None = None
+        self.dw_acc_initialised: bool = False  # the caller pre-fills dw_acc_buffer (embedding gradient) every step
+        self.dw_acc_init_event: torch.cuda.Event | None = None
         self.defer_dw: bool = False
         self.grad_hint_mismatch: torch.Tensor | None = None
 

@@ -114,14 +114,17 @@ def lmhead_ce_bwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, lse: t
 
 def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, grad_hint: torch.Tensor,
                        n_valid_total: torch.Tensor | None = None, ignore_index: int = -100,
-                       dW_acc: torch.Tensor | None = None, dw_ready_event: torch.cuda.Event | None = None):
+                       dW_acc: torch.Tensor | None = None, dw_ready_event: torch.cuda.Event | None = None,
+                       accumulate_dW_acc: bool = False, dw_acc_init_event: torch.cuda.Event | None = None):
     """Single-pass mode: fused projection + CE forward that also forms the gradients (each logits tile is
     computed once). Returns ``(loss_out, lse, n_valid, dX, dW_acc)``; ``dX`` bf16 ``[N, D]`` and ``dW_acc`` fp32
     ``[V, D]`` are the gradients for an upstream gradient of ``grad_hint`` (fp32 device scalar);
     :func:`lmhead_ce_apply_grad` rescales them for the gradient autograd actually delivers.
 
     ``dW_acc``: optional existing fp32 ``[V, D]`` buffer to write into (data-parallel mode passes the view of its
-    peer-visible exchange buffer); ``dw_ready_event``: recorded right after the last dW contraction.
+    peer-visible exchange buffer); ``dw_ready_event``: recorded right after the last dW contraction;
+    ``accumulate_dW_acc``: the caller initialised ``dW_acc`` and every dW contraction adds to it;
+    ``dw_acc_init_event``: the stream waits for it right before the first dW contraction.
     """
     dev = _require_cuda(X, W, labels, grad_hint)
     N, V, D = _check_xw(X, W)
@@ -143,17 +146,22 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     elif (tuple(dW_acc.shape) != (V, D) or dW_acc.dtype != torch.float32 or not dW_acc.is_contiguous()
           or dW_acc.device != dev):
         raise ValueError("ssi_b200: dW_acc must be a contiguous fp32 [V, D] tensor on the same device")
-    ev = None
-    if dw_ready_event is not None:
-        ev = dw_ready_event.cuda_event
-        if not ev:
-            raise ValueError("ssi_b200: dw_ready_event has no CUDA handle yet (record it once before first use)")
+    if accumulate_dW_acc and dW_acc is None:
+        raise ValueError("ssi_b200: accumulate_dW_acc needs an initialised dW_acc buffer")
+    evs = []
+    for e in (dw_acc_init_event, dw_ready_event):
+        h = None
+        if e is not None:
+            h = e.cuda_event
+            if not h:
+                raise ValueError("ssi_b200: event has no CUDA handle yet (record it once before first use)")
+        evs.append(h)
     with torch.cuda.device(dev):
-        rc = lib.ssi_b200_lmhead_ce_fwd_grad_ev(
+        rc = lib.ssi_b200_lmhead_ce_fwd_grad_dp(
             X.data_ptr(), W.data_ptr(), labels.data_ptr(), grad_hint.data_ptr(),
             n_valid_total.data_ptr() if n_valid_total is not None else None, N, V, D, int(ignore_index),
             lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), dX.data_ptr(), dW_acc.data_ptr(),
-            ws.data_ptr(), ws.numel(), _stream(dev), ev)
+            ws.data_ptr(), ws.numel(), _stream(dev), 1 if accumulate_dW_acc else 0, evs[0], evs[1])
     _lib.check(rc, "lmhead_ce_fwd_grad")
     return loss_out, lse, n_valid, dX, dW_acc
 
@@ -235,6 +243,40 @@ def embedding_grad_scatter_f32(dH: torch.Tensor, ids: torch.Tensor, dW_acc: torc
         rc = lib.ssi_b200_embedding_grad_scatter_f32(dH.data_ptr(), ids.data_ptr(), N, V, D, dW_acc.data_ptr(),
                                                      ws.data_ptr(), ws.numel(), _stream(dev))
     _lib.check(rc, "embedding_grad_scatter_f32")
+    return dW_acc
+
+
+def embedding_grad_sort(ids: torch.Tensor, V: int, D: int) -> torch.Tensor:
+    """First half of :func:`embedding_grad_scatter_f32`: radix-sort the token ids on the current stream. Returns
+    the workspace holding the order; pass it to :func:`embedding_grad_scatter_sorted_f32` (any stream that is
+    ordered after this call)."""
+    dev = _require_cuda(ids)
+    if ids.dtype != torch.int64 or not ids.is_contiguous():
+        raise ValueError("ssi_b200: ids must be contiguous int64")
+    N = ids.numel()
+    lib = _lib.load()
+    _, _, sc_b = _lib.workspace_bytes(N, V, D, "scatter")
+    ws = _workspace("scatter_sorted", sc_b, dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_embedding_grad_sort(ids.data_ptr(), N, V, D, ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "embedding_grad_sort")
+    return ws
+
+
+def embedding_grad_scatter_sorted_f32(dH: torch.Tensor, ws: torch.Tensor, dW_acc: torch.Tensor) -> torch.Tensor:
+    """Second half: ``dW_acc[id] += sum of the dH rows with that id`` in the order :func:`embedding_grad_sort`
+    left in ``ws`` (no shared memory: co-runs with a tensor-core contraction on another stream)."""
+    dev = _require_cuda(dH, ws, dW_acc)
+    if dH.dtype != torch.bfloat16 or dW_acc.dtype != torch.float32 or dH.dim() != 2 or dW_acc.dim() != 2:
+        raise TypeError("ssi_b200: expected bf16 dH [N, D] and fp32 dW_acc [V, D]")
+    if dH.size(1) != dW_acc.size(1) or not (dH.is_contiguous() and dW_acc.is_contiguous()):
+        raise ValueError("ssi_b200: dH and dW_acc must be contiguous with the same row length")
+    N, D = dH.shape
+    V = dW_acc.size(0)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_embedding_grad_scatter_sorted_f32(dH.data_ptr(), N, V, D, dW_acc.data_ptr(),
+                                                                    ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "embedding_grad_scatter_sorted_f32")
     return dW_acc
 
 

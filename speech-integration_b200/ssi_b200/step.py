@@ -57,11 +57,16 @@ class PathStep:
 
                 dev = weight.device
                 self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, dev)
-                self.side = torch.cuda.Stream(dev)
-                self.dw_ready = torch.cuda.Event()
-                self.dw_ready.record(torch.cuda.current_stream(dev))  # creates the CUDA handle
+                # SSI_B200_PEER_SERIAL=1 (diagnostics): run the exchange on the main stream after the step instead
+                self.side = (torch.cuda.current_stream(dev) if os.environ.get("SSI_B200_PEER_SERIAL") == "1"
+                             else torch.cuda.Stream(dev))
+                self.dw_ready, self.dw_init, self.sorted = (torch.cuda.Event() for _ in range(3))
+                for e in (self.dw_ready, self.dw_init, self.sorted):
+                    e.record(torch.cuda.current_stream(dev))  # creates the CUDA handle
                 self.loss_fn.dw_acc_buffer = self.peer.dw_acc
                 self.loss_fn.dw_ready_event = self.dw_ready
+                self.loss_fn.dw_acc_initialised = True
+                self.loss_fn.dw_acc_init_event = self.dw_init
                 self.loss_fn.defer_dw = True
 
     @property
@@ -86,6 +91,19 @@ class PathStep:
         ``self.weight.grad`` holds LM-head + embedding gradient (all-reduced when a process group is set)."""
         shifted, counts = ops.label_shift_count(labels, self.ignore_index)
         hidden = hidden.detach().requires_grad_(True)
+        if self.peer is not None:
+            # Embedding gradient FIRST: sort the ids here, then on the side stream (beside the first logits
+            # contraction) dW_acc = 0 + scatter-add of dH0; every dW contraction then adds to it (the first one
+            # waits for `dw_init`), and the exchange is the only thing left for the tail of the step.
+            main = torch.cuda.current_stream(hidden.device)
+            D_ = dH0.size(-1)
+            sort_ws = ops.embedding_grad_sort(tokens.reshape(-1), self.weight.size(0), self.weight.size(1))
+            self.sorted.record(main)
+            self.side.wait_event(self.sorted)
+            with torch.cuda.stream(self.side):
+                self.peer.dw_acc.zero_()
+                ops.embedding_grad_scatter_sorted_f32(dH0.reshape(-1, D_), sort_ws, self.peer.dw_acc)
+                self.dw_init.record(self.side)
         gcounts = counts
         if self.world > 1:
             from . import dist as ddist
@@ -102,16 +120,14 @@ class PathStep:
         D = dH0.size(-1)
         if self.peer is not None:
             # The forward above recorded `dw_ready` right after the last dW contraction.  Side stream, behind the
-            # last dX contraction and the rest of the main stream: embedding gradient into the fp32 sum, then the
-            # peer reduce (fp32 over ranks, one rounding) straight into .grad.
-            main = torch.cuda.current_stream(hidden.device)
+            # last dX contraction and the rest of the main stream: the peer reduce of the fp32 sums (LM head +
+            # embedding) over ranks, one rounding, straight into .grad.
             accumulate = self.weight.grad is not None
             if not accumulate:
                 self.weight.grad = torch.empty_like(self.weight)
             hint = self.loss_fn.grad_hint
             self.side.wait_event(self.dw_ready)
             with torch.cuda.stream(self.side):
-                ops.embedding_grad_scatter_f32(dH0.reshape(-1, D), tokens.reshape(-1), self.peer.dw_acc)
                 self.peer.exchange(self.weight.grad, hint, hint, accumulate=accumulate)
             loss_batch.backward()  # dX rescale only (a device-side no-op: the multiplier was announced)
             main.wait_stream(self.side)
