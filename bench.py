@@ -300,6 +300,13 @@ def run_ours(args):
                       "every step (LossReader, read one step behind)", "loss_last": e2e_losses[-1]}
         del hx, hd
 
+    # per-rank sum of the main-stream kernel classes: under a power cap the GPUs of one box differ by a few per
+    # cent, and every step ends at the slowest rank (the exchange is a barrier)
+    per_rank_ms = None
+    if world > 1:
+        mine = sum(ms for k, (ms, _) in classes.items() if k not in ("exchange",)) / args.steps
+        per_rank_ms = [None] * world
+        dist.all_gather_object(per_rank_ms, round(mine, 3))
     mismatch = path.loss_fn.grad_hint_mismatch
     if mismatch is not None and bool(mismatch.any().item()):
         raise SystemExit("bench.py: the peer exchange ran with a multiplier that backward did not confirm")
@@ -355,6 +362,8 @@ def run_ours(args):
         "step_frac_of_bf16_peak": {"burst": step_tflops / peaks["bf16_tflops"], "sustained": step_tflops / peak},
         "kernels": kern,
     }
+    if per_rank_ms is not None:
+        line["per_rank_kernel_ms_per_step"] = per_rank_ms
     if world == 1 and not args.no_cpu_baseline:
         tps, times, cores = cpu_reference_tokens_per_s(cfg, 2, 1)
         line["cpu_baseline"] = {
