@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 102
+#define SSI_B200_ABI_VERSION 103
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -190,6 +190,46 @@ int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V,
  */
 int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int64_t ignore_index,
                                int64_t* labels_out, int64_t* counts, void* stream);
+
+/*
+ * ---- Rows SURVEY.md 8(f) marks "next": the callers and data formats either side of the path (HBM-bound) ----
+ *
+ * Final RMSNorm (tt/torchtune/modules/rms_norm.py:38-43, applied at tt/torchtune/modules/transformer.py:653 right
+ * before the projection): y = bf16((float(x) * rsqrt(mean(float(x)^2) + eps)) * float(scale)); x, y [N, D] bf16,
+ * scale [D] bf16, rstd [N] fp32 (may be NULL in forward-only use).  Backward (fp32 math like autograd of the fp32
+ * F.rms_norm): g = dy * scale, dx = rstd * (g - x * rstd^2 * mean(g * x)) -> bf16; dscale [D] fp32 =
+ * sum over rows of dy * x * rstd (fixed-order partials in `ws`, deterministic).  D % 8 == 0, D <= 8192 (backward).
+ */
+int ssi_b200_rmsnorm_fwd(const void* x, const void* scale, float eps, int64_t N, int64_t D, void* y, float* rstd,
+                         void* stream);
+int ssi_b200_rmsnorm_bwd_workspace_bytes(int64_t N, int64_t D, size_t* bytes);
+int ssi_b200_rmsnorm_bwd(const void* dy, const void* x, const void* scale, const float* rstd, int64_t N, int64_t D,
+                         void* dx, float* dscale, void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * ssi_b200_label_shift_count plus the token-type histogram of ssi/train_utils.py:150-165 in the same pass, all
+ * results left on the device (the reference does one host sync per range, ssi/trainer.py:388-391):
+ *   range_lo / range_hi  HOST arrays [n_ranges] of inclusive token-id ranges (n_ranges <= 15)
+ *   type_counts [n_ranges + 1] int64 out: tokens inside each range, then "total" = #(tokens != pad_idx)
+ */
+int ssi_b200_label_shift_count_types(const int64_t* labels, const int64_t* tokens, int64_t B, int64_t S,
+                                     int64_t ignore_index, const int64_t* range_lo, const int64_t* range_hi,
+                                     int n_ranges, int64_t pad_idx, int64_t* labels_out, int64_t* counts,
+                                     int64_t* type_counts, void* stream);
+
+/*
+ * scale_grads (tt/torchtune/training/_grad_scaler.py:25-31: p.grad *= scaler) for one bf16 gradient buffer and, in
+ * the same pass, the sum of squares of the SCALED values that clip_grad_norm_ (ssi/trainer.py:405-408) needs of
+ * it: grad = bf16(float(grad) * scale[0]) in place; sqnorm_out[0] = sum(float(grad_new)^2), fp32, deterministic.
+ */
+int ssi_b200_grad_scale_sqnorm_workspace_bytes(size_t* bytes);
+int ssi_b200_grad_scale_sqnorm(void* grad, int64_t n_elems, const float* scale, float* sqnorm_out, void* ws,
+                               size_t ws_bytes, void* stream);
+
+/* Forward embedding gather (tt/torchtune/modules/transformer.py:628): out[i, :] = W[ids[i], :], bf16, exact copy;
+ * ids outside [0, V) give zero rows. */
+int ssi_b200_embedding_gather(const void* W, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* out,
+                              void* stream);
 
 /*
  * Optional per-kernel-class timing (used by bench.py for the roofline figure): between profile_begin and

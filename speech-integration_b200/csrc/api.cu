@@ -17,6 +17,7 @@
 #include "aux_kernels.cuh"
 #include "dp_exchange.cuh"
 #include "gemm.cuh"
+#include "next_rows.cuh"
 
 namespace {
 
@@ -1027,6 +1028,149 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
   ssi::label_shift_count_kernel<<<grid, 256, 0, st>>>(labels, B, S, ignore_index, labels_out,
                                                       reinterpret_cast<unsigned long long*>(counts));
   SSI_LAUNCH_OK("label_shift_count");
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// SURVEY.md 8(f) "next" rows (next_rows.cuh)
+// ---------------------------------------------------------------------------------------------------
+int ssi_b200_rmsnorm_fwd(const void* x, const void* scale, float eps, int64_t N, int64_t D, void* y, float* rstd,
+                         void* stream) {
+  SSI_CHECK_ARG(x && scale && y, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && D >= 8 && D % 8 == 0 && N < (int64_t(1) << 31), "bad shape N=%lld D=%lld", (long long)N,
+                (long long)D);
+  SSI_CHECK_ARG(((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(scale) | reinterpret_cast<uintptr_t>(y)) & 15) == 0,
+                "x / scale / y must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_AUX, st);
+  ssi::rmsnorm_fwd_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(x), static_cast<const uint4*>(scale),
+                                                       eps, static_cast<int>(N), static_cast<int>(D / 8),
+                                                       static_cast<uint4*>(y), rstd);
+  SSI_LAUNCH_OK("rmsnorm_fwd");
+  return 0;
+}
+
+namespace {
+constexpr int RMS_BWD_BLOCKS_PER_SM = 2;
+}
+
+int ssi_b200_rmsnorm_bwd_workspace_bytes(int64_t N, int64_t D, size_t* bytes) {
+  SSI_CHECK_ARG(bytes, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld D=%lld", (long long)N, (long long)D);
+  // one fp32 partial row of dscale per warp of the backward grid (148 SMs x 2 blocks x 8 warps at most)
+  *bytes = static_cast<size_t>(148) * RMS_BWD_BLOCKS_PER_SM * 8 * D * sizeof(float);
+  return 0;
+}
+
+int ssi_b200_rmsnorm_bwd(const void* dy, const void* x, const void* scale, const float* rstd, int64_t N, int64_t D,
+                         void* dx, float* dscale, void* ws, size_t ws_bytes, void* stream) {
+  SSI_CHECK_ARG(dy && x && scale && rstd && dx && dscale && ws, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && D >= 8 && D % 8 == 0 && N < (int64_t(1) << 31), "bad shape N=%lld D=%lld", (long long)N,
+                (long long)D);
+  SSI_CHECK_ARG(D <= 8192, "D=%lld > 8192 is not supported by the RMSNorm backward", (long long)D);
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int sms = di->sms < 148 ? di->sms : 148;
+  const int grid = sms * RMS_BWD_BLOCKS_PER_SM;
+  const int nparts = grid * 8;
+  SSI_CHECK_ARG(ws_bytes >= static_cast<size_t>(nparts) * D * sizeof(float), "RMSNorm backward workspace too small");
+  const int row_u4 = static_cast<int>(D / 8);
+  const int maxj = (row_u4 + 31) / 32;
+  float* partial = static_cast<float*>(ws);
+  ProfScope ps(CAT_AUX, st);
+#define SSI_RMS_BWD(J)                                                                                              \
+  ssi::rmsnorm_bwd_kernel<J><<<grid, 256, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(x),     \
+                                                   static_cast<const uint4*>(scale), rstd, static_cast<int>(N),    \
+                                                   row_u4, static_cast<uint4*>(dx), partial)
+  if (maxj <= 2) SSI_RMS_BWD(2);
+  else if (maxj <= 4) SSI_RMS_BWD(4);
+  else if (maxj <= 8) SSI_RMS_BWD(8);
+  else if (maxj <= 16) SSI_RMS_BWD(16);
+  else SSI_RMS_BWD(32);
+#undef SSI_RMS_BWD
+  SSI_LAUNCH_OK("rmsnorm_bwd");
+  ssi::rmsnorm_dscale_reduce_kernel<<<static_cast<int>(ceil_div(D, 256)), 256, 0, st>>>(partial, nparts,
+                                                                                      static_cast<int>(D), dscale);
+  SSI_LAUNCH_OK("rmsnorm_dscale_reduce");
+  return 0;
+}
+
+int ssi_b200_label_shift_count_types(const int64_t* labels, const int64_t* tokens, int64_t B, int64_t S,
+                                     int64_t ignore_index, const int64_t* range_lo, const int64_t* range_hi,
+                                     int n_ranges, int64_t pad_idx, int64_t* labels_out, int64_t* counts,
+                                     int64_t* type_counts, void* stream) {
+  SSI_CHECK_ARG(labels && tokens && labels_out && counts && type_counts, "null pointer argument");
+  SSI_CHECK_ARG(B >= 1 && S >= 1, "bad shape B=%lld S=%lld", (long long)B, (long long)S);
+  SSI_CHECK_ARG(n_ranges >= 0 && n_ranges <= ssi::MAX_TOKEN_RANGES && (n_ranges == 0 || (range_lo && range_hi)),
+                "n_ranges=%d not in [0, %d] or null range arrays (HOST arrays)", n_ranges, ssi::MAX_TOKEN_RANGES);
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ssi::TokenRanges tr;
+  memset(&tr, 0, sizeof(tr));
+  tr.n = n_ranges;
+  for (int k = 0; k < n_ranges; ++k) tr.lo[k] = range_lo[k], tr.hi[k] = range_hi[k];
+  SSI_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), st));
+  SSI_CUDA(cudaMemsetAsync(type_counts, 0, (n_ranges + 1) * sizeof(int64_t), st));
+  const int64_t total = B * S;
+  int grid = static_cast<int>(ceil_div(total, 256));
+  if (grid > di->sms * 8) grid = di->sms * 8;
+  ProfScope ps(CAT_AUX, st);
+  ssi::label_shift_count_types_kernel<<<grid, 256, 0, st>>>(labels, tokens, B, S, ignore_index, tr, pad_idx, labels_out,
+                                                            reinterpret_cast<unsigned long long*>(counts),
+                                                            reinterpret_cast<unsigned long long*>(type_counts));
+  SSI_LAUNCH_OK("label_shift_count_types");
+  return 0;
+}
+
+namespace {
+constexpr int SQNORM_BLOCKS = 148 * 8;
+}
+
+int ssi_b200_grad_scale_sqnorm_workspace_bytes(size_t* bytes) {
+  SSI_CHECK_ARG(bytes, "null pointer argument");
+  *bytes = SQNORM_BLOCKS * sizeof(float);
+  return 0;
+}
+
+int ssi_b200_grad_scale_sqnorm(void* grad, int64_t n_elems, const float* scale, float* sqnorm_out, void* ws,
+                               size_t ws_bytes, void* stream) {
+  SSI_CHECK_ARG(grad && scale && sqnorm_out && ws, "null pointer argument");
+  SSI_CHECK_ARG(n_elems >= 8 && n_elems % 8 == 0, "element count %lld must be a positive multiple of 8",
+                (long long)n_elems);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(grad) & 15) == 0, "grad must be 16-byte aligned");
+  SSI_CHECK_ARG(ws_bytes >= SQNORM_BLOCKS * sizeof(float), "workspace too small");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const size_t n_u4 = static_cast<size_t>(n_elems) / 8;
+  int grid = static_cast<int>(ceil_div(static_cast<int64_t>(n_u4), 256));
+  if (grid > SQNORM_BLOCKS) grid = SQNORM_BLOCKS;
+  ProfScope ps(CAT_AUX, st);
+  ssi::grad_scale_sqnorm_kernel<<<grid, 256, 0, st>>>(static_cast<uint4*>(grad), n_u4, scale, static_cast<float*>(ws));
+  SSI_LAUNCH_OK("grad_scale_sqnorm");
+  ssi::sqnorm_finalize_kernel<<<1, 256, 0, st>>>(static_cast<const float*>(ws), grid, sqnorm_out);
+  SSI_LAUNCH_OK("sqnorm_finalize");
+  return 0;
+}
+
+int ssi_b200_embedding_gather(const void* W, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* out,
+                              void* stream) {
+  SSI_CHECK_ARG(W && ids && out, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0 && N < (int64_t(1) << 31), "bad shape N=%lld V=%lld D=%lld",
+                (long long)N, (long long)V, (long long)D);
+  SSI_CHECK_ARG(((reinterpret_cast<uintptr_t>(W) | reinterpret_cast<uintptr_t>(out)) & 15) == 0,
+                "W / out must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_AUX, st);
+  ssi::embedding_gather_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(W), ids, static_cast<int>(N), V,
+                                                            static_cast<int>(D / 8), static_cast<uint4*>(out));
+  SSI_LAUNCH_OK("embedding_gather");
   return 0;
 }
 

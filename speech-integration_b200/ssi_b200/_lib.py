@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 102
+ABI_VERSION = 103
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -73,6 +73,20 @@ SYMBOLS = {
          c_void_p],
     ),
     "ssi_b200_label_shift_count": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ssi_b200_rmsnorm_fwd": (c_int, [c_void_p, c_void_p, ctypes.c_float, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ssi_b200_rmsnorm_bwd_workspace_bytes": (c_int, [c_int64, c_int64, POINTER(c_size_t)]),
+    "ssi_b200_rmsnorm_bwd": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_label_shift_count_types": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_int64, c_int64, POINTER(c_int64), POINTER(c_int64), c_int, c_int64, c_void_p,
+         c_void_p, c_void_p, c_void_p],
+    ),
+    "ssi_b200_grad_scale_sqnorm_workspace_bytes": (c_int, [POINTER(c_size_t)]),
+    "ssi_b200_grad_scale_sqnorm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ssi_b200_embedding_gather": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "ssi_b200_profile_begin": (c_int, []),
     "ssi_b200_profile_end": (c_int, [c_void_p, c_void_p]),
     "ssi_b200_debug_gemm": (

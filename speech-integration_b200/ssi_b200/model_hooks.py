@@ -39,6 +39,8 @@ class _EmbeddingFn(torch.autograd.Function):
         ctx.module = module
         ctx.save_for_backward(tokens)
         ctx.wshape = weight.shape
+        if weight.dtype == torch.bfloat16 and weight.is_contiguous():
+            return ops.embedding_gather(weight, tokens)  # the library's own row gather
         return torch.nn.functional.embedding(tokens, weight)
 
     @staticmethod
@@ -78,15 +80,68 @@ class TiedEmbeddingB200(nn.Embedding):
         return new
 
 
+class _RMSNormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, scale, eps):
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        need = x.requires_grad or scale.requires_grad
+        y, rstd = ops.rmsnorm_fwd(x2, scale, eps, want_rstd=need)
+        if need:
+            ctx.save_for_backward(x2, scale, rstd)
+        ctx.shape = shape
+        return y.reshape(shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, scale, rstd = ctx.saved_tensors
+        dy2 = dy.reshape(x2.shape)
+        if dy2.dtype != torch.bfloat16:
+            dy2 = dy2.to(torch.bfloat16)
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        dx, dscale = ops.rmsnorm_bwd(dy2, x2, scale, rstd)
+        return dx.reshape(ctx.shape), dscale.to(scale.dtype), None
+
+
+class RMSNormB200(nn.Module):
+    """Drop-in for torchtune's ``RMSNorm`` (tt/torchtune/modules/rms_norm.py:12-43: same ``scale`` parameter,
+    ``eps`` and ``normalized_shape`` attributes, fp32 math, output in the input dtype) for the final norm that
+    feeds the path (``model.norm``, tt/torchtune/modules/transformer.py:653).  bf16 CUDA tensors only."""
+
+    def __init__(self, dim: int, eps: float = 1e-6, device=None, dtype=None) -> None:
+        super().__init__()
+        self.normalized_shape = (dim,)
+        self.eps = eps
+        self.scale = nn.Parameter(torch.ones(dim, device=device, dtype=dtype))
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return _RMSNormFn.apply(x, self.scale, self.eps)
+
+    @classmethod
+    def from_norm(cls, norm: nn.Module) -> "RMSNormB200":
+        new = cls(norm.scale.numel(), eps=norm.eps, device="meta", dtype=norm.scale.dtype)
+        new.scale = norm.scale  # share the Parameter: optimizer / checkpoint key `norm.scale` unchanged
+        return new
+
+
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
-            replace_embedding: bool = True, mode: str | None = None) -> FusedLinearCrossEntropyLoss:
+            replace_embedding: bool = True, mode: str | None = None,
+            replace_norm: bool = False) -> FusedLinearCrossEntropyLoss:
     """Mirror of ``Trainer._setup_loss`` (ssi/trainer.py:299-304) for the fused path.
 
     Replaces ``model.output`` by a hidden passthrough, optionally swaps ``model.tok_embeddings`` for
     :class:`TiedEmbeddingB200` (sharing the same Parameter), calls ``model.set_num_output_chunks`` when the model
     has it, and returns the loss module to use as ``loss_fn``. ``mode``: ``"single_pass"`` (default) or
-    ``"recompute"``, see :func:`ssi_b200.loss.fused_linear_cross_entropy`.
+    ``"recompute"``, see :func:`ssi_b200.loss.fused_linear_cross_entropy`.  ``replace_norm``: also swap the final
+    ``model.norm`` (tt/torchtune/modules/transformer.py:653) for :class:`RMSNormB200`, sharing its ``scale``.
     """
+    norm = getattr(model, "norm", None)
+    if (replace_norm and norm is not None and hasattr(norm, "scale") and hasattr(norm, "eps")
+            and not isinstance(norm, RMSNormB200)):
+        model.norm = RMSNormB200.from_norm(norm)
     emb = model.tok_embeddings
     if replace_embedding and isinstance(emb, nn.Embedding) and not isinstance(emb, TiedEmbeddingB200):
         emb = TiedEmbeddingB200.from_embedding(emb)

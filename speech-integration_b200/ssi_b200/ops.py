@@ -319,3 +319,123 @@ def debug_gemm(A: torch.Tensor, B: torch.Tensor, a_mn_major: bool = False, b_mn_
                                      int(b_mn_major), int(acc), _stream(dev))
     _lib.check(rc, "debug_gemm")
     return C
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Rows SURVEY.md §8(f) marks "next": final RMSNorm, token-type histogram, scale_grads + grad norm, embedding gather
+# ----------------------------------------------------------------------------------------------------------
+def rmsnorm_fwd(x: torch.Tensor, scale: torch.Tensor, eps: float = 1e-6, want_rstd: bool = True):
+    """Final RMSNorm (tt/torchtune/modules/rms_norm.py:38-43): ``x [N, D]`` bf16, ``scale [D]`` bf16 ->
+    ``(y [N, D] bf16, rstd [N] fp32 or None)``, fp32 math, one rounding."""
+    dev = _require_cuda(x, scale)
+    if x.dtype != torch.bfloat16 or scale.dtype != torch.bfloat16:
+        raise TypeError("ssi_b200: x and scale must be bfloat16")
+    if x.dim() != 2 or scale.dim() != 1 or scale.numel() != x.size(1) or not (x.is_contiguous() and scale.is_contiguous()):
+        raise ValueError("ssi_b200: expected contiguous x [N, D] and scale [D]")
+    N, D = x.shape
+    y = torch.empty_like(x)
+    rstd = torch.empty(N, dtype=torch.float32, device=dev) if want_rstd else None
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_rmsnorm_fwd(x.data_ptr(), scale.data_ptr(), float(eps), N, D, y.data_ptr(),
+                                              rstd.data_ptr() if rstd is not None else None, _stream(dev))
+    _lib.check(rc, "rmsnorm_fwd")
+    return y, rstd
+
+
+def rmsnorm_bwd(dy: torch.Tensor, x: torch.Tensor, scale: torch.Tensor, rstd: torch.Tensor):
+    """Backward of :func:`rmsnorm_fwd`: returns ``(dx [N, D] bf16, dscale [D] fp32)``."""
+    dev = _require_cuda(dy, x, scale, rstd)
+    if dy.dtype != torch.bfloat16 or x.dtype != torch.bfloat16 or scale.dtype != torch.bfloat16:
+        raise TypeError("ssi_b200: dy, x and scale must be bfloat16")
+    if dy.shape != x.shape or x.dim() != 2 or not (dy.is_contiguous() and x.is_contiguous()):
+        raise ValueError("ssi_b200: dy and x must be contiguous [N, D] tensors of the same shape")
+    if rstd.dtype != torch.float32 or rstd.numel() != x.size(0):
+        raise ValueError("ssi_b200: rstd must be fp32 [N]")
+    N, D = x.shape
+    lib = _lib.load()
+    import ctypes
+
+    b = ctypes.c_size_t(0)
+    _lib.check(lib.ssi_b200_rmsnorm_bwd_workspace_bytes(N, D, ctypes.byref(b)), "rmsnorm_bwd_workspace_bytes")
+    ws = _workspace("rmsnorm_bwd", b.value, dev)
+    dx = torch.empty_like(x)
+    dscale = torch.empty(D, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_rmsnorm_bwd(dy.data_ptr(), x.data_ptr(), scale.data_ptr(), rstd.data_ptr(), N, D,
+                                      dx.data_ptr(), dscale.data_ptr(), ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "rmsnorm_bwd")
+    return dx, dscale
+
+
+def label_shift_count_types(labels: torch.Tensor, tokens: torch.Tensor, ranges: dict, pad_idx: int,
+                            ignore_index: int = -100):
+    """Label shift + valid-token counts (as :func:`label_shift_count`) and the token-type histogram of
+    ssi/train_utils.py:150-165 in one pass, everything left on the device (no host sync).
+
+    ``ranges``: ``{name: (first_id, last_id)}`` inclusive, at most 15 entries.  Returns ``(shifted, counts int64
+    [2], type_counts int64 [len(ranges) + 1])``; the last entry of ``type_counts`` is "total" = tokens != pad_idx,
+    the others follow ``ranges``' order."""
+    dev = _require_cuda(labels, tokens)
+    if labels.dtype != torch.int64 or labels.dim() != 2 or not labels.is_contiguous():
+        raise ValueError("ssi_b200: labels must be a contiguous int64 [B, S] tensor")
+    if tokens.dtype != torch.int64 or tokens.shape != labels.shape or not tokens.is_contiguous():
+        raise ValueError("ssi_b200: tokens must be a contiguous int64 tensor shaped like labels")
+    import ctypes
+
+    names = list(ranges)
+    n = len(names)
+    lo = (ctypes.c_int64 * max(n, 1))(*[int(ranges[k][0]) for k in names])
+    hi = (ctypes.c_int64 * max(n, 1))(*[int(ranges[k][1]) for k in names])
+    B, S = labels.shape
+    out = torch.empty_like(labels)
+    counts = torch.empty(2, dtype=torch.int64, device=dev)
+    type_counts = torch.empty(n + 1, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_label_shift_count_types(labels.data_ptr(), tokens.data_ptr(), B, S,
+                                                          int(ignore_index), lo, hi, n, int(pad_idx), out.data_ptr(),
+                                                          counts.data_ptr(), type_counts.data_ptr(), _stream(dev))
+    _lib.check(rc, "label_shift_count_types")
+    return out, counts, type_counts
+
+
+def grad_scale_sqnorm(grad: torch.Tensor, scale: torch.Tensor) -> torch.Tensor:
+    """``grad *= scale`` in place (tt/torchtune/training/_grad_scaler.py:25-31) and, in the same pass, the fp32
+    sum of squares of the scaled bf16 values (this parameter's share of clip_grad_norm_'s total norm, ssi/
+    trainer.py:405-408). ``scale``: fp32 device scalar. Returns the fp32 ``[1]`` sum of squares."""
+    dev = _require_cuda(grad, scale)
+    if grad.dtype != torch.bfloat16 or not grad.is_contiguous() or grad.numel() % 8:
+        raise ValueError("ssi_b200: grad must be a contiguous bf16 tensor with a multiple of 8 elements")
+    if scale.dtype != torch.float32 or scale.numel() != 1:
+        raise ValueError("ssi_b200: scale must be a single fp32 value on the device")
+    import ctypes
+
+    lib = _lib.load()
+    b = ctypes.c_size_t(0)
+    _lib.check(lib.ssi_b200_grad_scale_sqnorm_workspace_bytes(ctypes.byref(b)), "grad_scale_sqnorm_workspace_bytes")
+    ws = _workspace("sqnorm", b.value, dev)
+    out = torch.empty(1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = lib.ssi_b200_grad_scale_sqnorm(grad.data_ptr(), grad.numel(), scale.data_ptr(), out.data_ptr(),
+                                            ws.data_ptr(), ws.numel(), _stream(dev))
+    _lib.check(rc, "grad_scale_sqnorm")
+    return out
+
+
+def embedding_gather(W: torch.Tensor, ids: torch.Tensor) -> torch.Tensor:
+    """Forward of the tied ``nn.Embedding`` (tt/torchtune/modules/transformer.py:628): ``W[ids]`` as
+    ``[*ids.shape, D]`` bf16, an exact copy of the rows."""
+    dev = _require_cuda(W, ids)
+    if W.dtype != torch.bfloat16 or W.dim() != 2 or not W.is_contiguous():
+        raise ValueError("ssi_b200: W must be a contiguous bf16 [V, D] tensor")
+    if ids.dtype != torch.int64:
+        raise ValueError("ssi_b200: ids must be int64")
+    flat = ids.reshape(-1)
+    if not flat.is_contiguous():
+        flat = flat.contiguous()
+    V, D = W.shape
+    out = torch.empty(flat.numel(), D, dtype=W.dtype, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_embedding_gather(W.data_ptr(), flat.data_ptr(), flat.numel(), V, D, out.data_ptr(),
+                                                   _stream(dev))
+    _lib.check(rc, "embedding_gather")
+    return out.reshape(*ids.shape, D)
