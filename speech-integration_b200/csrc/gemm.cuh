@@ -417,6 +417,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             if (c0 >= p.vocab) break;
             float v[32];
             tmem_ld32(taddr + c * 32, v);
+            // the reference's logits are bf16 (tied_linear.py:25) and upcast before the CE
+            // (ce_chunked_output_loss.py:41): round here too, so every mode sees the same values
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const uint32_t pk = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+              v[2 * j] = bf16lo(pk);
+              v[2 * j + 1] = bf16hi(pk);
+            }
             if (tile_has_pad) {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
@@ -526,6 +534,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               float v[32];
               tmem_ld32(taddr + c * 64 + h * 32, v);
               const int ch0 = c0 + h * 32;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {  // bf16 logits, as in forward
+                const uint32_t pk = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                v[2 * j] = bf16lo(pk);
+                v[2 * j + 1] = bf16hi(pk);
+              }
 #pragma unroll
               for (int j = 0; j < 32; ++j) {
                 float g = valid ? fast_exp2(fmaf(v[j], LOG2E, -lse2)) * gscale : 0.f;

@@ -76,9 +76,12 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
     ``grad_out / grad_hint`` (1 when the trainer announced its multiplier) and rounds dW once into ``.grad``."""
 
     @staticmethod
-    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint):
+    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint, grad_enabled=True):
         ctx.holder = holder
-        ctx.with_grad = bool(ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
+        # `grad_enabled` is sampled by the caller: inside Function.forward grad mode is always off, and under
+        # torch.no_grad() / inference_mode() (the eval path, ssi/eval.py:27-33) needs_input_grad still reports the
+        # Parameter -- forming gradients there would triple the work of a forward-only call
+        ctx.with_grad = bool(grad_enabled and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]))
         if ctx.with_grad:
             hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
             loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(
@@ -111,15 +114,15 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
             # here only dX is rescaled, and a wrong announcement is left visible instead of silently ignored.
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
             holder.grad_hint_mismatch = (g != hint)
-            return dX, None, None, None, None, None, None
+            return dX, None, None, None, None, None, None, None
         if wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr:
             acc = wparam.grad is not None
             if not acc:
                 wparam.grad = torch.empty_like(wparam)
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc)
-            return dX, None, None, None, None, None, None
+            return dX, None, None, None, None, None, None, None
         _, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint)
-        return dX, dW, None, None, None, None, None
+        return dX, dW, None, None, None, None, None, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
@@ -134,7 +137,8 @@ def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, label
         return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
     if mode != "single_pass":
         raise ValueError(f"ssi_b200: unknown mode {mode!r} (expected 'single_pass' or 'recompute')")
-    return _FusedLinearCESinglePass.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, grad_hint)
+    return _FusedLinearCESinglePass.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, grad_hint,
+                                          torch.is_grad_enabled())
 
 
 class FusedLinearCrossEntropyLoss(nn.Module):

@@ -135,3 +135,26 @@ def test_gradient_accumulation_and_determinism():
         _, _, _, dW = oracle.train_step_path(mb["tokens"], mb["labels"], mb["X"], mb["dH0"], W)
         ref += dW
     assert_grad_close(g1, ref, "accumulated dW")
+
+
+@pytest.mark.parametrize("ctxmgr", [torch.inference_mode, torch.no_grad])
+def test_eval_path_is_forward_only(ctxmgr):
+    """ssi/eval.py:27-33 calls the loss under inference mode: only the online-LSE kernel may run there (no logits
+    block, no dW / dX contraction), and the value equals the training-mode loss."""
+    from ssi_b200 import _lib
+    from ssi_b200.step import PathStep
+
+    fx = torch.load(GOLDEN[0])
+    inp = fx["inputs"]
+    dev = torch.device("cuda")
+    step = PathStep(inp["W"].to(dev))
+    X, labels = inp["X"].to(dev), inp["labels"].to(dev)
+    _lib.profile_begin()
+    with ctxmgr():
+        shifted = torch.hstack((labels[..., 1:], torch.full_like(labels[..., :1], -100)))  # ssi/loss.py:16
+        loss = step.loss_fn(X, shifted)
+    cls = _lib.profile_end()
+    assert cls["lse_fwd"][1] >= 1
+    assert cls["dW"][1] == 0 and cls["dX"][1] == 0 and cls["softmax_grad"][1] == 0
+    want = fx["fp32"]["loss"].item()
+    assert abs(loss.item() - want) <= LOSS_RTOL * abs(want)
