@@ -1092,7 +1092,7 @@ int ssi_b200_rmsnorm_bwd(const void* dy, const void* x, const void* scale, const
   else SSI_RMS_BWD(32);
 #undef SSI_RMS_BWD
   SSI_LAUNCH_OK("rmsnorm_bwd");
-  ssi::rmsnorm_dscale_reduce_kernel<<<static_cast<int>(ceil_div(D, 256)), 256, 0, st>>>(partial, nparts,
+  ssi::rmsnorm_dscale_reduce_kernel<<<static_cast<int>(ceil_div(D, 32)), 256, 0, st>>>(partial, nparts,
                                                                                       static_cast<int>(D), dscale);
   SSI_LAUNCH_OK("rmsnorm_dscale_reduce");
   return 0;

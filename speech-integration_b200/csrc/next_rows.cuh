@@ -127,13 +127,33 @@ __global__ void __launch_bounds__(256) rmsnorm_bwd_kernel(const uint4* __restric
   }
 }
 
+// dscale[j] = sum over the partial rows, in a fixed order: a block owns 32 columns, its 8 warps each sum every
+// 8th partial row (coalesced 128-byte reads, 8 loads in flight), then the 8 sums are added in warp order.
 __global__ void __launch_bounds__(256) rmsnorm_dscale_reduce_kernel(const float* __restrict__ partial, int nparts,
                                                                     int d, float* __restrict__ dscale) {
-  const int j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= d) return;
+  __shared__ float s_acc[8][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
   float a = 0.f;
-  for (int p = 0; p < nparts; ++p) a += partial[static_cast<size_t>(p) * d + j];
-  dscale[j] = a;
+  if (j < d) {
+    int p = w;
+    for (; p + 56 < nparts; p += 64) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) v[u] = partial[static_cast<size_t>(p + 8 * u) * d + j];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) a += v[u];
+    }
+    for (; p < nparts; p += 8) a += partial[static_cast<size_t>(p) * d + j];
+  }
+  s_acc[w][lane] = a;
+  __syncthreads();
+  if (w == 0 && j < d) {
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += s_acc[k][lane];
+    dscale[j] = t;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------
