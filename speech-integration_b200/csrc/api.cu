@@ -158,7 +158,8 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
   return 0;
 }
 
-int cta_group();  // tuning knob, defined below
+int cta_group();       // tuning knobs, defined below
+int tail_split_opt();
 
 template <int EPI, bool A_MN, bool B_MN, int CG, int NW = 1>
 int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int grid_override) {
@@ -213,7 +214,11 @@ int launch_gemm(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* 
 // Long-K contractions (single-pass dW / dX): 256x512 tiles per CTA pair when `wide` == 2 ("wide_dw" / "wide_dx").
 template <int EPI, bool A_MN, bool B_MN>
 int launch_gemm_wide(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int wide) {
-  if (cta_group() == 2 && wide == 2) return launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(p, sms, st, name, cat, 0);
+  if (cta_group() == 2 && wide == 2) {
+    ssi::GemmParams q = p;
+    q.tail_split = tail_split_opt();
+    return launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(q, sms, st, name, cat, 0);
+  }
   return launch_gemm<EPI, A_MN, B_MN>(p, sms, st, name, cat);
 }
 
@@ -272,6 +277,7 @@ struct Tune {
   int k1_hints = 0, dw_hints = 0, dx_hints = 0;  // operand L2 policies: 10 * A + B; 1 evict-first, 2 evict-last
   int lockstep = 64;   // k-blocks between lockstep sync points of the dW / dX contractions (0 = off)
   int cta_group = 2;   // 2 = CTA pairs (tcgen05 cta_group::2, 256x256 tiles), 1 = single-CTA 128x256 tiles
+  int tail_split = 1;  // wide tiles: split the items of an at most half-full last wave into 256x256 halves
   int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
 };
 Tune& tune() {
@@ -288,6 +294,7 @@ Tune& tune() {
     if (const char* e = getenv("SSI_B200_LOCKSTEP")) x.lockstep = atoi(e);
     if (const char* e = getenv("SSI_B200_DW_HINTS")) x.dw_hints = atoi(e);
     if (const char* e = getenv("SSI_B200_DX_HINTS")) x.dx_hints = atoi(e);
+    if (const char* e = getenv("SSI_B200_TAIL_SPLIT")) x.tail_split = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
     return x;
@@ -296,6 +303,7 @@ Tune& tune() {
 }
 
 int cta_group() { return tune().cta_group; }
+int tail_split_opt() { return tune().tail_split; }
 unsigned long long policy_of(int code) {
   return code == 1 ? ssi::kEvictFirst : code == 2 ? ssi::kEvictLast : code == 3 ? ssi::kEvictNormal : 0ull;
 }
@@ -451,6 +459,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "lockstep")) t.lockstep = static_cast<int>(value);
   else if (!strcmp(name, "dw_hints")) t.dw_hints = static_cast<int>(value);
   else if (!strcmp(name, "dx_hints")) t.dx_hints = static_cast<int>(value);
+  else if (!strcmp(name, "tail_split")) t.tail_split = value ? 1 : 0;
   else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
   else return fail(-1, "unknown option '%s'", name);
@@ -707,7 +716,8 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
                                                   ignore_index, pos, idx, labels_c, dplan, f.vtiles_total, di->sms,
                                                   f.t_max, f.chunks_max,
                                                   (cta_group() == 2 && tune().wide_dx == 2) ? (d_tiles + 1) / 2 : d_tiles,
-                                                  n_valid, cta_group());
+                                                  n_valid, cta_group(),
+                                                  (cta_group() == 2 && tune().wide_dx == 2) ? tune().tail_split : 0);
     SSI_LAUNCH_OK("compact_scan");
     ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,

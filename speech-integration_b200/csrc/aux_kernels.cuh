@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
                                                             DevPlan* __restrict__ plan, int vtiles_total, int sms,
                                                             int chunk_t_max = 0, int chunks_max = 0,
                                                             int d_tiles = 0, int64_t* n_valid_out = nullptr,
-                                                            int cg = 1) {
+                                                            int cg = 1, int half_tail = 0) {
   __shared__ int s_sum[1024];
   __shared__ int s_chunk_t;
   const int per = (n + 1023) / 1024;
@@ -118,8 +118,13 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
         const int nch = full + (rem ? 1 : 0);
         if (nch > chunks_max) continue;
         const int wk = max(sms / cg, 1);  // concurrent work items (CTAs or CTA pairs)
-        float cost = static_cast<float>(full) * ((((t + cg - 1) / cg) * d_tiles + wk - 1) / wk) + 0.3f * nch;
-        if (rem) cost += (((rem + cg - 1) / cg) * d_tiles + wk - 1) / wk;
+        // waves of the dX contraction; with tail splitting an at most half-full last wave costs half a wave
+        auto waves = [&](int items) {
+          const int tail = items % wk;
+          return static_cast<float>(items / wk) + (tail == 0 ? 0.f : (half_tail && 2 * tail <= wk) ? 0.5f : 1.f);
+        };
+        float cost = static_cast<float>(full) * waves(((t + cg - 1) / cg) * d_tiles) + 0.3f * nch;
+        if (rem) cost += waves(((rem + cg - 1) / cg) * d_tiles);
         if (best_cost < 0.f || cost <= best_cost) best_cost = cost, best_t = t;
       }
     }

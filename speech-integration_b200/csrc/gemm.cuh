@@ -66,6 +66,7 @@ struct GemmParams {
   int a_r0, a_k0, b_r0, b_k0, c_r0, c_c0;
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
   int c_reduce_plan;  // 1 = take it from the chunk plan instead: reduce-add unless dplan->first
+  int tail_split;     // wide tiles (NW 2): run the items of a last, at most half-full wave as 256x256 halves
   unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
   unsigned long long a_policy, b_policy;  // L2 cache policy of the A / B operand loads (0 = default)
   // Lockstep throttle (EPI_BF16 / EPI_F32 only, uniform K loops): every `sync_every` k-blocks the producers of
@@ -208,7 +209,27 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     sc.group_m = max(1, sc.group_m >> 1);
   }
   if constexpr (NW == 2) sc.tiles_n = (sc.tiles_n + 1) >> 1;  // ... and over 512-column tile pairs
-  const int total_items = sc.tiles_m * sc.tiles_n;
+  // Wide tiles: when the last wave of the static schedule would be at most half full, its items are split into their
+  // two 256-column halves (one MMA per k-step instead of two, on the same stage layout), so that wave takes half
+  // as long: e.g. 256 items on 74 CTA pairs = 3 waves + 34 items -> 3 waves + 68 half items.
+  const int wide_items = sc.tiles_m * sc.tiles_n;
+  int split_from = wide_items, total_items = wide_items;
+  if constexpr (NW == 2) {
+    if (p.tail_split && workers > 0) {
+      const int tail = wide_items % workers;
+      if (tail > 0 && 2 * tail <= workers) split_from = wide_items - tail, total_items = split_from + 2 * tail;
+    }
+  }
+  // item -> (tile, first 256-column half, number of halves)
+  auto get_item = [&](int item, int& h0, int& nh) {
+    if (NW == 2 && item >= split_from) {
+      const int j = item - split_from;
+      h0 = j & 1, nh = 1;
+      return decode_item<EPI>(sc, split_from + (j >> 1));
+    }
+    h0 = 0, nh = NW;
+    return decode_item<EPI>(sc, item);
+  };
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&p.tmA);
@@ -251,12 +272,13 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const int sync_pts = throttle ? (sc.k_blocks - 1) / sync_T : 0;  // points at kb = T, 2T, ... < k_blocks
       unsigned int sync_base = 0;                                       // arrivals of all earlier rounds
       for (int item = worker; item < total_items; item += workers) {
-        const TileItem it = decode_item<EPI>(sc, item);
+        int h0, nh;
+        const TileItem it = get_item(item, h0, nh);
         const int m_tile = (CG == 2) ? (2 * it.m + static_cast<int>(cta_rank)) : it.m;
         const unsigned int round_workers = static_cast<unsigned int>(min(workers, total_items - (item - worker)));
         for (int t = 0; t < it.ncount; ++t) {
           const int nt = it.n0 + t;
-          const int b_row = p.b_r0 + nt * BNW + static_cast<int>(cta_rank) * BN_CTA;
+          const int b_row = p.b_r0 + nt * BNW + h0 * BN + static_cast<int>(cta_rank) * BN_CTA;
           int next_arrive = sync_T, next_wait = 0x7fffffff, sync_j = 0;
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
             if (throttle) {
@@ -276,7 +298,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             mbar_wait(empty_bar(stage), phase ^ 1u);
             // CG 2: both CTAs signal the LEADER's full barrier; only the leader posts the expected bytes
             const uint32_t fb = (CG == 2) ? (full_bar(stage) & 0xFEFFFFFFu) : full_bar(stage);
-            if (CG == 1 || cta_rank == 0) mbar_expect_tx(full_bar(stage), CG * STAGE_BYTES);
+            if (CG == 1 || cta_rank == 0)
+              mbar_expect_tx(full_bar(stage), CG * (A_STAGE_BYTES + nh * B_HALF_BYTES));
             const uint32_t sA = smem_stage0 + stage * STAGE_BYTES;
             const uint32_t sB = sA + A_STAGE_BYTES;
             if constexpr (!A_MN) {
@@ -289,6 +312,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             }
 #pragma unroll
             for (int h = 0; h < NW; ++h) {
+              if (h >= nh) break;
               if constexpr (!B_MN) {
                 tma_load_2d_g<CG>(sB + h * B_HALF_BYTES, &p.tmB, p.b_k0 + kb * BK, b_row + h * BN, fb, p.b_policy);
               } else {
@@ -320,7 +344,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int item = worker; item < total_items; item += workers) {
-        const TileItem it = decode_item<EPI>(sc, item);
+        int h0, nh;
+        const TileItem it = get_item(item, h0, nh);
         for (int t = 0; t < it.ncount; ++t) {
           if constexpr (CG == 2)
             mbar_wait_cluster(tempty_bar(acc), acc_phase ^ 1u);
@@ -338,6 +363,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               const uint64_t adesc = make_smem_desc(sA + k * A_KADV, A_LBO, 1024);
 #pragma unroll
               for (int h = 0; h < NW; ++h) {
+                if (h >= nh) break;
                 const uint64_t bdesc = make_smem_desc(sB + h * B_HALF_BYTES + k * B_KADV, B_LBO, 1024);
                 umma_bf16<CG>(d_tmem + h * BN, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
               }
@@ -382,7 +408,8 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
     }
 
     for (int item = worker; item < total_items; item += workers) {
-      const TileItem it = decode_item<EPI>(sc, item);
+      int h0, nh;
+      const TileItem it = get_item(item, h0, nh);
       const int m_tile = (CG == 2) ? (2 * it.m + static_cast<int>(cta_rank)) : it.m;
       const bool m_ok = (CG == 1) || (m_tile < tiles_m_real);  // odd tile count: the pair's 2nd tile is a phantom
       const int row = m_tile * BM + row_in_tile;  // row of this thread (relative to the plan's row0)
@@ -577,7 +604,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         } else if constexpr (EPI == EPI_BF16) {
 #pragma unroll 1
-          for (int c = 0; c < BNW / 64; ++c) {
+          for (int c = 0; c < nh * (BN / 64); ++c) {
             uint32_t w[32];
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
@@ -590,7 +617,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
               for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
             }
-            if (c == BNW / 64 - 1) {
+            if (c == nh * (BN / 64) - 1) {
               tc_fence_before();
               __syncwarp();
               if (lane == 0) release_acc<CG>(tempty_bar(acc));
@@ -602,7 +629,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
-              const int cc = p.c_c0 + nt * BNW + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
+              const int cc = p.c_c0 + nt * BNW + h0 * BN + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (sc.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)
@@ -615,7 +642,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         } else {  // EPI_F32
 #pragma unroll 1
-          for (int c = 0; c < BNW / 32; ++c) {
+          for (int c = 0; c < nh * (BN / 32); ++c) {
             uint32_t w[32];
             {
               float v[32];
@@ -623,7 +650,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
               for (int j = 0; j < 32; ++j) w[j] = zero_acc ? 0u : __float_as_uint(v[j]);
             }
-            if (c == BNW / 32 - 1) {
+            if (c == nh * (BN / 32) - 1) {
               tc_fence_before();
               __syncwarp();
               if (lane == 0) release_acc<CG>(tempty_bar(acc));
@@ -635,7 +662,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             fence_proxy_async_smem();
             named_bar_sync(1, EPI_THREADS);
             if (issuer && m_ok) {
-              const int cc = p.c_c0 + nt * BNW + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
+              const int cc = p.c_c0 + nt * BNW + h0 * BN + c * 32, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
               if (sc.c_reduce)
                 tma_reduce_add_2d(&p.tmC, buf, cc, cr);
               else if (p.store_policy)

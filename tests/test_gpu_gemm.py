@@ -6,8 +6,10 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
+# (4864, 2048, 320): 19 m-pairs x 4 wide n-tiles = 76 items on 74 CTA pairs -> 74 wide items + 2 x 2 half items
+# (tail splitting of the 256x512 schedule); (1000, 2048, 520): 16 items, all of them split
 SHAPES = [(128, 256, 64), (128, 256, 256), (256, 512, 192), (200, 264, 136), (8, 8, 8), (1000, 2048, 520),
-          (384, 1024, 2048)]
+          (384, 1024, 2048), (4864, 2048, 320), (4904, 1800, 136)]
 
 
 def _mk(shape, seed):
