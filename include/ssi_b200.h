@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 103
+#define SSI_B200_ABI_VERSION 104
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -180,6 +180,9 @@ int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle);
 int ssi_b200_dp_open(const void* ipc_handle, void** ptr);
 int ssi_b200_dp_close(void* ptr);
 int ssi_b200_dp_free(void* ptr);
+/* Synchronising check (set-up / tear-down class): *timed_out != 0 if a wait inside dp_exchange gave up after 20 s
+ * because a peer never arrived (its process died); the gradients of that step are then invalid. */
+int ssi_b200_dp_status(const void* own_buf, int* timed_out);
 int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, uint32_t epoch,
                          const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW, void* stream);
 

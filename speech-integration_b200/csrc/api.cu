@@ -7,6 +7,7 @@
 
 #include <atomic>
 #include <cstdarg>
+#include <cstddef>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -974,6 +975,15 @@ int ssi_b200_dp_close(void* ptr) {
 int ssi_b200_dp_free(void* ptr) {
   SSI_CHECK_ARG(ptr, "null pointer argument");
   SSI_CUDA(cudaFree(ptr));
+  return 0;
+}
+
+int ssi_b200_dp_status(const void* own_buf, int* timed_out) {
+  SSI_CHECK_ARG(own_buf && timed_out, "null pointer argument");
+  unsigned int v = 0;
+  SSI_CUDA(cudaMemcpy(&v, static_cast<const char*>(own_buf) + offsetof(ssi::DpCtrl, timed_out), sizeof(v),
+                      cudaMemcpyDeviceToHost));
+  *timed_out = static_cast<int>(v);
   return 0;
 }
 

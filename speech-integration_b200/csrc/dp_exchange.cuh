@@ -35,7 +35,9 @@ struct DpCtrl {
   unsigned int arrive_a[DP_MAX_WORLD];  // written by peers: epoch of their last "dW_acc complete"
   unsigned int arrive_b[DP_MAX_WORLD];  // written by peers: epoch of their last "slice reduced"
   unsigned int blocks_done;             // local: blocks of dp_reduce_kernel that finished (reset by the last one)
+  unsigned int timed_out;               // local: set when a wait gave up (a peer never arrived): results are invalid
 };
+constexpr unsigned long long DP_WAIT_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;  // a dead peer must not hang the GPU
 
 struct DpPeers {
   char* buf[DP_MAX_WORLD];  // exchange buffer of every rank as mapped in THIS process (own buffer included)
@@ -66,11 +68,27 @@ __device__ __forceinline__ uint4 ld_peer_u4(const uint4* p) {
   return v;
 }
 
-// wait until every peer's slot in `flags` (this rank's own ctrl block) has reached `epoch`
-__device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world, int rank, unsigned int epoch) {
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// wait until every peer's slot in `flags` (this rank's own ctrl block) has reached `epoch`; gives up after
+// DP_WAIT_TIMEOUT_NS and records it in *timed_out (checked by the host with ssi_b200_dp_status)
+__device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world, int rank, unsigned int epoch,
+                                            unsigned int* timed_out) {
   if (threadIdx.x < static_cast<unsigned>(world) && static_cast<int>(threadIdx.x) != rank) {
     // epochs only grow; the signed difference keeps the comparison valid across 32-bit wrap-around
-    while (static_cast<int>(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) __nanosleep(64);
+    const unsigned long long t0 = global_timer_ns();
+    unsigned int spins = 0;
+    while (static_cast<int>(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
+      __nanosleep(64);
+      if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > DP_WAIT_TIMEOUT_NS) {
+        *timed_out = 1u;
+        break;
+      }
+    }
   }
   __syncthreads();
 }
@@ -87,7 +105,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, in
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_a[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_a, WORLD, rank, epoch);
+  dp_wait_all(ctrl->arrive_a, WORLD, rank, epoch, &ctrl->timed_out);
 
   const float ratio = grad_ratio(grad_out, grad_hint);
   const long long begin = static_cast<long long>(rank) * slice_f4;
@@ -147,8 +165,8 @@ template <int WORLD>
 __global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, int rank, long long slice_f4,
                                                                long long total_f4, unsigned int epoch,
                                                                uint2* __restrict__ dW) {
-  const DpCtrl* ctrl = reinterpret_cast<const DpCtrl*>(peers.buf[rank]);
-  dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch);
+  DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
+  dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch, &ctrl->timed_out);
   // bf16 slices move as 16-byte words: 2 of the fp32-quad units per word (slice_f4 is even, see the host side)
   const long long slice_u4 = slice_f4 / 2, total_u4 = total_f4 / 2;
   const long long stride = static_cast<long long>(gridDim.x) * DP_THREADS;

@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 103
+ABI_VERSION = 104
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -67,6 +67,7 @@ SYMBOLS = {
     "ssi_b200_dp_open": (c_int, [c_void_p, POINTER(c_void_p)]),
     "ssi_b200_dp_close": (c_int, [c_void_p]),
     "ssi_b200_dp_free": (c_int, [c_void_p]),
+    "ssi_b200_dp_status": (c_int, [c_void_p, POINTER(c_int)]),
     "ssi_b200_dp_exchange": (
         c_int,
         [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_int,

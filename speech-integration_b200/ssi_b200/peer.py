@@ -100,10 +100,19 @@ class TiedGradExchange:
         _lib.check(rc, "dp_exchange")
         return dW
 
+    def timed_out(self) -> bool:
+        """True if a wait inside an exchange gave up because a peer never arrived (synchronises)."""
+        flag = ctypes.c_int(0)
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().ssi_b200_dp_status(self._own, ctypes.byref(flag)), "dp_status")
+        return bool(flag.value)
+
     def close(self) -> None:
         if self._own is None:
             return
         torch.cuda.synchronize(self.device)
+        if self.timed_out():
+            raise RuntimeError("ssi_b200.peer: an exchange timed out waiting for a peer; gradients were invalid")
         if dist.is_initialized():
             dist.barrier(group=self.group)  # nobody may unmap while a peer can still read
         lib = _lib.load()
