@@ -49,7 +49,7 @@ const char* ssi_b200_last_error(void);
 int64_t ssi_b200_launch_count(void);
 
 /* Tuning knobs (also read once from the environment as SSI_B200_<NAME>): "g_cap_mib" = size cap of the bf16
- * logits/dlogits block scratch in MiB (default 4096), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx",
+ * logits/dlogits block scratch in MiB (default 4608), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx",
  * "store_hint". Workspace sizes depend on g_cap_mib: query them again after changing it. */
 int ssi_b200_set_option(const char* name, int64_t value);
 

@@ -271,7 +271,9 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
 
 // Tuning knobs (environment, read once): for experiments from bench.py without rebuilding.
 struct Tune {
-  int64_t g_cap_elems = int64_t(1) << 31;  // logits / dlogits block scratch cap: 4 GiB of bf16
+  // logits / dlogits block scratch cap: 4.5 GiB of bf16 -- the 16,384 rows a rank holds when the 64 x 2048 batch
+  // is split over 8 GPUs fit ONE row chunk at V = 133,258 (then the whole dX contraction hides the exchange)
+  int64_t g_cap_elems = int64_t(4608) << 19;
   int64_t g_tiles = 0;                     // force the block width (256-column tiles); 0 = auto
   int group_m_grad = 16, group_m_dw = 1, group_m_dx = 1;  // m-tiles per raster group (1 = n-fastest)
   int store_hint = 0;  // 1 = evict-first L2 policy on the dlogits / dW / dX tile stores
