@@ -694,17 +694,22 @@ __global__ void __launch_bounds__(256) scatter_reduce_kernel(const __nv_bfloat16
 #pragma unroll
       for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
     int run_start = 0;
-    for (int i = 0; i < cnt; ++i) {
-      const uint32_t key = __shfl_sync(0xffffffffu, my_key, i);
-      const uint32_t row = __shfl_sync(0xffffffffu, my_row, i);
-      const uint32_t nkey = (i + 1 < cnt) ? __shfl_sync(0xffffffffu, my_key, (i + 1) & 31) : KEY_NONE;
+    // software pipeline: the 8 x 16-byte loads of row i + 1 are in flight while row i is accumulated
+    uint4 u[8], un[8];
+    auto load_row = [&](int i, uint4 (&dst)[8]) {
+      const uint32_t row = __shfl_sync(0xffffffffu, my_row, i & 31);
       const __nv_bfloat16* src = dH + static_cast<size_t>(row) * D + d0;
-      uint4 u[8];
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         const int col = g * 256 + lane * 8;
-        u[g] = (col < dcols) ? __ldg(reinterpret_cast<const uint4*>(src + col)) : make_uint4(0, 0, 0, 0);
+        dst[g] = (col < dcols) ? __ldg(reinterpret_cast<const uint4*>(src + col)) : make_uint4(0, 0, 0, 0);
       }
+    };
+    load_row(0, u);
+    for (int i = 0; i < cnt; ++i) {
+      const uint32_t key = __shfl_sync(0xffffffffu, my_key, i);
+      const uint32_t nkey = (i + 1 < cnt) ? __shfl_sync(0xffffffffu, my_key, (i + 1) & 31) : KEY_NONE;
+      if (i + 1 < cnt) load_row(i + 1, un);
 #pragma unroll
       for (int g = 0; g < 8; ++g) {
         float f[8];
@@ -712,6 +717,8 @@ __global__ void __launch_bounds__(256) scatter_reduce_kernel(const __nv_bfloat16
 #pragma unroll
         for (int e = 0; e < 8; ++e) acc[g][e] += f[e];
       }
+#pragma unroll
+      for (int g = 0; g < 8; ++g) u[g] = un[g];
       const bool end_of_run = (i == cnt - 1) || (nkey != key);
       if (end_of_run) {
         const bool open_left = (run_start == 0) && (prev_key == key);
