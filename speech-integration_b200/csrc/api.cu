@@ -280,6 +280,7 @@ struct Tune {
   int k1_hints = 0, dw_hints = 0, dx_hints = 0;  // operand L2 policies: 10 * A + B; 1 evict-first, 2 evict-last
   int lockstep = 64;   // k-blocks between lockstep sync points of the dW / dX contractions (0 = off)
   int cta_group = 2;   // 2 = CTA pairs (tcgen05 cta_group::2, 256x256 tiles), 1 = single-CTA 128x256 tiles
+  int lockstep_k1 = 1;  // single-pass K1: lockstep of the vocabulary sweep (one sync point per tile); 0 = off
   int tail_split = 1;  // wide tiles: split the items of an at most half-full last wave into 256x256 halves
   int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
 };
@@ -297,6 +298,7 @@ Tune& tune() {
     if (const char* e = getenv("SSI_B200_LOCKSTEP")) x.lockstep = atoi(e);
     if (const char* e = getenv("SSI_B200_DW_HINTS")) x.dw_hints = atoi(e);
     if (const char* e = getenv("SSI_B200_DX_HINTS")) x.dx_hints = atoi(e);
+    if (const char* e = getenv("SSI_B200_LOCKSTEP_K1")) x.lockstep_k1 = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_TAIL_SPLIT")) x.tail_split = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
@@ -462,6 +464,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "lockstep")) t.lockstep = static_cast<int>(value);
   else if (!strcmp(name, "dw_hints")) t.dw_hints = static_cast<int>(value);
   else if (!strcmp(name, "dx_hints")) t.dx_hints = static_cast<int>(value);
+  else if (!strcmp(name, "lockstep_k1")) t.lockstep_k1 = value ? 1 : 0;
   else if (!strcmp(name, "tail_split")) t.tail_split = value ? 1 : 0;
   else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
@@ -711,7 +714,7 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
   const int64_t* nvt = n_valid_total ? n_valid_total : n_valid;
   unsigned int* sync_area = reinterpret_cast<unsigned int*>(wsb + f.off_sync);
   const int lockstep = tune().lockstep;
-  if (lockstep > 0) SSI_CUDA(cudaMemsetAsync(sync_area, 0, SYNC_AREA_BYTES, st));
+  if (lockstep > 0 || tune().lockstep_k1) SSI_CUDA(cudaMemsetAsync(sync_area, 0, SYNC_AREA_BYTES, st));
 
   {
     ProfScope ps(CAT_AUX, st);
@@ -757,6 +760,7 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
       p.part_m = part_m, p.part_l = part_l, p.part_z = part_z;
       p.part_stride = static_cast<int>(rows_cap);
       set_hints(p, tune().k1_hints);
+      if (tune().lockstep_k1) p.sync_ctr = sync_area + 256 + ch, p.sync_every = 1;
       if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
         return r;
     }

@@ -271,6 +271,12 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const int sync_T = throttle ? p.sync_every : 0x7fffffff;
       const int sync_pts = throttle ? (sc.k_blocks - 1) / sync_T : 0;  // points at kb = T, 2T, ... < k_blocks
       unsigned int sync_base = 0;                                       // arrivals of all earlier rounds
+      // K1 (LSE epilogues): the items of one round sweep their vocabulary tiles together -- one sync point per tile
+      // after the first (arrive at its first k-block, wait at its middle).  Splits are ragged, so an item with
+      // fewer tiles than the longest posts the arrivals it will never make when it ends ("catch-up").
+      const bool throttle_v = is_lse_epi<EPI>() && p.sync_ctr != nullptr && p.sync_every > 0 && cta_rank == 0 &&
+                              workers > 1 && sc.k_blocks >= 2;
+      const int v_pts = throttle_v ? sc.vtiles_per_split - 1 : 0;
       for (int item = worker; item < total_items; item += workers) {
         int h0, nh;
         const TileItem it = get_item(item, h0, nh);
@@ -281,6 +287,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           const int b_row = p.b_r0 + nt * BNW + h0 * BN + static_cast<int>(cta_rank) * BN_CTA;
           int next_arrive = sync_T, next_wait = 0x7fffffff, sync_j = 0;
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
+            if (throttle_v && t >= 1) {
+              if (kb == 0) atomicAdd(p.sync_ctr, 1u);
+              if (kb == (sc.k_blocks >> 1)) {
+                const unsigned int target = sync_base + static_cast<unsigned int>(t) * round_workers;
+                while (ld_acquire_gpu(p.sync_ctr) < target) {
+                }
+              }
+            }
             if (throttle) {
               if (kb == next_arrive) {
                 atomicAdd(p.sync_ctr, 1u);
@@ -329,6 +343,11 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           }
         }
         sync_base += static_cast<unsigned int>(sync_pts) * round_workers;
+        if (throttle_v) {
+          const int missing = v_pts - (it.ncount - 1);
+          if (missing > 0) atomicAdd(p.sync_ctr, static_cast<unsigned int>(missing));
+          sync_base += static_cast<unsigned int>(v_pts) * round_workers;
+        }
       }
     }
   } else if (warp == 1) {
