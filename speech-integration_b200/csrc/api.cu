@@ -246,7 +246,7 @@ struct FwdPlan {
   int64_t n_pad;
   int tiles_m, vtiles_total, combine_blocks;
   CompactWs cw;
-  size_t off_m, off_l, off_z, off_bl, off_bc, bytes;
+  size_t off_m, off_l, off_z, off_bl, off_bc, off_sync, bytes;
 };
 
 FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
@@ -265,6 +265,7 @@ FwdPlan plan_fwd(int64_t N, int64_t V, int64_t D) {
   f.off_z = o, o += part;
   f.off_bl = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(float), 256);
   f.off_bc = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(int), 256);
+  f.off_sync = o, o += 256;  // lockstep counter of the forward-only K1
   f.bytes = o;
   return f;
 }
@@ -538,6 +539,10 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   p.part_l = reinterpret_cast<float*>(wsb + f.off_l);
   p.part_z = reinterpret_cast<float*>(wsb + f.off_z);
   p.part_stride = static_cast<int>(f.n_pad);
+  if (tune().lockstep_k1) {
+    SSI_CUDA(cudaMemsetAsync(wsb + f.off_sync, 0, 256, st));
+    p.sync_ctr = reinterpret_cast<unsigned int*>(wsb + f.off_sync), p.sync_every = 1;
+  }
   if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse", CAT_LSE, di->sms)) return r;
 
   ProfScope ps_aux(CAT_AUX, st);
