@@ -905,11 +905,13 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
   if (!(phases & 2)) return 0;
   float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
   ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
-  const int grid = static_cast<int>(ceil_div(s.nwarps, 8));
-  ssi::scatter_reduce_kernel<OutT><<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
+  // 128-thread blocks (4 warps x ~190 registers = 24 K registers): small enough to co-reside with a persistent
+  // tensor-core CTA (K1: 192 threads x 128 registers) when this runs on a side stream beside the first contraction
+  const int grid = static_cast<int>(ceil_div(s.nwarps, 4));
+  ssi::scatter_reduce_kernel<OutT><<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
                                                          static_cast<uint32_t>(V), static_cast<int>(D), dW, partial, info);
   SSI_LAUNCH_OK("scatter_reduce");
-  ssi::scatter_fixup_kernel<OutT><<<grid, 256, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
+  ssi::scatter_fixup_kernel<OutT><<<grid, 128, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
                                                         static_cast<int>(D), dW);
   SSI_LAUNCH_OK("scatter_fixup");
   return 0;
