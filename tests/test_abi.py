@@ -47,3 +47,31 @@ def test_host_side_argument_errors_need_no_gpu():
     assert fwd > 0 and bwd >= 32768 * 256 * 2 and sc > 32768 * 4 * 4
     # null pointers are rejected before any CUDA call
     assert lib.ssi_b200_lmhead_ce_fwd(None, None, None, 1, 1, 64, -100, None, None, None, None, 0, None) < 0
+
+
+def test_data_parallel_and_next_row_entry_points_validate_on_the_host():
+    """Size queries and argument errors of the exchange and of the §8(f) rows need no GPU."""
+    from ctypes import POINTER, byref, c_int64, c_size_t
+
+    from ssi_b200 import _lib
+
+    lib = _lib.load()
+    nbytes, off = c_size_t(0), c_size_t(0)
+    V, D = 133258, 2048
+    assert lib.ssi_b200_dp_buffer_bytes(V, D, 8, byref(nbytes), byref(off)) == 0
+    slice_rows = -(-V // 8)
+    assert off.value == 4096 and nbytes.value == 4096 + V * D * 4 + slice_rows * D * 2
+    assert lib.ssi_b200_dp_buffer_bytes(V, D, 9, byref(nbytes), byref(off)) < 0  # one NVSwitch node: <= 8 ranks
+    assert b"world size" in lib.ssi_b200_last_error()
+    assert lib.ssi_b200_dp_exchange(None, 0, 2, V, D, 1, None, None, None, 0, None) < 0
+    b = c_size_t(0)
+    assert lib.ssi_b200_rmsnorm_bwd_workspace_bytes(32768, D, byref(b)) == 0 and b.value >= 148 * 2 * 8 * D * 4
+    assert lib.ssi_b200_rmsnorm_fwd(None, None, 1e-6, 8, 64, None, None, None) < 0
+    assert lib.ssi_b200_grad_scale_sqnorm_workspace_bytes(byref(b)) == 0 and b.value > 0
+    lo = (c_int64 * 16)(*range(16))
+    rc = lib.ssi_b200_label_shift_count_types(1, 1, 2, 8, -100, lo, lo, 16, 0, 1, 1, 1, None)  # 16 ranges > 15
+    assert rc < 0 and b"n_ranges" in lib.ssi_b200_last_error()
+    with pytest.raises(RuntimeError):
+        _lib.set_option("no_such_option", 1)
+    for name, val in (("lockstep_k1", 1), ("tail_split", 1), ("wide_dw", 2), ("wide_dx", 2), ("g_cap_mib", 4608)):
+        _lib.set_option(name, val)
