@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 104
+#define SSI_B200_ABI_VERSION 105
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -130,6 +130,18 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
                                    int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                    float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
                                    void* dw_acc_init_event, void* dw_ready_event);
+
+/* The same with the final RMSNorm (tt/torchtune/modules/rms_norm.py:38-43, applied at transformer.py:653) fused in:
+ * when `norm_scale` (bf16 [D]) is not NULL, X holds the PRE-norm hidden states; the norm is applied while the valid
+ * rows are gathered (no separate pass), its backward runs while the compact dX rows are scattered back, so dX is
+ * d(pre-norm h) and `dscale` [D] fp32 receives the gradient of the scale (for the upstream gradient grad_hint;
+ * scale it by grad_out / grad_hint like dW_acc). norm_scale == NULL: identical to ssi_b200_lmhead_ce_fwd_grad_dp. */
+int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                     const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                     int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                     float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
+                                     void* dw_acc_init_event, void* dw_ready_event, const void* norm_scale,
+                                     float norm_eps, float* dscale);
 
 /*
  * Backward of single-pass mode: ratio = grad_out / grad_hint (exactly 1 when the hint was right);

@@ -368,9 +368,11 @@ struct SpPlan {
   int64_t n_pad, vpad;
   int tiles_m, vtiles_total, combine_blocks, t_max, chunks_max;
   CompactWs cw;
-  size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_dxc, off_s, bytes;
+  size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_rstd, off_dsp, off_dxc, off_s, bytes;
 };
 constexpr size_t SYNC_AREA_BYTES = 4096;
+constexpr int NORM_BWD_BLOCKS = 148 * 2;            // grid of the fused norm-backward scatter
+constexpr int NORM_BWD_PARTS = NORM_BWD_BLOCKS * 8;  // one dscale partial row per warp
 
 int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   SpPlan f;
@@ -399,6 +401,9 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   f.off_bl = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(float), 256);
   f.off_bc = o, o += align_up(static_cast<size_t>(f.combine_blocks) * sizeof(int), 256);
   f.off_sync = o, o += SYNC_AREA_BYTES;
+  // fused final RMSNorm (fwd_grad_norm): per-row rstd of the compact rows, per-warp partial rows of dscale
+  f.off_rstd = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
+  f.off_dsp = o, o += align_up(static_cast<size_t>(NORM_BWD_PARTS) * D * sizeof(float), 256);
   f.off_dxc = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
   f.off_s = o, o += align_up(static_cast<size_t>(f.t_max) * ssi::BM * f.vpad * 2, 1024);
   f.bytes = o;
@@ -688,7 +693,20 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
                                    int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
                                    float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
                                    void* dw_acc_init_event, void* dw_ready_event) {
+  return ssi_b200_lmhead_ce_fwd_grad_norm(X, W, labels, grad_hint, n_valid_total, N, V, D, ignore_index, lse, loss_out,
+                                          n_valid, dX, dW_acc, ws, ws_bytes, stream, accumulate_dW_acc,
+                                          dw_acc_init_event, dw_ready_event, nullptr, 0.f, nullptr);
+}
+
+int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                     const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                     int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                     float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
+                                     void* dw_acc_init_event, void* dw_ready_event, const void* norm_scale,
+                                     float norm_eps, float* dscale) {
   if (int r = check_common(X, W, N, V, D)) return r;
+  SSI_CHECK_ARG(!norm_scale || (dscale && (reinterpret_cast<uintptr_t>(norm_scale) & 15) == 0 && D <= 8192),
+                "fused norm needs a 16-byte aligned scale, a dscale output and D <= 8192");
   SSI_CHECK_ARG(labels && grad_hint && lse && loss_out && n_valid && dX && dW_acc && ws, "null pointer argument");
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0,
                 "dX / dW_acc must be 16-byte aligned");
@@ -730,9 +748,17 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
                                                   n_valid, cta_group(),
                                                   (cta_group() == 2 && tune().wide_dx == 2) ? tune().tail_split : 0);
     SSI_LAUNCH_OK("compact_scan");
-    ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
-                                                         static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
-                                                         nullptr);
+    if (norm_scale) {  // X holds PRE-norm hidden states: the final RMSNorm is applied while gathering the valid rows
+      ssi::gather_rows_norm_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
+                                                                static_cast<int>(D / 8),
+                                                                static_cast<const uint4*>(norm_scale), norm_eps,
+                                                                static_cast<uint4*>(Xc),
+                                                                reinterpret_cast<float*>(wsb + f.off_rstd));
+    } else {
+      ssi::gather_rows_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(X), idx, dplan,
+                                                           static_cast<int>(D / 8), static_cast<uint4*>(Xc), nullptr,
+                                                           nullptr);
+    }
     SSI_LAUNCH_OK("gather_rows");
   }
 
@@ -826,6 +852,28 @@ int ssi_b200_lmhead_ce_fwd_grad_dp(const void* X, const void* W, const int64_t* 
   SSI_LAUNCH_OK("stash_finish");
   ssi::loss_finalize_kernel<<<1, 256, 0, st>>>(blk_loss, blk_cnt, f.combine_blocks, loss_out, n_valid);
   SSI_LAUNCH_OK("loss_finalize");
+  if (norm_scale) {
+    // backward of the fused norm while the compact dX rows go back to their positions: dX = d(pre-norm h)
+    const int row_u4 = static_cast<int>(D / 8);
+    const int maxj = (row_u4 + 31) / 32;
+    float* partial = reinterpret_cast<float*>(wsb + f.off_dsp);
+    const float* rstd_c = reinterpret_cast<const float*>(wsb + f.off_rstd);
+#define SSI_NORM_SCATTER(J)                                                                                         \
+  ssi::dx_scatter_norm_bwd_kernel<J><<<NORM_BWD_BLOCKS, 256, 0, st>>>(                                              \
+      static_cast<const uint4*>(dXc), pos, static_cast<const uint4*>(X), static_cast<const uint4*>(norm_scale),     \
+      rstd_c, static_cast<int>(N), row_u4, static_cast<uint4*>(dX), partial)
+    if (maxj <= 2) SSI_NORM_SCATTER(2);
+    else if (maxj <= 4) SSI_NORM_SCATTER(4);
+    else if (maxj <= 8) SSI_NORM_SCATTER(8);
+    else if (maxj <= 16) SSI_NORM_SCATTER(16);
+    else SSI_NORM_SCATTER(32);
+#undef SSI_NORM_SCATTER
+    SSI_LAUNCH_OK("dx_scatter_norm_bwd");
+    ssi::rmsnorm_dscale_reduce_kernel<<<static_cast<int>(ceil_div(D, 32)), 256, 0, st>>>(partial, NORM_BWD_PARTS,
+                                                                                       static_cast<int>(D), dscale);
+    SSI_LAUNCH_OK("rmsnorm_dscale_reduce");
+    return 0;
+  }
   ssi::dx_scatter_bf16_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(dXc), pos, static_cast<int>(N),
                                                            static_cast<int>(D / 8), static_cast<uint4*>(dX));
   SSI_LAUNCH_OK("dx_scatter");

@@ -279,4 +279,125 @@ __global__ void __launch_bounds__(256) embedding_gather_kernel(const uint4* __re
   }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// f1 fused into the path (single-pass mode with a norm scale): the final RMSNorm is applied WHILE the valid rows
+// are gathered into X_c (no separate pass over the hidden states), and its backward runs WHILE the compact dX rows
+// are scattered back to their positions, so the path hands back d(pre-norm h) directly.
+// ---------------------------------------------------------------------------------------------------
+// X_c[c, :] = rmsnorm(X[idx[c], :]) for c < n_valid (zeros for tile padding rows); rstd_c[c] kept for backward.
+__global__ void __launch_bounds__(256) gather_rows_norm_kernel(const uint4* __restrict__ X, const int* __restrict__ idx,
+                                                               const DevPlan* __restrict__ plan, int row_u4,
+                                                               const uint4* __restrict__ scale, float eps,
+                                                               uint4* __restrict__ Xc, float* __restrict__ rstd_c) {
+  const int n_valid = plan->n_valid;
+  const int rows = plan->tiles_m * 128;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float inv_d = 1.f / static_cast<float>(row_u4 * 8);
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < rows; c += warps) {
+    uint4* dst = Xc + static_cast<size_t>(c) * row_u4;
+    if (c >= n_valid) {
+      for (int j = lane; j < row_u4; j += 32) dst[j] = make_uint4(0, 0, 0, 0);
+      if (lane == 0) rstd_c[c] = 0.f;
+      continue;
+    }
+    const uint4* src = X + static_cast<size_t>(idx[c]) * row_u4;
+    float ss = 0.f;
+    for (int j = lane; j < row_u4; j += 32) {
+      float f[8];
+      bf16x8_to_f32(__ldg(src + j), f);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) ss = fmaf(f[e], f[e], ss);
+    }
+    ss = warp_sum(ss);
+    const float rs = rsqrtf(ss * inv_d + eps);
+    if (lane == 0) rstd_c[c] = rs;
+    for (int j = lane; j < row_u4; j += 32) {
+      float f[8], g[8];
+      bf16x8_to_f32(__ldg(src + j), f);
+      bf16x8_to_f32(__ldg(scale + j), g);
+      uint4 o;
+      o.x = pack_bf16x2((f[0] * rs) * g[0], (f[1] * rs) * g[1]);
+      o.y = pack_bf16x2((f[2] * rs) * g[2], (f[3] * rs) * g[3]);
+      o.z = pack_bf16x2((f[4] * rs) * g[4], (f[5] * rs) * g[5]);
+      o.w = pack_bf16x2((f[6] * rs) * g[6], (f[7] * rs) * g[7]);
+      dst[j] = o;
+    }
+  }
+}
+
+// dX[r, :] = rmsnorm_backward(dy = dXc[pos[r], :], x = X[r, :]) for valid rows, zeros for ignored rows; dscale
+// partials per warp as in rmsnorm_bwd_kernel (summed by rmsnorm_dscale_reduce_kernel).
+template <int MAXJ>
+__global__ void __launch_bounds__(256) dx_scatter_norm_bwd_kernel(const uint4* __restrict__ dXc,
+                                                                  const int* __restrict__ pos,
+                                                                  const uint4* __restrict__ X,
+                                                                  const uint4* __restrict__ scale,
+                                                                  const float* __restrict__ rstd_c, int n, int row_u4,
+                                                                  uint4* __restrict__ dX, float* __restrict__ partial) {
+  const int lane = threadIdx.x & 31;
+  const int warp_g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float inv_d = 1.f / static_cast<float>(row_u4 * 8);
+  float ds[MAXJ][8];
+#pragma unroll
+  for (int k = 0; k < MAXJ; ++k)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ds[k][e] = 0.f;
+  for (int r = warp_g; r < n; r += warps) {
+    const int c = pos[r];
+    uint4* pd = dX + static_cast<size_t>(r) * row_u4;
+    if (c < 0) {
+      for (int j = lane; j < row_u4; j += 32) pd[j] = make_uint4(0, 0, 0, 0);
+      continue;
+    }
+    const uint4* py = dXc + static_cast<size_t>(c) * row_u4;
+    const uint4* px = X + static_cast<size_t>(r) * row_u4;
+    const float rs = rstd_c[c];
+    float cc = 0.f;
+#pragma unroll
+    for (int k = 0; k < MAXJ; ++k) {
+      const int j = lane + 32 * k;
+      if (j < row_u4) {
+        float fy[8], fx[8], g[8];
+        bf16x8_to_f32(py[j], fy);
+        bf16x8_to_f32(__ldg(px + j), fx);
+        bf16x8_to_f32(__ldg(scale + j), g);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          cc = fmaf(fy[e] * g[e], fx[e], cc);
+          ds[k][e] = fmaf(fy[e] * fx[e], rs, ds[k][e]);
+        }
+      }
+    }
+    cc = warp_sum(cc) * inv_d;
+    const float a = rs * rs * cc;
+#pragma unroll
+    for (int k = 0; k < MAXJ; ++k) {
+      const int j = lane + 32 * k;
+      if (j < row_u4) {
+        float fy[8], fx[8], g[8];
+        bf16x8_to_f32(py[j], fy);
+        bf16x8_to_f32(__ldg(px + j), fx);
+        bf16x8_to_f32(__ldg(scale + j), g);
+        uint4 o;
+        o.x = pack_bf16x2(rs * (fy[0] * g[0] - fx[0] * a), rs * (fy[1] * g[1] - fx[1] * a));
+        o.y = pack_bf16x2(rs * (fy[2] * g[2] - fx[2] * a), rs * (fy[3] * g[3] - fx[3] * a));
+        o.z = pack_bf16x2(rs * (fy[4] * g[4] - fx[4] * a), rs * (fy[5] * g[5] - fx[5] * a));
+        o.w = pack_bf16x2(rs * (fy[6] * g[6] - fx[6] * a), rs * (fy[7] * g[7] - fx[7] * a));
+        pd[j] = o;
+      }
+    }
+  }
+  float* pp = partial + static_cast<size_t>(warp_g) * row_u4 * 8;
+#pragma unroll
+  for (int k = 0; k < MAXJ; ++k) {
+    const int j = lane + 32 * k;
+    if (j < row_u4) {
+      *reinterpret_cast<float4*>(pp + j * 8) = make_float4(ds[k][0], ds[k][1], ds[k][2], ds[k][3]);
+      *reinterpret_cast<float4*>(pp + j * 8 + 4) = make_float4(ds[k][4], ds[k][5], ds[k][6], ds[k][7]);
+    }
+  }
+}
+
 }  // namespace ssi

@@ -76,21 +76,30 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
     ``grad_out / grad_hint`` (1 when the trainer announced its multiplier) and rounds dW once into ``.grad``."""
 
     @staticmethod
-    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint, grad_enabled=True):
+    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint, grad_enabled=True,
+                norm_scale=None, norm_eps=1e-6):
         ctx.holder = holder
+        ctx.dscale = None
         # `grad_enabled` is sampled by the caller: inside Function.forward grad mode is always off, and under
         # torch.no_grad() / inference_mode() (the eval path, ssi/eval.py:27-33) needs_input_grad still reports the
         # Parameter -- forming gradients there would triple the work of a forward-only call
-        ctx.with_grad = bool(grad_enabled and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]))
+        ctx.with_grad = bool(grad_enabled and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
+                                               or (norm_scale is not None and ctx.needs_input_grad[8])))
         if ctx.with_grad:
             hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
-            loss_out, lse, n_valid, dX, dW_acc = ops.lmhead_ce_fwd_grad(
+            out = ops.lmhead_ce_fwd_grad(
                 X, W, labels, hint, n_valid_override, ignore_index,
                 dW_acc=getattr(holder, "dw_acc_buffer", None), dw_ready_event=getattr(holder, "dw_ready_event", None),
                 accumulate_dW_acc=getattr(holder, "dw_acc_initialised", False),
-                dw_acc_init_event=getattr(holder, "dw_acc_init_event", None))
+                dw_acc_init_event=getattr(holder, "dw_acc_init_event", None),
+                norm_scale=norm_scale.detach() if norm_scale is not None else None, norm_eps=norm_eps)
+            loss_out, lse, n_valid, dX, dW_acc = out[:5]
+            if norm_scale is not None:  # X was the PRE-norm state: dX is its gradient, dscale the scale's
+                ctx.dscale, ctx.scale_dtype = out[5], norm_scale.dtype
             ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
         else:
+            if norm_scale is not None:  # forward only (eval): the stand-alone norm kernel, then K1
+                X = ops.rmsnorm_fwd(X, norm_scale.detach(), norm_eps, want_rstd=False)[0]
             loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
         if holder is not None:
             holder.last_loss_sum = loss_out[0:1]
@@ -107,6 +116,10 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         holder = ctx.holder
         dX, dW_acc, hint = ctx.dX, ctx.dW_acc, ctx.hint
         ctx.dX = ctx.dW_acc = None
+        dscale = None
+        if ctx.dscale is not None:  # gradient of the fused norm's scale, formed for `hint` like dX and dW_acc
+            dscale = (ctx.dscale * (g / hint)).to(ctx.scale_dtype)
+            ctx.dscale = None
         wparam = holder.weight_param() if holder is not None else None
         if holder is not None and getattr(holder, "defer_dw", False):
             # data-parallel peer exchange (ssi_b200.peer / PathStep): the SUMMED fp32 dW is rounded into .grad by
@@ -114,31 +127,40 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
             # here only dX is rescaled, and a wrong announcement is left visible instead of silently ignored.
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
             holder.grad_hint_mismatch = (g != hint)
-            return dX, None, None, None, None, None, None, None
+            return dX, None, None, None, None, None, None, None, dscale, None
         if wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr:
             acc = wparam.grad is not None
             if not acc:
                 wparam.grad = torch.empty_like(wparam)
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc)
-            return dX, None, None, None, None, None, None, None
+            return dX, None, None, None, None, None, None, None, dscale, None
         _, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint)
-        return dX, dW, None, None, None, None, None, None
+        return dX, dW, None, None, None, None, None, None, dscale, None
 
 
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                                ignore_index: int = -100, n_valid_total: torch.Tensor | None = None,
                                _holder=None, mode: str = "single_pass",
-                               grad_hint: torch.Tensor | None = None) -> torch.Tensor:
+                               grad_hint: torch.Tensor | None = None, norm_scale: torch.Tensor | None = None,
+                               norm_eps: float = 1e-6) -> torch.Tensor:
     """Functional form: ``hidden [N, D]`` bf16, ``weight [V, D]`` bf16, ``labels [N]`` int64 -> fp32 0-dim loss.
 
     ``mode``: ``"single_pass"`` (default; gradients formed during forward, 6 N V D flop) or ``"recompute"``
-    (forward keeps only the per-row logsumexp, backward recomputes the logits tiles, 8 N V D flop, no stash)."""
+    (forward keeps only the per-row logsumexp, backward recomputes the logits tiles, 8 N V D flop, no stash).
+
+    ``norm_scale`` (bf16 ``[D]`` Parameter) / ``norm_eps``: ``hidden`` is the PRE-norm state and the final RMSNorm
+    (tt/torchtune/modules/rms_norm.py:38-43) runs inside the path (single-pass mode: fused into its row gather and
+    dX scatter), with gradients for ``hidden`` and for the scale."""
     if mode == "recompute":
+        if norm_scale is not None:  # no fused form in recompute mode: the stand-alone norm kernels in front
+            from .model_hooks import _RMSNormFn
+
+            hidden = _RMSNormFn.apply(hidden, norm_scale, norm_eps)
         return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
     if mode != "single_pass":
         raise ValueError(f"ssi_b200: unknown mode {mode!r} (expected 'single_pass' or 'recompute')")
     return _FusedLinearCESinglePass.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, grad_hint,
-                                          torch.is_grad_enabled())
+                                          torch.is_grad_enabled(), norm_scale, norm_eps)
 
 
 class FusedLinearCrossEntropyLoss(nn.Module):
@@ -189,10 +211,24 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         self.dw_acc_init_event: torch.cuda.Event | None = None
         self.defer_dw: bool = False
         self.grad_hint_mismatch: torch.Tensor | None = None
+        object.__setattr__(self, "_norm", None)  # fused final RMSNorm (set_fused_norm); not a registered submodule
 
     @property
     def tied_module(self) -> nn.Module:
         return self._tied
+
+    def set_fused_norm(self, norm: nn.Module | None) -> None:
+        """Take over the model's final RMSNorm (``model.norm``, applied at tt/torchtune/modules/transformer.py:653):
+        ``norm`` must expose ``scale`` (bf16 ``[D]`` Parameter) and ``eps``.  The model then hands PRE-norm hidden
+        states to the loss (``install(model, fuse_norm=True)`` swaps ``model.norm`` for a passthrough that still
+        owns the Parameter, so ``norm.scale`` stays in the state dict and the optimizer)."""
+        if norm is not None and not (hasattr(norm, "scale") and hasattr(norm, "eps")):
+            raise AttributeError("ssi_b200: the fused norm needs `scale` and `eps` attributes (torchtune RMSNorm)")
+        object.__setattr__(self, "_norm", norm)
+
+    def _norm_args(self):
+        n = self._norm
+        return (None, 1e-6) if n is None else (n.scale, float(n.eps))
 
     def weight_param(self):
         w = self._tied.weight
@@ -202,7 +238,8 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         """Sum-reduced CE of one chunk of hidden states (mirrors ce_chunked_output_loss.py:35-43, which takes
         logits): returned so that ``training.compile_loss``-style wrappers that call it keep working."""
         loss = fused_linear_cross_entropy(hidden.reshape(-1, hidden.size(-1)), self._tied.weight,
-                                          labels.reshape(-1), self.ignore_index, None, self, self.mode, self.grad_hint)
+                                          labels.reshape(-1), self.ignore_index, None, self, self.mode, self.grad_hint,
+                                          *self._norm_args())
         return loss * self.last_n_valid[0].to(torch.float32)
 
     def forward(self, hidden: Union[torch.Tensor, Sequence[torch.Tensor]], labels: torch.Tensor) -> torch.Tensor:
@@ -222,7 +259,7 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         if lab.numel() != X.size(0):
             raise ValueError(f"labels ({tuple(labels.shape)}) do not match hidden rows ({X.size(0)})")
         return fused_linear_cross_entropy(X, W, lab, self.ignore_index, self.n_valid_total, self, self.mode,
-                                          self.grad_hint)
+                                          self.grad_hint, *self._norm_args())
 
 
 def make_torchtune_subclass():

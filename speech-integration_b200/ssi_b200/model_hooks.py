@@ -127,9 +127,23 @@ class RMSNormB200(nn.Module):
         return new
 
 
+class FusedNormPassthrough(nn.Module):
+    """Stands where ``model.norm`` stood when the final RMSNorm is fused into the loss: returns its input unchanged
+    but still OWNS the ``scale`` Parameter (state-dict key ``norm.scale``, optimizer membership unchanged)."""
+
+    def __init__(self, norm: nn.Module) -> None:
+        super().__init__()
+        self.normalized_shape = tuple(norm.scale.shape)
+        self.eps = norm.eps
+        self.scale = norm.scale
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return x
+
+
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
             replace_embedding: bool = True, mode: str | None = None,
-            replace_norm: bool = False) -> FusedLinearCrossEntropyLoss:
+            replace_norm: bool = False, fuse_norm: bool = False) -> FusedLinearCrossEntropyLoss:
     """Mirror of ``Trainer._setup_loss`` (ssi/trainer.py:299-304) for the fused path.
 
     Replaces ``model.output`` by a hidden passthrough, optionally swaps ``model.tok_embeddings`` for
@@ -137,9 +151,17 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     has it, and returns the loss module to use as ``loss_fn``. ``mode``: ``"single_pass"`` (default) or
     ``"recompute"``, see :func:`ssi_b200.loss.fused_linear_cross_entropy`.  ``replace_norm``: also swap the final
     ``model.norm`` (tt/torchtune/modules/transformer.py:653) for :class:`RMSNormB200`, sharing its ``scale``.
+    ``fuse_norm``: instead, fuse that norm into the loss (row gather / dX scatter of single-pass mode):
+    ``model.norm`` becomes a :class:`FusedNormPassthrough` and the model hands pre-norm hidden states to the loss.
     """
     norm = getattr(model, "norm", None)
-    if (replace_norm and norm is not None and hasattr(norm, "scale") and hasattr(norm, "eps")
+    fused_norm = None
+    if fuse_norm:
+        if norm is None or not (hasattr(norm, "scale") and hasattr(norm, "eps")):
+            raise AttributeError("ssi_b200.install(fuse_norm=True): model.norm has no `scale` / `eps`")
+        fused_norm = norm if isinstance(norm, FusedNormPassthrough) else FusedNormPassthrough(norm)
+        model.norm = fused_norm
+    elif (replace_norm and norm is not None and hasattr(norm, "scale") and hasattr(norm, "eps")
             and not isinstance(norm, RMSNormB200)):
         model.norm = RMSNormB200.from_norm(norm)
     emb = model.tok_embeddings
@@ -149,6 +171,8 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     model.output = HiddenPassthroughOutput(emb)
     cls = make_torchtune_subclass() or FusedLinearCrossEntropyLoss
     loss_fn = cls(emb, num_output_chunks=num_output_chunks, ignore_index=ignore_index, mode=mode)
+    if fused_norm is not None:
+        loss_fn.set_fused_norm(fused_norm)
     if hasattr(model, "set_num_output_chunks"):
         model.set_num_output_chunks(loss_fn.num_output_chunks)
     return loss_fn

@@ -115,7 +115,8 @@ def lmhead_ce_bwd(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, lse: t
 def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, grad_hint: torch.Tensor,
                        n_valid_total: torch.Tensor | None = None, ignore_index: int = -100,
                        dW_acc: torch.Tensor | None = None, dw_ready_event: torch.cuda.Event | None = None,
-                       accumulate_dW_acc: bool = False, dw_acc_init_event: torch.cuda.Event | None = None):
+                       accumulate_dW_acc: bool = False, dw_acc_init_event: torch.cuda.Event | None = None,
+                       norm_scale: torch.Tensor | None = None, norm_eps: float = 1e-6):
     """Single-pass mode: fused projection + CE forward that also forms the gradients (each logits tile is
     computed once). Returns ``(loss_out, lse, n_valid, dX, dW_acc)``; ``dX`` bf16 ``[N, D]`` and ``dW_acc`` fp32
     ``[V, D]`` are the gradients for an upstream gradient of ``grad_hint`` (fp32 device scalar);
@@ -125,6 +126,10 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     peer-visible exchange buffer); ``dw_ready_event``: recorded right after the last dW contraction;
     ``accumulate_dW_acc``: the caller initialised ``dW_acc`` and every dW contraction adds to it;
     ``dw_acc_init_event``: the stream waits for it right before the first dW contraction.
+
+    ``norm_scale`` (bf16 ``[D]``): ``X`` holds the PRE-norm hidden states and the final RMSNorm
+    (tt/torchtune/modules/rms_norm.py:38-43) is fused into the row gather / dX scatter of the path; ``dX`` is then
+    the gradient of the pre-norm states and a sixth value ``dscale`` (fp32 ``[D]``) is returned.
     """
     dev = _require_cuda(X, W, labels, grad_hint)
     N, V, D = _check_xw(X, W)
@@ -156,13 +161,23 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
             if not h:
                 raise ValueError("ssi_b200: event has no CUDA handle yet (record it once before first use)")
         evs.append(h)
+    dscale = None
+    if norm_scale is not None:
+        if (norm_scale.dtype != torch.bfloat16 or norm_scale.numel() != D or not norm_scale.is_contiguous()
+                or norm_scale.device != dev):
+            raise ValueError("ssi_b200: norm_scale must be a contiguous bf16 [D] tensor on the same device")
+        dscale = torch.empty(D, dtype=torch.float32, device=dev)
     with torch.cuda.device(dev):
-        rc = lib.ssi_b200_lmhead_ce_fwd_grad_dp(
+        rc = lib.ssi_b200_lmhead_ce_fwd_grad_norm(
             X.data_ptr(), W.data_ptr(), labels.data_ptr(), grad_hint.data_ptr(),
             n_valid_total.data_ptr() if n_valid_total is not None else None, N, V, D, int(ignore_index),
             lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), dX.data_ptr(), dW_acc.data_ptr(),
-            ws.data_ptr(), ws.numel(), _stream(dev), 1 if accumulate_dW_acc else 0, evs[0], evs[1])
+            ws.data_ptr(), ws.numel(), _stream(dev), 1 if accumulate_dW_acc else 0, evs[0], evs[1],
+            norm_scale.data_ptr() if norm_scale is not None else None, float(norm_eps),
+            dscale.data_ptr() if dscale is not None else None)
     _lib.check(rc, "lmhead_ce_fwd_grad")
+    if norm_scale is not None:
+        return loss_out, lse, n_valid, dX, dW_acc, dscale
     return loss_out, lse, n_valid, dX, dW_acc
 
 

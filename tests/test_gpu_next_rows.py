@@ -115,3 +115,51 @@ def test_embedding_gather_and_tied_embedding_forward():
     h.backward(dH.cuda())
     ref = oracle.embedding_grad(ids, dH, 3001)
     assert torch.allclose(emb.weight.grad.float().cpu(), ref, rtol=2 ** -7, atol=1e-2)
+
+
+@pytest.mark.parametrize("mode", ["single_pass", "recompute"])
+@pytest.mark.parametrize("B,S,V,D,cfg", [(3, 150, 3001, 256, "c2"), (2, 300, 5002, 2048, "c3")])
+def test_final_norm_fused_into_the_path(B, S, V, D, cfg, mode):
+    """install(fuse_norm=True) semantics: the loss takes PRE-norm hidden states plus the norm's scale and returns the
+    loss and the gradients the reference gets from norm -> projection -> chunked CE (transformer.py:653, 499-502,
+    ce_chunked_output_loss.py:45-83), including d(scale).  Oracle in fp32 on the same bf16 inputs."""
+    import ssi_b200
+    from ssi_b200 import synth
+    from test_gpu_parity import LOSS_RTOL, assert_grad_close
+
+    inp = synth.make_inputs(synth.CONFIGS[cfg], batch=B, seq=S, vocab=V, hidden=D, seed=21)
+    g = torch.Generator().manual_seed(5)
+    h_pre = (inp["X"].float() * (1 + torch.rand(B, S, 1, generator=g) * 3)).to(torch.bfloat16)  # rows of varied rms
+    scale = (1 + 0.2 * torch.randn(D, generator=g)).to(torch.bfloat16)
+    shifted = oracle.shift_labels(inp["labels"])
+    upstream = float((inp["labels"] != -100).sum())
+
+    # oracle: fp32 autograd through the restated reference ops
+    hp = h_pre.float().requires_grad_(True)
+    sc = scale.float().requires_grad_(True)
+    ww = inp["W"].float().requires_grad_(True)
+    normed = torch.nn.functional.rms_norm(hp, (D,), weight=sc, eps=1e-6)
+    ref = oracle.lmhead_ce(normed, ww, shifted)
+    (ref * upstream).backward()
+
+    dev = torch.device("cuda")
+    emb = torch.nn.Embedding(V, D, dtype=torch.bfloat16, device=dev)
+    norm = ssi_b200.RMSNormB200(D, dtype=torch.bfloat16, device=dev)
+    with torch.no_grad():
+        emb.weight.copy_(inp["W"])
+        norm.scale.copy_(scale)
+    loss_fn = ssi_b200.FusedLinearCrossEntropyLoss(emb, mode=mode)
+    loss_fn.set_fused_norm(norm)
+    loss_fn.grad_hint = torch.tensor([upstream], device=dev)
+    hc = h_pre.to(dev).requires_grad_(True)
+    loss = loss_fn(hc, shifted.to(dev))
+    (loss * upstream).backward()
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref.item()) <= LOSS_RTOL * abs(ref.item())
+    assert_grad_close(hc.grad, hp.grad, "d(pre-norm h)")
+    assert_grad_close(emb.weight.grad, ww.grad, "dW")
+    assert norm.scale.grad.dtype == torch.bfloat16
+    assert_grad_close(norm.scale.grad, sc.grad, "dscale")
+    with torch.inference_mode():
+        l_eval = loss_fn(h_pre.to(dev), shifted.to(dev))
+    assert abs(l_eval.item() - ref.item()) <= LOSS_RTOL * abs(ref.item())

@@ -89,3 +89,32 @@ def test_shard_rows_partitions_exactly():
         assert spans[0][0] == 0 and spans[-1][1] == n
         assert all(spans[i][1] == spans[i + 1][0] for i in range(w - 1))
         assert max(e - b for b, e in spans) - min(e - b for b, e in spans) <= 1
+
+
+def test_install_fuse_norm_keeps_the_state_dict_and_hands_over_the_scale():
+    import ssi_b200
+    from ssi_b200.model_hooks import FusedNormPassthrough
+
+    class Norm(nn.Module):  # shape of torchtune's RMSNorm (tt/torchtune/modules/rms_norm.py:23-27)
+        def __init__(self, dim):
+            super().__init__()
+            self.normalized_shape, self.eps = (dim,), 1e-6
+            self.scale = nn.Parameter(torch.ones(dim))
+
+    class Model(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.tok_embeddings = nn.Embedding(50, 16)
+            self.norm = Norm(16)
+            self.output = None
+
+    m = Model()
+    keys = set(m.state_dict())
+    scale = m.norm.scale
+    loss_fn = ssi_b200.install(m, fuse_norm=True)
+    assert isinstance(m.norm, FusedNormPassthrough) and m.norm.scale is scale
+    assert set(m.state_dict()) == keys and "norm.scale" in keys
+    x = torch.randn(2, 3, 16)
+    assert m.norm(x) is x
+    assert loss_fn._norm_args()[0] is scale and loss_fn._norm_args()[1] == 1e-6
+    assert "scale" not in dict(loss_fn.named_parameters())  # the loss does not own it
