@@ -58,24 +58,48 @@ class TiedGradExchange:
         self.nbytes, self._acc_off = nbytes.value, off.value
         own = ctypes.c_void_p(0)
         handle = (ctypes.c_ubyte * 64)()
-        with torch.cuda.device(self.device):
-            _lib.check(lib.ssi_b200_dp_alloc(self.nbytes, ctypes.byref(own), ctypes.cast(handle, ctypes.c_void_p)),
-                       "dp_alloc")
-        self._own = own.value
-        handles: list = [None] * self.world
-        dist.all_gather_object(handles, bytes(handle), group=group)
+        self._own = None
         self._peer_ptrs: list[int] = []
         self._opened: list[int] = []
-        with torch.cuda.device(self.device):
-            for r in range(self.world):
-                if r == self.rank:
-                    self._peer_ptrs.append(self._own)
-                    continue
-                buf = (ctypes.c_ubyte * 64).from_buffer_copy(handles[r])
-                p = ctypes.c_void_p(0)
-                _lib.check(lib.ssi_b200_dp_open(ctypes.cast(buf, ctypes.c_void_p), ctypes.byref(p)), "dp_open")
-                self._peer_ptrs.append(p.value)
-                self._opened.append(p.value)
+        # Set-up is collective: a failure on ANY rank (no IPC in this container, no P2P between two GPUs, out of
+        # memory) is agreed on by all ranks before anyone raises, so that callers can fall back together.
+        err = None
+        try:
+            with torch.cuda.device(self.device):
+                _lib.check(lib.ssi_b200_dp_alloc(self.nbytes, ctypes.byref(own),
+                                                 ctypes.cast(handle, ctypes.c_void_p)), "dp_alloc")
+            self._own = own.value
+        except RuntimeError as e:
+            err = str(e)
+        gathered: list = [None] * self.world
+        dist.all_gather_object(gathered, (bytes(handle), err), group=group)
+        if all(e is None for _, e in gathered):
+            try:
+                with torch.cuda.device(self.device):
+                    for r in range(self.world):
+                        if r == self.rank:
+                            self._peer_ptrs.append(self._own)
+                            continue
+                        buf = (ctypes.c_ubyte * 64).from_buffer_copy(gathered[r][0])
+                        p = ctypes.c_void_p(0)
+                        _lib.check(lib.ssi_b200_dp_open(ctypes.cast(buf, ctypes.c_void_p), ctypes.byref(p)),
+                                   "dp_open")
+                        self._peer_ptrs.append(p.value)
+                        self._opened.append(p.value)
+            except RuntimeError as e:
+                err = str(e)
+        errs: list = [None] * self.world
+        dist.all_gather_object(errs, err, group=group)
+        if any(e is not None for _, e in gathered) or any(e is not None for e in errs):
+            if self._opened or self._own is not None:
+                with torch.cuda.device(self.device):
+                    for p in self._opened:
+                        lib.ssi_b200_dp_close(p)
+                    if self._own is not None:
+                        lib.ssi_b200_dp_free(self._own)
+            self._opened, self._own = [], None
+            why = next(e for e in [g[1] for g in gathered] + errs if e is not None)
+            raise RuntimeError(f"ssi_b200.peer: peer-memory set-up failed on at least one rank: {why}")
         self._ptr_array = (ctypes.c_void_p * self.world)(*self._peer_ptrs)
         self.dw_acc = torch.as_tensor(_DevicePtr(self._own + self._acc_off, (self.V, self.D), "<f4"),
                                       device=self.device)

@@ -56,7 +56,17 @@ class PathStep:
                 from .peer import TiedGradExchange
 
                 dev = weight.device
-                self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, dev)
+                try:
+                    self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, dev)
+                except RuntimeError as e:
+                    if exchange == "peer" or os.environ.get("SSI_B200_EXCHANGE") == "peer":
+                        raise  # asked for explicitly
+                    import warnings
+
+                    # the failure was agreed on by all ranks (TiedGradExchange), so all of them land here together
+                    warnings.warn(f"{e}; using the NCCL all-reduce of the tied gradient instead")
+                    self.exchange = "nccl"
+            if self.peer is not None:
                 # SSI_B200_PEER_SERIAL=1 (diagnostics): run the exchange on the main stream after the step instead
                 self.side = (torch.cuda.current_stream(dev) if os.environ.get("SSI_B200_PEER_SERIAL") == "1"
                              else torch.cuda.Stream(dev))

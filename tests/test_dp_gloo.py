@@ -60,3 +60,35 @@ def test_dp2_matches_single_process_oracle():
     mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
     assert out["loss_ok"] and out["dw_ok"] and out["dh_ok"], dict(out)
     assert out["counts"][0] == out["n_iter"]
+
+
+def _peer_setup_worker(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from ssi_b200.peer import TiedGradExchange
+
+        try:
+            TiedGradExchange(300, 64, dist.group.WORLD, torch.device("cuda", 0))
+            out[rank] = "no error"
+        except RuntimeError as e:
+            out[rank] = str(e)
+        dist.barrier()  # both ranks got here: nobody hangs in a collective the other one skipped
+    finally:
+        dist.destroy_process_group()
+
+
+def test_peer_setup_failure_is_agreed_on_by_all_ranks():
+    """On a box without a GPU the exchange buffers cannot be allocated: every rank must raise the same RuntimeError
+    (so that callers can fall back to NCCL together) instead of one rank raising while the other waits."""
+    if torch.cuda.is_available():
+        import pytest
+
+        pytest.skip("needs a box without CUDA to provoke the set-up failure")
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_peer_setup_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert len(out) == 2
+    for r in (0, 1):
+        assert "peer-memory set-up failed" in out[r], out[r]
