@@ -51,7 +51,7 @@ int64_t ssi_b200_launch_count(void);
 /* Tuning knobs (also read once from the environment as SSI_B200_<NAME>): "g_cap_mib" = size cap of the bf16
  * logits/dlogits block scratch in MiB (default 4608; workspace sizes depend on it: query them again after changing
  * it), "cta_group" (2 = CTA pairs, default), "wide_dw" / "wide_dx" (2 = 256x512 tiles for the long-K contractions,
- * default), "tail_split" (1 = a last wave that is at most half full runs as 256x256 halves, default), "lockstep"
+ * default), "tail_split" (1 = a last wave that is at most half full runs as 256x256 halves, default), "shape_gate" (1 = the 256x256 kernel is enqueued as well and the device-side plan picks, default), "lockstep"
  * (k-blocks between sync points of dW / dX, default 64, 0 = off), "lockstep_k1" (1 = K1 sweeps its vocabulary tiles
  * in lockstep, default), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints",
  * "dw_hints", "dx_hints" (experiments; see profiles/r01_tuning_notes.md). */

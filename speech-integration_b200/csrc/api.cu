@@ -161,6 +161,7 @@ int make_tmap(CUtensorMap* m, CUtensorMapDataType dt, int esize, const void* ptr
 
 int cta_group();       // tuning knobs, defined below
 int tail_split_opt();
+int shape_gate_opt();
 
 template <int EPI, bool A_MN, bool B_MN, int CG, int NW = 1>
 int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int grid_override) {
@@ -218,7 +219,12 @@ int launch_gemm_wide(const ssi::GemmParams& p, int sms, cudaStream_t st, const c
   if (cta_group() == 2 && wide == 2) {
     ssi::GemmParams q = p;
     q.tail_split = tail_split_opt();
-    return launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(q, sms, st, name, cat, 0);
+    if (!shape_gate_opt()) return launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(q, sms, st, name, cat, 0);
+    // both tile shapes are enqueued; the device-side plan decides which one runs (GemmParams::shape_gate)
+    q.shape_gate = 1, q.gate_workers = sms / 2;
+    if (int r = launch_gemm_cg<EPI, A_MN, B_MN, 2, 2>(q, sms, st, name, cat, 0)) return r;
+    q.shape_gate = 2;
+    return launch_gemm_cg<EPI, A_MN, B_MN, 2, 1>(q, sms, st, name, cat, 0);
   }
   return launch_gemm<EPI, A_MN, B_MN>(p, sms, st, name, cat);
 }
@@ -282,6 +288,7 @@ struct Tune {
   int lockstep = 64;   // k-blocks between lockstep sync points of the dW / dX contractions (0 = off)
   int cta_group = 2;   // 2 = CTA pairs (tcgen05 cta_group::2, 256x256 tiles), 1 = single-CTA 128x256 tiles
   int lockstep_k1 = 1;  // single-pass K1: lockstep of the vocabulary sweep (one sync point per tile); 0 = off
+  int shape_gate = 1;  // wide dW / dX: also enqueue the 256x256 kernel and let the device-side plan pick (small problems)
   int tail_split = 1;  // wide tiles: split the items of an at most half-full last wave into 256x256 halves
   int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
 };
@@ -300,6 +307,7 @@ Tune& tune() {
     if (const char* e = getenv("SSI_B200_DW_HINTS")) x.dw_hints = atoi(e);
     if (const char* e = getenv("SSI_B200_DX_HINTS")) x.dx_hints = atoi(e);
     if (const char* e = getenv("SSI_B200_LOCKSTEP_K1")) x.lockstep_k1 = atoi(e) ? 1 : 0;
+    if (const char* e = getenv("SSI_B200_SHAPE_GATE")) x.shape_gate = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_TAIL_SPLIT")) x.tail_split = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
@@ -310,6 +318,7 @@ Tune& tune() {
 
 int cta_group() { return tune().cta_group; }
 int tail_split_opt() { return tune().tail_split; }
+int shape_gate_opt() { return tune().shape_gate; }
 unsigned long long policy_of(int code) {
   return code == 1 ? ssi::kEvictFirst : code == 2 ? ssi::kEvictLast : code == 3 ? ssi::kEvictNormal : 0ull;
 }
@@ -471,6 +480,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "dw_hints")) t.dw_hints = static_cast<int>(value);
   else if (!strcmp(name, "dx_hints")) t.dx_hints = static_cast<int>(value);
   else if (!strcmp(name, "lockstep_k1")) t.lockstep_k1 = value ? 1 : 0;
+  else if (!strcmp(name, "shape_gate")) t.shape_gate = value ? 1 : 0;
   else if (!strcmp(name, "tail_split")) t.tail_split = value ? 1 : 0;
   else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;

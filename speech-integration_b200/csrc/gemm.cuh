@@ -67,6 +67,10 @@ struct GemmParams {
   int c_reduce;  // EPI_BF16 / EPI_F32: 1 = TMA reduce-add into C, 0 = plain store
   int c_reduce_plan;  // 1 = take it from the chunk plan instead: reduce-add unless dplan->first
   int tail_split;     // wide tiles (NW 2): run the items of a last, at most half-full wave as 256x256 halves
+  // Shape gate (sizes that depend on the number of valid rows are only known on the device): the host enqueues the
+  // 256x512 kernel (gate 1) AND the 256x256 kernel (gate 2) for the same contraction; each evaluates the same
+  // predicate from the plan and exactly one of them runs, the other exits at once.  0 = no gate.
+  int shape_gate, gate_workers;
   unsigned long long store_policy;  // L2 cache policy for plain C / G stores (0 = default)
   unsigned long long a_policy, b_policy;  // L2 cache policy of the A / B operand loads (0 = default)
   // Lockstep throttle (EPI_BF16 / EPI_F32 only, uniform K loops): every `sync_every` k-blocks the producers of
@@ -203,6 +207,14 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
   const int worker = (CG == 2) ? (blockIdx.x >> 1) : blockIdx.x;       // CTA (pair) index
   const int workers = (CG == 2) ? (gridDim.x >> 1) : gridDim.x;
   Sched sc = make_sched<EPI>(p);
+  if (p.shape_gate != 0) {
+    // wide tiles pay off when they fill more than half a wave (otherwise every item is a latency-starved half
+    // item) and the K loop is long enough to amortise their single-buffered epilogue
+    const int pairs = (sc.tiles_m + 1) >> 1;
+    const int wide_items_g = pairs * ((sc.tiles_n + 1) >> 1);
+    const bool wide_ok = (2 * wide_items_g > p.gate_workers) && (sc.k_blocks >= 48);
+    if ((p.shape_gate == 1) != wide_ok) return;  // uniform over the whole grid
+  }
   const int tiles_m_real = sc.tiles_m;  // in 128-row tiles
   if constexpr (CG == 2) {
     sc.tiles_m = (sc.tiles_m + 1) >> 1;  // the schedule runs over 256-row tile pairs

@@ -30,11 +30,23 @@ def test_debug_gemm(M, N, K, a_mn, b_mn, wide):
     _lib.load()
     _lib.set_option("wide_dw", wide)
     _lib.set_option("wide_dx", wide)
+    _lib.set_option("shape_gate", 0)  # force the tile shape under test (the gate would pick 256x256 for small shapes)
     try:
         _run_debug_gemm(ops, M, N, K, a_mn, b_mn)
     finally:
         _lib.set_option("wide_dw", 2)
         _lib.set_option("wide_dx", 2)
+        _lib.set_option("shape_gate", 1)
+
+
+@pytest.mark.parametrize("M,N,K", [(1000, 2048, 520), (4864, 2048, 3200), (9728, 2048, 128)])
+@pytest.mark.parametrize("a_mn,b_mn", [(True, True), (False, True)])
+def test_debug_gemm_shape_gate(M, N, K, a_mn, b_mn):
+    """Default configuration: both tile shapes are enqueued and the device-side predicate picks one (few items or a
+    short K loop -> 256x256, else 256x512); exactly one of them must write the result."""
+    from ssi_b200 import ops
+
+    _run_debug_gemm(ops, M, N, K, a_mn, b_mn)
 
 
 def _run_debug_gemm(ops, M, N, K, a_mn, b_mn):
