@@ -94,6 +94,52 @@ CASES = {
 }
 
 
+def _reference_function(path: str, name: str):
+    """One top-level function of a reference file whose module cannot be imported here (absent packages)."""
+    import ast
+
+    tree = ast.parse(open(path).read())
+    fn = next(n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name == name)
+    ns = {"Tensor": torch.Tensor, "torch": torch, "nn": nn}
+    exec(compile(ast.Module(body=[fn], type_ignores=[]), path, "exec"), ns)
+    return ns[name]
+
+
+def next_rows_fixture():
+    """Outputs of the REFERENCE's own code for the rows SURVEY.md §8(f) marks next: RMSNorm forward + autograd
+    backward (tt/torchtune/modules/rms_norm.py), count_token_types (ssi/train_utils.py:150-165) and scale_grads
+    (tt/torchtune/training/_grad_scaler.py:11-31) followed by the squared norm clip_grad_norm_ would take."""
+    rms = _load("ref_rms_norm", os.path.join(TT, "modules", "rms_norm.py"))
+    count_token_types = _reference_function(os.path.join(REF, "ssi", "train_utils.py"), "count_token_types")
+    scale_grads = _reference_function(os.path.join(TT, "training", "_grad_scaler.py"), "scale_grads")
+    g = torch.Generator().manual_seed(42831)
+    N, D, V = 200, 256, 1000
+    x = (torch.randn(N, D, generator=g) * 2.5).to(torch.bfloat16)
+    scale = (1 + 0.2 * torch.randn(D, generator=g)).to(torch.bfloat16)
+    dy = (torch.randn(N, D, generator=g) * 1e-2).to(torch.bfloat16)
+    norm = rms.RMSNorm(D).to(torch.bfloat16)
+    with torch.no_grad():
+        norm.scale.copy_(scale)
+    xx = x.clone().requires_grad_(True)
+    y = norm(xx)
+    y.backward(dy)
+    tokens = torch.randint(0, V, (6, 50), generator=g)
+    ranges = {"text": (0, 599), "special": (600, 639), "dsu": (640, 997), "modality": (998, 999)}
+    pad = 601
+    grad = (torch.randn(V, D, generator=g) * 40).to(torch.bfloat16)
+    lin = nn.Embedding(V, D).to(torch.bfloat16)
+    lin.weight.grad = grad.clone()
+    scaler = torch.tensor(1 / 4099)
+    scale_grads(lin, scaler)
+    return {
+        "rms": {"x": x, "scale": scale, "dy": dy, "eps": norm.eps, "y": y.detach(), "dx": xx.grad,
+                "dscale": norm.scale.grad},
+        "types": {"tokens": tokens, "ranges": ranges, "pad": pad, "counts": count_token_types(tokens, ranges, pad)},
+        "scale_grads": {"grad": grad, "scaler": scaler, "scaled": lin.weight.grad.clone(),
+                        "sqnorm": lin.weight.grad.float().pow(2).sum()},
+    }
+
+
 def main():
     sys.path.insert(0, os.path.join(os.path.dirname(OUT), "..", "speech-integration_b200"))
     from ssi_b200 import synth
@@ -112,6 +158,9 @@ def main():
         torch.save(fx, os.path.join(OUT, f"{name}.pt"))
         print(name, "loss", fx["fp32"]["loss"].item(), "n", fx["fp32"]["num_tokens_iter"],
               os.path.getsize(os.path.join(OUT, f"{name}.pt")) // 1024, "KiB")
+    os.makedirs(os.path.join(OUT, "next_rows"), exist_ok=True)
+    torch.save(next_rows_fixture(), os.path.join(OUT, "next_rows", "next_rows_small.pt"))
+    print("next_rows_small", os.path.getsize(os.path.join(OUT, "next_rows", "next_rows_small.pt")) // 1024, "KiB")
 
 
 if __name__ == "__main__":

@@ -163,3 +163,28 @@ def test_final_norm_fused_into_the_path(B, S, V, D, cfg, mode):
     with torch.inference_mode():
         l_eval = loss_fn(h_pre.to(dev), shifted.to(dev))
     assert abs(l_eval.item() - ref.item()) <= LOSS_RTOL * abs(ref.item())
+
+
+def test_next_rows_against_the_reference_fixture():
+    """The CUDA kernels against outputs of the REFERENCE's own code (tests/golden/next_rows/, generated in the build
+    container by oracle/gen_golden.py; the GPU box has no reference checkout)."""
+    import os
+
+    from ssi_b200 import ops
+
+    fx = torch.load(os.path.join(os.path.dirname(__file__), "golden", "next_rows", "next_rows_small.pt"))
+    r = fx["rms"]
+    y, rstd = ops.rmsnorm_fwd(r["x"].cuda(), r["scale"].cuda(), r["eps"])
+    dx, dscale = ops.rmsnorm_bwd(r["dy"].cuda(), r["x"].cuda(), r["scale"].cuda(), rstd)
+    _ulp_close(y, r["y"], "y")
+    _ulp_close(dx, r["dx"], "dx", exact_frac=0.98)
+    assert torch.allclose(dscale.cpu(), r["dscale"].float(), rtol=2 ** -6, atol=1e-4)
+    t = fx["types"]
+    labels = t["tokens"].clone()
+    _, _, types = ops.label_shift_count_types(labels.cuda(), t["tokens"].cuda(), t["ranges"], t["pad"])
+    assert dict(zip(list(t["ranges"]) + ["total"], types.tolist())) == t["counts"]
+    s = fx["scale_grads"]
+    g = s["grad"].cuda()
+    sq = ops.grad_scale_sqnorm(g, s["scaler"].reshape(1).cuda())
+    assert torch.equal(g.cpu(), s["scaled"])
+    assert abs(sq.item() - s["sqnorm"].item()) <= 1e-5 * s["sqnorm"].item()
