@@ -3,14 +3,18 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--config c5]
 
-One "step" = one pass of the hot path over one batch of synthetic input: label shift + token
-counts, the fused projection + CE forward and backward (default single-pass mode: per row chunk K1 logits tiles ->
-bf16 block + online LSE, softmax-grad in place, dW_acc += G^T X, dX = G W, then rescale/round in backward;
---mode recompute: K1 online-LSE forward, K2 recompute backward), K3 tied-embedding scatter-add and, for N > 1, the
-NCCL all-reduce of the token counts and of the tied gradient.  The default workload is
-BASELINE.json configs[4] / SURVEY c5 — HuBERT 5000-DSU vocabulary (V = 133,258, the "@133k vocab" the metric is
-quoted on), global batch 64 x 2048 — sharded by sequences over the ranks (strong scaling: the global batch is
-fixed; at N = 1 the whole batch runs on one GPU).
+One "step" = one pass of the hot path over one batch of synthetic input, driven through the drop-in
+API (ssi_b200.install via PathStep) in the CAUSAL order of a training step: embedding gather (+ the id sort its
+backward needs), label shift + token counts, the fused projection + CE forward and backward (default single-pass
+mode: per row chunk K1 logits tiles -> bf16 block + online LSE, softmax-grad in place, dW_acc += G^T X, dX = G W,
+then rescale/round in backward; --mode recompute: K1 online-LSE forward, K2 recompute backward), and only then --
+where the decoder backward would have produced dH0 -- the K3 tied-embedding scatter-add.  For N > 1 the tied
+gradient is exchanged in three parts (token counts through the peers' ctrl blocks, the LM-head part behind the last dX
+contraction, the embedding part as compact rows after the embedding backward; --exchange nccl = bf16 all-reduce after
+the embedding backward).  The default workload is BASELINE.json configs[4] / SURVEY c5 — HuBERT 5000-DSU vocabulary
+(V = 133,258, the "@133k vocab" the metric is quoted on), global batch 64 x 2048, generated ONCE with the global seed
+and sliced by sequences over the ranks (strong scaling: the global batch is fixed; at N = 1 the whole batch runs on
+one GPU).
 
 Prints ONE JSON line on rank 0.  `value` = global token positions per second with inputs resident in HBM;
 `e2e` = the same through the public module API with pinned-host inputs copied in and the loss read back every
@@ -50,6 +54,9 @@ def parse_args():
                          "the last dX contraction; nccl = bf16 all_reduce after the step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-fwd-only", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="N > 1: skip rank 0's N = 1 re-run of the global batch")
     return ap.parse_args()
 
 
@@ -122,9 +129,12 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------- CPU reference arm
-def cpu_reference_tokens_per_s(cfg, iters: int, warmup: int):
-    """The reference's CPU path (oracle restatement, bf16 like the reference: conf/common.yaml:32) on a bounded
-    sample of the workload: 1 x 2048 token rows at the workload's vocabulary, fwd + bwd + embedding backward."""
+def cpu_reference_run(cfg, iters: int, warmup: int, dtype_name: str = "bf16"):
+    """The reference's CPU path (oracle restatement; bf16 is the reference's dtype, conf/common.yaml:32) on a bounded
+    sample of the workload: 1 x 2048 token rows at the workload's vocabulary, fwd + bwd + embedding backward.
+    Returns (tokens/s from the MEDIAN iteration, times, cores, last outputs)."""
+    import statistics
+
     import torch
 
     from oracle import reference_path as oracle
@@ -132,42 +142,92 @@ def cpu_reference_tokens_per_s(cfg, iters: int, warmup: int):
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    dt_ = torch.bfloat16 if dtype_name == "bf16" else torch.float32
     inp = synth.make_inputs(cfg, batch=1, seq=CPU_SAMPLE_ROWS)
-    times = []
+    times, out = [], None
     for i in range(warmup + iters):
         t0 = time.perf_counter()
-        oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"], inp["dH0"], inp["W"],
-                               compute_dtype=torch.bfloat16)
+        out = oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"], inp["dH0"], inp["W"], compute_dtype=dt_)
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
-    return CPU_SAMPLE_ROWS / (sum(times) / len(times)), times, cores
+    return CPU_SAMPLE_ROWS / statistics.median(times), times, cores, (inp, out)
+
+
+def cpu_sample_text(cfg, dtype_name, times, warmup):
+    return (f"{CPU_SAMPLE_ROWS} token rows (1x2048) of {cfg.name} at V={cfg.vocab}, D=2048, {dtype_name}, fwd+bwd+"
+            f"embedding backward per step; median of {len(times)} iterations after {warmup} warm-up")
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    import statistics
+
+    import torch
+
     from ssi_b200 import synth
 
     cfg = synth.CONFIGS[args.config]
-    # each step = one bounded sample; keep the whole run within a few minutes
+    # each step = one bounded sample; same warm-up count as our arm, steps capped so the run ends within minutes
     steps = max(1, min(args.steps, 20))
-    warm = max(1, min(args.warmup, 3))
-    tps, times, cores = cpu_reference_tokens_per_s(cfg, steps, warm)
-    ms = 1e3 * sum(times) / len(times)
-    sample = (f"{CPU_SAMPLE_ROWS} token rows (1x2048) of {cfg.name} at V={cfg.vocab}, D=2048, bf16, fwd+bwd+embedding "
-              f"backward per step")
+    warm = max(args.warmup, 3)
+    tps, times, cores, _ = cpu_reference_run(cfg, steps, warm, "bf16")
+    ms = 1e3 * statistics.median(times)
+    sample = cpu_sample_text(cfg, "bf16", times, warm)
     line = {
         "impl": "reference", "metric": METRIC, "value": tps, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warm, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(cfg), "reference_arm": "CPU restatement of the reference path "
-                   "(oracle/reference_path.py: same torch ops at the reference's call sites), host cores only"},
+                   "(oracle/reference_path.py: same torch ops at the reference's call sites), host cores only",
+                   "parallel_info": torch.__config__.parallel_info().strip().splitlines()[:6]},
         "cpu_baseline": {"value": tps, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": tps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------- GPU contender
+def gpu_reference_tokens_per_s(W, tokens, labels, X, dH0, iters: int = 3):
+    """"The kernel to beat" (SURVEY.md §2.2 / §8d): the reference's own op sequence on the SAME GPU, eager PyTorch in
+    bf16 -- F.embedding, F.linear per chunk (tied_linear.py:25; cuBLAS), upcast + F.cross_entropy(sum) per chunk
+    (ce_chunked_output_loss.py:41-43; ATen), (loss * n).backward(), embedding backward.  A contender, not product
+    code: restated here with torch ops only, nothing of ssi_b200 runs in it."""
+    import statistics
+
+    import torch
+    import torch.nn.functional as F
+
+    Wp = W.detach().clone().requires_grad_(True)
+    n_chunks, ignore = 8, -100
+    shifted = torch.hstack((labels[..., 1:], torch.full_like(labels[..., -1:], ignore)))
+    n_iter = (labels != ignore).sum()
+    times = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for i in range(iters + 1):
+        Wp.grad = None
+        e0.record()
+        h0 = F.embedding(tokens, Wp)
+        h = X.detach().requires_grad_(True)
+        logits = [F.linear(c, Wp) for c in h.chunk(n_chunks, dim=1)]
+        total = (shifted != ignore).sum()
+        loss = 0.0
+        for lg, lb in zip(logits, shifted.chunk(n_chunks, dim=1)):
+            loss = loss + F.cross_entropy(lg.reshape(-1, lg.size(-1)).float(), lb.reshape(-1), ignore_index=ignore,
+                                          reduction="sum")
+        del logits
+        ((loss / total) * n_iter).backward()
+        h0.backward(dH0)
+        e1.record()
+        torch.cuda.synchronize()
+        if i > 0:
+            times.append(e0.elapsed_time(e1))
+    del Wp
+    torch.cuda.empty_cache()
+    rows = tokens.numel()
+    return rows / (statistics.median(times) * 1e-3), times
 
 
 def workload_name(cfg) -> str:
@@ -176,6 +236,19 @@ def workload_name(cfg) -> str:
 
 
 # ----------------------------------------------------------------------------------------- our arm
+def grad_checksums(g):
+    """Two order-sensitive integer checksums of a bf16 tensor's bit pattern (exact, device-side)."""
+    import torch
+
+    v = g.view(torch.int16).reshape(-1).to(torch.int64)
+    w = (torch.arange(v.numel(), device=v.device, dtype=torch.int64) % 8191) + 1
+    return torch.stack([v.sum(), (v * w).sum()])
+
+
+def rel_fro(a, b):
+    return float(((a.float() - b.float()).norm() / (b.float().norm() + 1e-30)).item())
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -200,17 +273,15 @@ def run_ours(args):
     cfg = synth.CONFIGS[args.config]
     D = synth.HIDDEN
     V = cfg.vocab
+    warmup = max(args.warmup, 3)
 
-    # ---- synthetic inputs: W replicated (global seed), this rank's sequences of the global batch
+    # ---- synthetic inputs: W replicated (global seed); the GLOBAL batch is generated once with the global seed and
+    # this rank takes its contiguous slice of sequences, so losses are comparable across N
     b0, b1 = ddist.shard_rows(cfg.batch, rank, world)
     Bl = b1 - b0
     gw = torch.Generator().manual_seed(synth.SEED)
     W = (torch.randn(V, D, generator=gw) * 0.02).to(torch.bfloat16).to(dev)
-    g = torch.Generator().manual_seed(synth.SEED + 1 + rank)
-    tokens_h, labels_h = synth.make_tokens_labels(cfg, g, batch=Bl)
-    gd = torch.Generator(device=dev).manual_seed(synth.SEED + 1 + rank)
-    X = torch.randn(Bl, cfg.seq, D, generator=gd, device=dev).to(torch.bfloat16)
-    dH0 = (torch.randn(Bl, cfg.seq, D, generator=gd, device=dev) * 1e-3).to(torch.bfloat16)
+    tokens_h, labels_h, X, dH0 = synth.global_batch_rows(cfg, b0, b1, dev)
     tokens, labels = tokens_h.to(dev), labels_h.to(dev)
     n_valid_local = int((labels_h[:, 1:] != synth.IGNORE).sum())
     nv = torch.tensor([n_valid_local], dtype=torch.int64, device=dev)
@@ -218,7 +289,7 @@ def run_ours(args):
         dist.all_reduce(nv)
     n_valid_global = int(nv.item())
 
-    path = PathStep(W, process_group=pg, mode=args.mode, exchange=args.exchange)
+    path = PathStep(W, process_group=pg, mode=args.mode, exchange=args.exchange, max_tokens_per_rank=Bl * cfg.seq)
     mode = path.loss_fn.mode
 
     def step():
@@ -231,7 +302,7 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(max(args.warmup, 3)):
+    for _ in range(warmup):
         step()
     barrier()
 
@@ -256,7 +327,56 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = t.item() / args.steps
     value = cfg.rows / (ms_step * 1e-3)
-    loss_batch = float(out[0].item())
+    loss_batch = out[0].detach().clone()
+
+    # ---- parity block: the global loss * n and the tied gradient against the N = 1 path on the SAME global batch
+    # (N > 1; rank 0 re-runs the whole batch alone), the gradient's bit pattern identical on every rank
+    parity = None
+    if world > 1:
+        lg = loss_batch.reshape(1).to(torch.float64)
+        dist.all_reduce(lg)
+        cs = grad_checksums(path.weight.grad)
+        all_cs = [torch.empty_like(cs) for _ in range(world)]
+        dist.all_gather(all_cs, cs)
+        same = all(bool(torch.equal(c, all_cs[0])) for c in all_cs)
+        parity = {"loss_times_n_global": float(lg.item()), "grad_bits_identical_on_all_ranks": same}
+        if rank == 0 and not args.no_parity:
+            tk, lb, Xg, dHg = synth.global_batch_rows(cfg, 0, cfg.batch, dev)
+            solo = PathStep(W.detach().clone())
+            l1, _, _ = solo(tk.to(dev), lb.to(dev), Xg, dHg)
+            torch.cuda.synchronize()
+            parity.update({
+                "loss_times_n_at_n1": float(l1.item()),
+                "loss_rel_err_vs_n1": abs(float(lg.item()) - float(l1.item())) / abs(float(l1.item())),
+                "dW_rel_frobenius_vs_n1": rel_fro(path.weight.grad, solo.weight.grad),
+                "how": "rank 0 re-ran the whole 64 x 2048 global batch alone (N = 1 path, same W) after the timed "
+                       "region; N = 1 itself is checked against the CPU oracle in its own bench line and in tests/"})
+            del solo, Xg, dHg
+            from ssi_b200 import ops as _ops
+
+            _ops.free_workspaces()
+            torch.cuda.empty_cache()
+        barrier()
+
+    # ---- forward only (the eval path, ssi/eval.py:27-33): K1 alone
+    fwd_only = None
+    if not args.no_fwd_only:
+        for _ in range(2):
+            path.forward_only(X, labels)
+        barrier()
+        kf = max(3, min(args.steps, 10))
+        e0.record()
+        for _ in range(kf):
+            lf = path.forward_only(X, labels)
+        e1.record()
+        barrier()
+        tf = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(tf, op=dist.ReduceOp.MAX)
+        ms_f = tf.item() / kf
+        fwd_only = {"value": cfg.rows / (ms_f * 1e-3), "unit": UNIT, "ms_per_step": ms_f, "steps": kf,
+                    "algorithmic_tflops_per_gpu": 2.0 * n_valid_local * V * D / (ms_f * 1e-3) / 1e12,
+                    "loss_rank0": float(lf.item())}
 
     # ---- end to end through the public API with pinned host inputs
     e2e = None
@@ -307,9 +427,8 @@ def run_ours(args):
         mine = sum(ms for k, (ms, _) in classes.items() if k not in ("exchange",)) / args.steps
         per_rank_ms = [None] * world
         dist.all_gather_object(per_rank_ms, round(mine, 3))
-    mismatch = path.loss_fn.grad_hint_mismatch
-    if mismatch is not None and bool(mismatch.any().item()):
-        raise SystemExit("bench.py: the peer exchange ran with a multiplier that backward did not confirm")
+    if path.sync is not None:
+        path.sync.check()  # raises if the exchange ran with a multiplier that backward did not confirm / timed out
     exchange = path.exchange
     path.close()
     if rank != 0:
@@ -346,30 +465,74 @@ def run_ours(args):
             traffic = None
     roofline = {"bound": "tensor", "kernel": f"gemm_kernel<{dom}>", "achieved": achieved, "peak": peak,
                 "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
-                "peak_kind": "sustained bf16 cuBLAS, " + peaks["source"],
-                "frac_of_burst_peak": achieved / peaks["bf16_tflops"],
+                "traffic_source": "static: one ncu --set full capture of this kernel at this shape "
+                                  "(profiles/traffic.json), bytes per launch; not re-measured in this run",
+                "peak_kind": "sustained bf16 cuBLAS (kernel timed inside a long step), " + peaks["source"],
+                "frac_of_burst_peak": achieved / peaks["bf16_tflops"], "burst_peak": peaks["bf16_tflops"],
                 "algorithmic_flops_per_launch": dom_alg, "avg_launch_ms": dom_ms}
+    # the HBM-bound row the north star singles out: K3 embedding scatter (sort + segmented reduce, one record per call)
+    k3 = None
+    if classes["scatter"][1] > 0 and world == 1:
+        uniq = int(torch.unique(tokens_h).numel())
+        k3_bytes = n_local * D * 2 + n_local * 8 + 2 * uniq * D * 2
+        k3 = {"bound": "hbm", "algorithmic_bytes_per_step": k3_bytes,
+              "ms_per_step": classes["scatter"][0] / args.steps,
+              "achieved_gbs": k3_bytes / (classes["scatter"][0] / args.steps * 1e-3) / 1e9,
+              "peak_gbs": peaks["hbm_gbs"],
+              "frac": k3_bytes / (classes["scatter"][0] / args.steps * 1e-3) / 1e9 / peaks["hbm_gbs"],
+              "unique_ids": uniq, "note": "sort (embedding forward) + segmented reduce (embedding backward)"}
     step_tflops = alg_total / (ms_step * 1e-3) / 1e12
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
+        "warmup": warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": workload_name(cfg), "rows_per_rank": n_local, "valid_rows_global": n_valid_global,
-                   "parallelism": f"dp{world}", "mode": mode, "exchange": exchange, "l2": "inputs (X, W, dlogits blocks) are several times larger than "
-                   "the 126 MB L2, no explicit flush", "loss_batch_rank0": loss_batch},
+                   "parallelism": f"dp{world}", "mode": mode, "exchange": exchange,
+                   "flow": "causal: the embedding gradient is handed over only after dX was returned "
+                           "(ssi/trainer.py:393-394), through install()",
+                   "l2": "inputs (X, W, dlogits blocks) are several times larger than "
+                   "the 126 MB L2, no explicit flush", "loss_batch_rank0": float(loss_batch.item())},
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
         "step_algorithmic_tflops_per_gpu": step_tflops,
         "step_frac_of_bf16_peak": {"burst": step_tflops / peaks["bf16_tflops"], "sustained": step_tflops / peak},
-        "kernels": kern,
+        "kernels": kern, "fwd_only": fwd_only, "parity": parity, "k3_roofline": k3,
     }
     if per_rank_ms is not None:
         line["per_rank_kernel_ms_per_step"] = per_rank_ms
+    if world == 1 and not args.no_gpu_reference:
+        # the reference's own op sequence (cuBLAS + ATen, eager bf16) on this GPU, on a bounded slice of the batch
+        nb = min(Bl, 16)
+        try:
+            tps_ref, tms = gpu_reference_tokens_per_s(W, tokens[:nb], labels[:nb], X[:nb], dH0[:nb])
+            line["gpu_reference"] = {
+                "value": tps_ref, "unit": UNIT, "ms_per_step": sorted(tms)[len(tms) // 2],
+                "rows": nb * cfg.seq, "ratio_ours_over_it": value / tps_ref,
+                "what": "the reference's op sequence on this GPU, eager PyTorch bf16: F.embedding, F.linear per chunk "
+                        "(cuBLAS), upcast + F.cross_entropy(sum) per chunk (ATen), backward, embedding backward; "
+                        f"{nb} of the {Bl} sequences (its fp32 log-prob tensors need N*V*8 B); median of "
+                        f"{len(tms)} after 1 warm-up"}
+        except Exception as e:  # out of memory on a smaller part: report, do not fail the bench
+            line["gpu_reference"] = {"unavailable": f"{type(e).__name__}: {str(e)[:160]}"}
+            torch.cuda.empty_cache()
     if world == 1 and not args.no_cpu_baseline:
-        tps, times, cores = cpu_reference_tokens_per_s(cfg, 2, 1)
-        line["cpu_baseline"] = {
-            "value": tps, "unit": UNIT, "cores": cores, "kind": "port",
-            "sample": f"{CPU_SAMPLE_ROWS} token rows (1x2048) of {cfg.name} at V={V}, bf16, fwd+bwd+embedding "
-                      f"backward, mean of {len(times)} iterations after 1 warm-up"}
+        tps, times, cores, (inp, ref) = cpu_reference_run(cfg, 3, 1, "bf16")
+        line["cpu_baseline"] = {"value": tps, "unit": UNIT, "cores": cores, "kind": "port",
+                                "sample": cpu_sample_text(cfg, "bf16", times, 1),
+                                "parallel_info": torch.__config__.parallel_info().strip().splitlines()[:6]}
+        tps32, times32, _, (inp, ref32) = cpu_reference_run(cfg, 3, 1, "fp32")
+        line["cpu_baseline"]["fp32"] = {"value": tps32, "unit": UNIT, "sample": cpu_sample_text(cfg, "fp32", times32, 1)}
+        # N = 1 parity: the same sample through the GPU path against the fp32 CPU oracle run just timed
+        solo = PathStep(inp["W"].to(dev))
+        lb, dXs, _ = solo(*(inp[k].to(dev) for k in ("tokens", "labels", "X", "dH0")))
+        torch.cuda.synchronize()
+        ref_loss, n_iter, ref_dH, ref_dW = ref32
+        want = ref_loss.item() * n_iter
+        line["parity"] = {"sample": f"{CPU_SAMPLE_ROWS} token rows of {cfg.name} (the cpu_baseline sample)",
+                          "loss_times_n": float(lb.item()), "loss_times_n_oracle_fp32": want,
+                          "loss_rel_err": abs(float(lb.item()) - want) / abs(want),
+                          "dX_rel_frobenius": rel_fro(dXs.reshape(ref_dH.shape).cpu(), ref_dH),
+                          "dW_rel_frobenius": rel_fro(solo.weight.grad.cpu(), ref_dW),
+                          "tolerance": "loss rel <= 1e-3, gradients rel-Frobenius <= 4e-3 (tests/test_gpu_parity.py)"}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

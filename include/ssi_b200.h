@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 105
+#define SSI_B200_ABI_VERSION 110
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -143,6 +143,29 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
                                      void* dw_acc_init_event, void* dw_ready_event, const void* norm_scale,
                                      float norm_eps, float* dscale);
 
+/* The general form: every optional argument of the variants above in one struct (zero-initialise it), plus
+ *   pre_grad_event  cudaEvent_t or NULL: `stream` waits for it right before the FIRST softmax-grad pass, the first
+ *                   consumer of *grad_hint and *n_valid_total -- under data parallelism both are produced by
+ *                   ssi_b200_dp_counts on another stream beside the first logits contraction. */
+typedef struct ssi_b200_fwd_grad_opts {
+  int accumulate_dW_acc;
+  void* dw_acc_init_event;
+  void* dw_ready_event;
+  void* pre_grad_event;
+  const void* norm_scale;
+  float norm_eps;
+  float* dscale;
+} ssi_b200_fwd_grad_opts;
+int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                   const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                   int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream,
+                                   const ssi_b200_fwd_grad_opts* opts);
+
+/* Synchronising debug query: *gave_up != 0 if a lockstep wait inside the last single-pass call on `ws` timed out
+ * (part of the persistent grid was not resident; the kernels then ran un-throttled -- slower, still correct). */
+int ssi_b200_single_pass_lockstep_status(const void* ws, int64_t N, int64_t V, int64_t D, int* gave_up);
+
 /*
  * Backward of single-pass mode: ratio = grad_out / grad_hint (exactly 1 when the hint was right);
  *   dX *= ratio in place (skipped on the device when ratio == 1; dX may be NULL)
@@ -154,9 +177,9 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
 
 /*
  * Tied-embedding gradient: dW[ids[i], :] += dH[i, :] for i in [0, N), ids in [0, V) (ids < 0 or >= V are
- * skipped).  Rows are grouped by a stable radix sort of the ids and reduced in fp32 by a warp-level
- * segmented reduction in sorted order (deterministic: no floating-point atomics), one read-modify-write
- * of each touched dW row.
+ * skipped).  Rows are grouped by a stable radix sort of the ids (one launch: a single-block LSD sort with 9-bit
+ * digits) and reduced in fp32 by a warp-level segmented reduction in sorted order (deterministic: no
+ * floating-point atomics), one read-modify-write of each touched dW row.  Three launches in all.
  */
 int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
                                     void* ws, size_t ws_bytes, void* stream);
@@ -172,35 +195,64 @@ int ssi_b200_embedding_grad_sort(const int64_t* ids, int64_t N, int64_t V, int64
                                  void* stream);
 int ssi_b200_embedding_grad_scatter_sorted_f32(const void* dH, int64_t N, int64_t V, int64_t D, float* dW_acc,
                                                void* ws, size_t ws_bytes, void* stream);
+/* ... and the reduction into a bf16 [V, D] buffer (the tied weight's .grad) from an earlier ssi_b200_embedding_grad_sort
+ * (the sort needs only the token ids, so the embedding FORWARD can start it). */
+int ssi_b200_embedding_grad_scatter_sorted(const void* dH, int64_t N, int64_t V, int64_t D, void* dW, void* ws,
+                                           size_t ws_bytes, void* stream);
 
 /*
  * Data-parallel exchange of the tied LM-head / embedding gradient over NVLink peer memory (one process per GPU,
  * one NVSwitch node; the reference is single-process, semantics follow tt/recipes/full_finetune_distributed.py:
  * 844-851,867: gradients of the global mean).  Each rank owns one exchange buffer
- *     [ctrl 4 KiB][dW_acc fp32 V x D][stage bf16 ceil(V / world) x D]
- * that its peers map through CUDA IPC.  dp_buffer_bytes gives its size and the offset of dW_acc (pass that
- * address as `dW_acc` of ssi_b200_lmhead_ce_fwd_grad[_ev] / ssi_b200_embedding_grad_scatter_f32).  dp_alloc /
- * dp_open / dp_close / dp_free are SET-UP calls (they allocate and synchronise); `ipc_handle` is 64 bytes to
- * be carried to the peers by the host (torch.distributed all_gather).
+ *     [ctrl 4 KiB][dW_acc fp32 V x D][stage bf16 ceil(V / world) x D][slot u64 V][emb_ids i32 R][emb_rows bf16 R x D]
+ * (R = max_rows = the largest number of token rows one call hands to dp_embedding_exchange) that its peers map through
+ * CUDA IPC.  dp_buffer_bytes gives its size and the offset of dW_acc (pass that address as `dW_acc` of
+ * ssi_b200_lmhead_ce_fwd_grad*).  dp_alloc / dp_open / dp_close / dp_free are SET-UP calls (they allocate and
+ * synchronise); `ipc_handle` is 64 bytes to be carried to the peers by the host (torch.distributed all_gather).
+ * The three exchanges of a step, in the order a training step produces their inputs (all enqueue-only; `epoch` is a
+ * counter the caller increments by one per step, starting at 1, identical on all ranks; `host_flag` is NULL or a
+ * pinned, device-mapped host word that a timed-out wait sets to 1 so the host can notice without synchronising --
+ * after a time-out every exchange writes NaN instead of sums):
  *
- * dp_exchange (enqueue-only, like every other entry point):
- *   dW = bf16((accumulate_dW ? dW : 0) + (grad_out / grad_hint) * sum over ranks in rank order of dW_acc_rank)
- * on every rank, bit-identical across ranks and runs: rank r reduces vocabulary slice r in fp32 from its peers'
- * buffers (P2P loads), rounds once, and all ranks then pull the finished bf16 slices.  The kernels use no
- * shared memory, so they co-reside with the tensor-core CTAs of a dX contraction running on another stream.
- *   peer_bufs  host array [world] of the exchange buffers as mapped in this process (entry `rank` = own buffer)
- *   epoch      a counter the caller increments by one per exchange, starting at 1, identical on all ranks
+ * dp_counts             global_counts[0..1] = sum over ranks of local_counts[0..1] ({unshifted, shifted} valid-token
+ *                       counts, ssi/trainer.py:391 and ce_chunked_output_loss.py:66) and, if hint_out != NULL,
+ *                       hint_out[0] = float(global_counts[0]) (the multiplier of ssi/trainer.py:393).  Eight-byte
+ *                       peer stores and flags, no collective library call.
+ * dp_exchange           the LM-head part, as soon as dW_acc is final:
+ *                         dW = bf16((accumulate_dW ? dW : 0) + (grad_out / grad_hint) * sum_ranks dW_acc_rank)
+ *                       on every rank, bit-identical across ranks and runs: rank r reduces vocabulary slice r in fp32
+ *                       from its peers' buffers (P2P loads) in rank order, rounds once, and all ranks then pull the
+ *                       finished bf16 slices.  No shared memory: the kernels co-reside with the tensor-core CTAs of
+ *                       the dX contraction still running on another stream.
+ * dp_embedding_exchange the embedding part, once dH (the gradient reaching the embedding output) exists -- in a
+ *                       training step that is AFTER the decoder backward, so it cannot join dW_acc before the dense
+ *                       exchange.  `sort_ws` holds the order left by ssi_b200_embedding_grad_sort for the same
+ *                       N, V, D.  This rank's dH rows are summed per distinct id (fp32, sorted order) into its compact
+ *                       list (emb_rows bf16, slot[id] = epoch | index); then every rank adds, for every id present on
+ *                       any rank, the ranks' rows in rank order in fp32 to its bf16 dW row (one rounding, identical on
+ *                       all ranks).  Must follow this step's dp_exchange in stream order.  N <= max_rows.
  */
-int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, size_t* bytes, size_t* dw_acc_offset);
+int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, int64_t max_rows, size_t* bytes,
+                             size_t* dw_acc_offset);
 int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle);
 int ssi_b200_dp_open(const void* ipc_handle, void** ptr);
 int ssi_b200_dp_close(void* ptr);
 int ssi_b200_dp_free(void* ptr);
-/* Synchronising check (set-up / tear-down class): *timed_out != 0 if a wait inside dp_exchange gave up after 20 s
- * because a peer never arrived (its process died); the gradients of that step are then invalid. */
+/* Synchronising check (set-up / tear-down class): *timed_out != 0 if a wait inside an exchange gave up after 20 s
+ * because a peer never arrived (its process died); the gradients of that step are NaN. */
 int ssi_b200_dp_status(const void* own_buf, int* timed_out);
-int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, uint32_t epoch,
-                         const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW, void* stream);
+int ssi_b200_dp_counts(void* const* peer_bufs, int rank, int world, uint32_t epoch, const int64_t* local_counts,
+                       int64_t* global_counts, float* hint_out, void* host_flag, void* stream);
+int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,
+                         uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW,
+                         void* host_flag, void* stream);
+int ssi_b200_dp_embedding_exchange(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
+                                   size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world, int64_t max_rows,
+                                   uint32_t epoch, void* dW, void* host_flag, void* stream);
+
+/* dst = bf16(float(dst) + float(src)) over n_elems bf16 values (NCCL exchange with gradient accumulation: only the
+ * NEW micro-batch's contribution is summed over ranks, then joins the existing gradient with this call). */
+int ssi_b200_grad_add(void* dst, const void* src, int64_t n_elems, void* stream);
 
 /*
  * labels_out[b, s] = labels[b, s+1] for s < S-1, ignore_index for s == S-1 (ssi/loss.py:16);
@@ -209,6 +261,10 @@ int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V,
  */
 int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int64_t ignore_index,
                                int64_t* labels_out, int64_t* counts, void* stream);
+
+/* counts[0] = counts[1] = #(labels != ignore_index) over a flat array of n (already shifted) labels
+ * (ce_chunked_output_loss.py:66): the local count a data-parallel loss call posts when the trainer announced none. */
+int ssi_b200_count_valid(const int64_t* labels, int64_t n, int64_t ignore_index, int64_t* counts, void* stream);
 
 /*
  * ---- Rows SURVEY.md 8(f) marks "next": the callers and data formats either side of the path (HBM-bound) ----

@@ -19,6 +19,9 @@
 #include "dp_exchange.cuh"
 #include "gemm.cuh"
 #include "next_rows.cuh"
+#include "scatter.cuh"
+
+#include <nvtx3/nvToolsExt.h>
 
 namespace {
 
@@ -48,10 +51,19 @@ struct ProfState {
   }
 };
 ProfState g_prof;
+const char* const kCatNames[CAT_COUNT] = {"ssi_b200:K1 logits+LSE", "ssi_b200:K2a dlogits", "ssi_b200:K2b dW",
+                                          "ssi_b200:K2c dX",        "ssi_b200:K3 embedding scatter",
+                                          "ssi_b200:aux",           "ssi_b200:softmax-grad",
+                                          "ssi_b200:K4 exchange"};
 struct ProfScope {
   cudaStream_t st;
   cudaEvent_t b = nullptr;
+  bool nvtx = false;
   ProfScope(int cat, cudaStream_t s) : st(s) {
+    if (cat >= 0 && cat < CAT_COUNT) {  // NVTX range around the enqueue (free when no tool is attached)
+      nvtxRangePushA(kCatNames[cat]);
+      nvtx = true;
+    }
     if (!g_prof.on || cat < 0) return;
     std::lock_guard<std::mutex> lk(g_prof.mu);
     cudaEvent_t a = g_prof.get();
@@ -61,6 +73,7 @@ struct ProfScope {
   }
   ~ProfScope() {
     if (b) cudaEventRecord(b, st);
+    if (nvtx) nvtxRangePop();
   }
 };
 
@@ -95,6 +108,7 @@ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 struct DeviceInfo {
   int ok = 0;  // 1 = sm_100, -1 = unusable
+  int dev = 0;
   int sms = 0;
   int cc_major = 0, cc_minor = 0;
   char why[256] = "";
@@ -111,6 +125,7 @@ int device_info(DeviceInfo** out) {
   if (d.ok == 0) {
     cudaDeviceProp prop;
     SSI_CUDA(cudaGetDeviceProperties(&prop, dev));
+    d.dev = dev;
     d.sms = prop.multiProcessorCount;
     d.cc_major = prop.major;
     d.cc_minor = prop.minor;
@@ -167,25 +182,39 @@ template <int EPI, bool A_MN, bool B_MN, int CG, int NW = 1>
 int launch_gemm_cg(const ssi::GemmParams& p, int sms, cudaStream_t st, const char* name, int cat, int grid_override,
                    bool prof = true) {
   auto kern = ssi::gemm_kernel<EPI, A_MN, B_MN, CG, NW>;
-  static bool attr_set = false;  // per instantiation
-  static int max_workers = 0;    // CTAs (CG 1) or CTA pairs (CG 2) that can be co-resident
-  if (!attr_set) {
-    SSI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::GEMM_SMEM_BYTES));
-    max_workers = sms / CG;
-    if (CG == 2) {
-      cudaLaunchConfig_t qc = {};
-      qc.gridDim = dim3(sms / 2 * 2), qc.blockDim = dim3(ssi::GEMM_THREADS);
-      qc.dynamicSmemBytes = ssi::GEMM_SMEM_BYTES;
-      cudaLaunchAttribute qa[1];
-      qa[0].id = cudaLaunchAttributeClusterDimension;
-      qa[0].val.clusterDim.x = 2, qa[0].val.clusterDim.y = 1, qa[0].val.clusterDim.z = 1;
-      qc.attrs = qa, qc.numAttrs = 1;
-      int n = 0;
-      SSI_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &qc));
-      if (n < 1) return fail(-5, "%s: no CTA pair can be resident (cudaOccupancyMaxActiveClusters = %d)", name, n);
-      if (n < max_workers) max_workers = n;
+  // cudaFuncSetAttribute and the occupancy answer are per DEVICE: cache them per (instantiation, device ordinal)
+  struct PerDev {
+    bool attr_set = false;
+    int max_workers = 0;  // CTAs (CG 1) or CTA pairs (CG 2) that can be co-resident
+  };
+  static PerDev per_dev[64];
+  static std::mutex mu;
+  int dev = 0;
+  SSI_CUDA(cudaGetDevice(&dev));
+  SSI_CHECK_ARG(dev >= 0 && dev < 64, "device ordinal %d out of range", dev);
+  int max_workers = 0;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    PerDev& pd = per_dev[dev];
+    if (!pd.attr_set) {
+      SSI_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::GEMM_SMEM_BYTES));
+      pd.max_workers = sms / CG;
+      if (CG == 2) {
+        cudaLaunchConfig_t qc = {};
+        qc.gridDim = dim3(sms / 2 * 2), qc.blockDim = dim3(ssi::GEMM_THREADS);
+        qc.dynamicSmemBytes = ssi::GEMM_SMEM_BYTES;
+        cudaLaunchAttribute qa[1];
+        qa[0].id = cudaLaunchAttributeClusterDimension;
+        qa[0].val.clusterDim.x = 2, qa[0].val.clusterDim.y = 1, qa[0].val.clusterDim.z = 1;
+        qc.attrs = qa, qc.numAttrs = 1;
+        int n = 0;
+        SSI_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &qc));
+        if (n < 1) return fail(-5, "%s: no CTA pair can be resident (cudaOccupancyMaxActiveClusters = %d)", name, n);
+        if (n < pd.max_workers) pd.max_workers = n;
+      }
+      pd.attr_set = true;
     }
-    attr_set = true;
+    max_workers = pd.max_workers;
   }
   const int tiles_m = (CG == 2) ? (p.tiles_m + 1) / 2 : p.tiles_m;
   const int items = tiles_m * ((p.tiles_n + NW - 1) / NW);  // host-side upper bound when the schedule is device-side
@@ -294,7 +323,10 @@ struct Tune {
   int tail_split = 1;  // wide tiles: split the items of an at most half-full last wave into 256x256 halves
   int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
 };
-Tune& tune() {
+// The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
+// thread-local SNAPSHOT under the mutex (TuneScope), so one call never sees half of an update.
+std::mutex g_tune_mu;
+Tune& global_tune() {
   static Tune t = [] {
     Tune x;
     if (const char* e = getenv("SSI_B200_G_CAP_MIB")) x.g_cap_elems = atoll(e) * (int64_t(1) << 19);
@@ -317,6 +349,14 @@ Tune& tune() {
   }();
   return t;
 }
+thread_local Tune tl_tune;
+struct TuneScope {
+  TuneScope() {
+    std::lock_guard<std::mutex> lk(g_tune_mu);
+    tl_tune = global_tune();
+  }
+};
+Tune& tune() { return tl_tune; }  // the snapshot of the running API call
 
 int cta_group() { return tune().cta_group; }
 int tail_split_opt() { return tune().tail_split; }
@@ -337,6 +377,13 @@ struct BwdPlan {
   size_t off_lse_c, off_g, off_dxacc, bytes;
 };
 
+// SM count of the current device for host-side schedules (148 on B200; queried, not assumed)
+int current_sms() {
+  DeviceInfo* di = nullptr;
+  if (device_info(&di) == 0 && di->sms > 0) return di->sms;
+  return 148;  // no usable device in this process (size queries on a build box): the B200 figure
+}
+
 BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   BwdPlan b;
   b.n_pad = ceil_div(N, ssi::BM) * ssi::BM;
@@ -350,7 +397,7 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   if (t_max < 4) t_max = 4;
   if (t_max > b.vtiles_total) t_max = b.vtiles_total;
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
-  const int sms = 148;
+  const int sms = current_sms();
   int64_t best_t = t_max;
   double best_cost = -1.0;
   for (int64_t t = (tune().g_tiles > 0 ? tune().g_tiles : 4); t <= t_max; ++t) {
@@ -423,24 +470,25 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
 }
 
 struct ScatPlan {
-  int blocks, nwarps, passes;
-  size_t off_k0, off_v0, off_k1, off_v1, off_hist, off_partial, off_info, bytes;
+  int nwarps, passes, slabs;
+  size_t off_k0, off_v0, off_k1, off_v1, off_urank, off_nuniq, off_partial, off_info, bytes;
 };
 
 ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
   ScatPlan s;
-  s.blocks = static_cast<int>(ceil_div(N, ssi::SORT_CHUNK));
   s.nwarps = static_cast<int>(ceil_div(N, 32));
+  s.slabs = static_cast<int>(ceil_div(D, ssi::SCAT_COLS));
   int bits = 1;
   while ((int64_t(1) << bits) <= V) ++bits;  // keys are in [0, V] (V = out-of-range sentinel)
-  s.passes = (bits + 7) / 8;
+  s.passes = (bits + ssi::SORT_BITS - 1) / ssi::SORT_BITS;
   size_t o = 0;
   const size_t arr = align_up(static_cast<size_t>(N) * 4, 256);
   s.off_k0 = o, o += arr;
   s.off_v0 = o, o += arr;
   s.off_k1 = o, o += arr;
   s.off_v1 = o, o += arr;
-  s.off_hist = o, o += align_up(static_cast<size_t>(256) * s.blocks * 4, 256);
+  s.off_urank = o, o += arr;
+  s.off_nuniq = o, o += 256;
   s.off_partial = o, o += align_up(static_cast<size_t>(s.nwarps) * 2 * D * sizeof(float), 256);
   s.off_info = o, o += align_up(static_cast<size_t>(s.nwarps) * sizeof(ssi::ScatInfo), 256);
   s.bytes = o;
@@ -467,7 +515,8 @@ const char* ssi_b200_last_error(void) { return g_err; }
 
 int ssi_b200_set_option(const char* name, int64_t value) {
   SSI_CHECK_ARG(name, "null option name");
-  Tune& t = tune();
+  std::lock_guard<std::mutex> lk(g_tune_mu);
+  Tune& t = global_tune();
   if (!strcmp(name, "g_cap_mib")) {
     SSI_CHECK_ARG(value >= 1, "g_cap_mib must be >= 1");
     t.g_cap_elems = value * (int64_t(1) << 19);
@@ -494,6 +543,7 @@ int64_t ssi_b200_launch_count(void) { return g_launches.load(std::memory_order_r
 
 int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes, size_t* bwd_bytes,
                              size_t* scatter_bytes) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
   if (fwd_bytes || bwd_bytes)
@@ -507,6 +557,7 @@ int ssi_b200_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* fwd_bytes,
 int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, int64_t N, int64_t V, int64_t D,
                            int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* ws,
                            size_t ws_bytes, void* stream) {
+  TuneScope tune_scope_;
   if (int r = check_common(X, W, N, V, D)) return r;
   SSI_CHECK_ARG(labels && lse && loss_out && n_valid && ws, "null pointer argument");
   DeviceInfo* di = nullptr;
@@ -559,6 +610,7 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   if (tune().lockstep_k1) {
     SSI_CUDA(cudaMemsetAsync(wsb + f.off_sync, 0, 256, st));
     p.sync_ctr = reinterpret_cast<unsigned int*>(wsb + f.off_sync), p.sync_every = 1;
+    p.sync_err = p.sync_ctr + 63;
   }
   if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_lse", CAT_LSE, di->sms)) return r;
 
@@ -577,6 +629,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
                            const float* grad_out, const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
                            int64_t ignore_index, void* dX, void* dW, int accumulate_dW, void* ws, size_t ws_bytes,
                            void* stream) {
+  TuneScope tune_scope_;
   if (int r = check_common(X, W, N, V, D)) return r;
   SSI_CHECK_ARG(labels && lse && grad_out && n_valid_total && dX && dW && ws, "null pointer argument");
   DeviceInfo* di = nullptr;
@@ -683,6 +736,7 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
 }
 
 int ssi_b200_single_pass_workspace_bytes(int64_t N, int64_t V, int64_t D, size_t* bytes) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(bytes, "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64 && D % 64 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
@@ -716,6 +770,30 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
                                      float* dW_acc, void* ws, size_t ws_bytes, void* stream, int accumulate_dW_acc,
                                      void* dw_acc_init_event, void* dw_ready_event, const void* norm_scale,
                                      float norm_eps, float* dscale) {
+  ssi_b200_fwd_grad_opts o;
+  memset(&o, 0, sizeof(o));
+  o.accumulate_dW_acc = accumulate_dW_acc, o.dw_acc_init_event = dw_acc_init_event, o.dw_ready_event = dw_ready_event;
+  o.norm_scale = norm_scale, o.norm_eps = norm_eps, o.dscale = dscale;
+  return ssi_b200_lmhead_ce_fwd_grad_ex(X, W, labels, grad_hint, n_valid_total, N, V, D, ignore_index, lse, loss_out,
+                                        n_valid, dX, dW_acc, ws, ws_bytes, stream, &o);
+}
+
+int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* labels, const float* grad_hint,
+                                   const int64_t* n_valid_total, int64_t N, int64_t V, int64_t D,
+                                   int64_t ignore_index, float* lse, float* loss_out, int64_t* n_valid, void* dX,
+                                   float* dW_acc, void* ws, size_t ws_bytes, void* stream,
+                                   const ssi_b200_fwd_grad_opts* opts) {
+  TuneScope tune_scope_;
+  ssi_b200_fwd_grad_opts defaults;
+  memset(&defaults, 0, sizeof(defaults));
+  if (!opts) opts = &defaults;
+  const int accumulate_dW_acc = opts->accumulate_dW_acc;
+  void* const dw_acc_init_event = opts->dw_acc_init_event;
+  void* const dw_ready_event = opts->dw_ready_event;
+  void* const pre_grad_event = opts->pre_grad_event;
+  const void* const norm_scale = opts->norm_scale;
+  const float norm_eps = opts->norm_eps;
+  float* const dscale = opts->dscale;
   if (int r = check_common(X, W, N, V, D)) return r;
   SSI_CHECK_ARG(!norm_scale || (dscale && (reinterpret_cast<uintptr_t>(norm_scale) & 15) == 0 && D <= 8192),
                 "fused norm needs a 16-byte aligned scale, a dscale output and D <= 8192");
@@ -803,7 +881,7 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
       p.part_m = part_m, p.part_l = part_l, p.part_z = part_z;
       p.part_stride = static_cast<int>(rows_cap);
       set_hints(p, tune().k1_hints);
-      if (tune().lockstep_k1) p.sync_ctr = sync_area + 256 + ch, p.sync_every = 1;
+      if (tune().lockstep_k1) p.sync_ctr = sync_area + 256 + ch, p.sync_err = sync_area + 1023, p.sync_every = 1;
       if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
         return r;
     }
@@ -814,6 +892,9 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
     }
     // ---- S -> G in place (softmax - onehot) * grad_hint / n_valid_total
     {
+      // data parallel: grad_hint / n_valid_total are filled by the counts exchange running on another stream beside
+      // the first logits contraction; this is the first consumer
+      if (ch == 0 && pre_grad_event) SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pre_grad_event), 0));
       ProfScope ps(CAT_SOFTMAX, st);
       ssi::softmax_grad_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(S), static_cast<int>(f.vpad / 8),
                                                             cplan, lse_c, labels_c, static_cast<int>(V), grad_hint,
@@ -835,7 +916,7 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
       if (ch == 0 && dw_acc_init_event)
         SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(dw_acc_init_event), 0));
       set_hints(p, tune().dw_hints);
-      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_every = lockstep;
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
         return r;
       // dW_acc is final after the last round's contraction (the real chunks occupy the last rounds): let the
@@ -852,7 +933,7 @@ int ssi_b200_lmhead_ce_fwd_grad_norm(const void* X, const void* W, const int64_t
       p.k_blocks = f.vtiles_total * (ssi::BN / ssi::BK);
       p.group_m = tune().group_m_dx;
       set_hints(p, tune().dx_hints);
-      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch + 1, p.sync_every = lockstep;
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch + 1, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX, tune().wide_dx))
         return r;
     }
@@ -920,95 +1001,108 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
 
 }  // extern "C"
 namespace {
-template <typename OutT>
-int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, OutT* dW,
-                                void* ws, size_t ws_bytes, void* stream, int phases = 3) {
-  // phases: bit 0 = sort the ids (leaves the order in ws), bit 1 = segmented reduction of dH rows in that order
-  SSI_CHECK_ARG(ws && (!(phases & 1) || ids) && (!(phases & 2) || (dH && dW)), "null pointer argument");
+// phases: bit 0 = sort the ids (leaves the order in ws), bit 1 = segmented reduction of the dH rows in that order
+template <int MODE>
+int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
+                                const ssi::ScatOut& out, void* ws, size_t ws_bytes, void* stream, int phases) {
+  SSI_CHECK_ARG(ws && (!(phases & 1) || ids) && (!(phases & 2) || dH), "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
-  SSI_CHECK_ARG(N < (int64_t(1) << 31) && V < (int64_t(1) << 31), "N/V too large");
-  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dH) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
-                "dH/dW must be 16-byte aligned");
+  SSI_CHECK_ARG(N < (int64_t(1) << 31) && V < (int64_t(1) << 31) - 1, "N/V too large");
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dH) & 15) == 0, "dH must be 16-byte aligned");
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const ScatPlan s = plan_scatter(N, V, D);
   SSI_CHECK_ARG(ws_bytes >= s.bytes, "scatter workspace too small: %zu < %zu", ws_bytes, s.bytes);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "scatter workspace must be 16-byte aligned");
   char* wsb = static_cast<char*>(ws);
   uint32_t* k[2] = {reinterpret_cast<uint32_t*>(wsb + s.off_k0), reinterpret_cast<uint32_t*>(wsb + s.off_k1)};
   uint32_t* v[2] = {reinterpret_cast<uint32_t*>(wsb + s.off_v0), reinterpret_cast<uint32_t*>(wsb + s.off_v1)};
-  uint32_t* hist = reinterpret_cast<uint32_t*>(wsb + s.off_hist);
+  int* urank = reinterpret_cast<int*>(wsb + s.off_urank);
+  int* nuniq = reinterpret_cast<int*>(wsb + s.off_nuniq);
   const int n = static_cast<int>(N);
 
   ProfScope ps_scat(CAT_SCATTER, st);
   if (phases & 1) {
-    ssi::sort_prepare_kernel<<<static_cast<int>(ceil_div(N, 256)), 256, 0, st>>>(ids, n, V, k[0], v[0]);
-    SSI_LAUNCH_OK("sort_prepare");
-  }
-  int cur = 0;
-  for (int pass = 0; pass < s.passes; ++pass) {
-    if (!(phases & 1)) {
-      cur ^= 1;
-      continue;
-    }
-    const int shift = pass * 8;
-    ssi::sort_hist_kernel<<<s.blocks, ssi::SORT_THREADS, 0, st>>>(k[cur], n, shift, hist, s.blocks);
-    SSI_LAUNCH_OK("sort_hist");
-    ssi::sort_scan_kernel<<<1, 1024, 0, st>>>(hist, 256 * s.blocks);
-    SSI_LAUNCH_OK("sort_scan");
-    ssi::sort_scatter_kernel<<<s.blocks, ssi::SORT_THREADS, 0, st>>>(k[cur], v[cur], k[cur ^ 1], v[cur ^ 1], n, shift,
-                                                                     hist, s.blocks);
-    SSI_LAUNCH_OK("sort_scatter");
-    cur ^= 1;
+    static std::once_flag once[64];
+    std::call_once(once[di->dev], [] {
+      cudaFuncSetAttribute(ssi::sort_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::SORT_SMEM_BYTES);
+    });
+    ssi::sort_block_kernel<<<1, ssi::SORT_THREADS, ssi::SORT_SMEM_BYTES, st>>>(ids, n, V, s.passes, k[0], v[0], k[1],
+                                                                               v[1], urank, nuniq);
+    SSI_LAUNCH_OK("sort_block");
   }
   if (!(phases & 2)) return 0;
+  const int cur = (s.passes - 1) & 1;
   float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
   ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
-  // 128-thread blocks (4 warps x ~190 registers = 24 K registers): small enough to co-reside with a persistent
-  // tensor-core CTA (K1: 192 threads x 128 registers) when this runs on a side stream beside the first contraction
-  const int grid = static_cast<int>(ceil_div(s.nwarps, 4));
-  ssi::scatter_reduce_kernel<OutT><<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], n,
-                                                         static_cast<uint32_t>(V), static_cast<int>(D), dW, partial, info);
+  // 128-thread blocks, no shared memory: small enough to co-reside with a persistent tensor-core CTA
+  const dim3 grid(static_cast<unsigned>(ceil_div(s.nwarps, 4)), static_cast<unsigned>(s.slabs));
+  ssi::scatter_reduce_kernel<MODE><<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], urank,
+                                                         n, static_cast<uint32_t>(V), static_cast<int>(D), out,
+                                                         partial, info);
   SSI_LAUNCH_OK("scatter_reduce");
-  ssi::scatter_fixup_kernel<OutT><<<grid, 128, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
-                                                        static_cast<int>(D), dW);
+  ssi::scatter_fixup_kernel<MODE><<<grid, 128, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
+                                                        static_cast<int>(D), out);
   SSI_LAUNCH_OK("scatter_fixup");
   return 0;
+}
+
+ssi::ScatOut dense_out(void* dW) {
+  ssi::ScatOut o;
+  memset(&o, 0, sizeof(o));
+  o.dense = dW;
+  return o;
 }
 }  // namespace
 extern "C" {
 
 int ssi_b200_embedding_grad_scatter(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* dW,
                                     void* ws, size_t ws_bytes, void* stream) {
-  return embedding_grad_scatter_impl(dH, ids, N, V, D, static_cast<__nv_bfloat16*>(dW), ws, ws_bytes, stream);
+  SSI_CHECK_ARG(dW && (reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be a 16-byte aligned device pointer");
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_BF16>(dH, ids, N, V, D, dense_out(dW), ws, ws_bytes, stream, 3);
 }
 
 int ssi_b200_embedding_grad_scatter_f32(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
                                         float* dW_acc, void* ws, size_t ws_bytes, void* stream) {
-  return embedding_grad_scatter_impl(dH, ids, N, V, D, dW_acc, ws, ws_bytes, stream);
+  SSI_CHECK_ARG(dW_acc && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0, "dW_acc must be 16-byte aligned");
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_F32>(dH, ids, N, V, D, dense_out(dW_acc), ws, ws_bytes, stream,
+                                                          3);
 }
 
 int ssi_b200_embedding_grad_sort(const int64_t* ids, int64_t N, int64_t V, int64_t D, void* ws, size_t ws_bytes,
                                  void* stream) {
-  return embedding_grad_scatter_impl<float>(nullptr, ids, N, V, D, nullptr, ws, ws_bytes, stream, 1);
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_F32>(nullptr, ids, N, V, D, dense_out(nullptr), ws, ws_bytes,
+                                                          stream, 1);
+}
+
+int ssi_b200_embedding_grad_scatter_sorted(const void* dH, int64_t N, int64_t V, int64_t D, void* dW, void* ws,
+                                           size_t ws_bytes, void* stream) {
+  SSI_CHECK_ARG(dW && (reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be a 16-byte aligned device pointer");
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_BF16>(dH, nullptr, N, V, D, dense_out(dW), ws, ws_bytes, stream,
+                                                           2);
 }
 
 int ssi_b200_embedding_grad_scatter_sorted_f32(const void* dH, int64_t N, int64_t V, int64_t D, float* dW_acc,
                                                void* ws, size_t ws_bytes, void* stream) {
-  return embedding_grad_scatter_impl<float>(dH, nullptr, N, V, D, dW_acc, ws, ws_bytes, stream, 2);
+  SSI_CHECK_ARG(dW_acc && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0, "dW_acc must be 16-byte aligned");
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_F32>(dH, nullptr, N, V, D, dense_out(dW_acc), ws, ws_bytes,
+                                                          stream, 2);
 }
 
 // ---------------------------------------------------------------------------------------------------
 // Data-parallel exchange of the tied gradient over NVLink peer memory (dp_exchange.cuh)
 // ---------------------------------------------------------------------------------------------------
-int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, size_t* bytes, size_t* dw_acc_offset) {
+int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, int64_t max_rows, size_t* bytes,
+                             size_t* dw_acc_offset) {
   SSI_CHECK_ARG(bytes, "null pointer argument");
   SSI_CHECK_ARG(V >= 1 && D >= 8 && D % 8 == 0, "bad shape V=%lld D=%lld", (long long)V, (long long)D);
   SSI_CHECK_ARG(world >= 1 && world <= ssi::DP_MAX_WORLD, "world size %d not in [1, %d]", world, ssi::DP_MAX_WORLD);
-  const int64_t vs = ceil_div(V, world);
-  *bytes = ssi::DP_CTRL_BYTES + static_cast<size_t>(V) * D * 4 + static_cast<size_t>(vs) * D * 2;
-  if (dw_acc_offset) *dw_acc_offset = ssi::DP_CTRL_BYTES;
+  SSI_CHECK_ARG(max_rows >= 0 && max_rows < (int64_t(1) << 31), "bad max_rows %lld", (long long)max_rows);
+  const ssi::DpLayout l = ssi::dp_layout(V, D, world, max_rows);
+  *bytes = l.bytes;
+  if (dw_acc_offset) *dw_acc_offset = l.off_acc;
   return 0;
 }
 
@@ -1018,7 +1112,7 @@ int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle) {
   if (int r = device_info(&di)) return r;
   void* p = nullptr;
   SSI_CUDA(cudaMalloc(&p, bytes));
-  SSI_CUDA(cudaMemset(p, 0, ssi::DP_CTRL_BYTES));
+  SSI_CUDA(cudaMemset(p, 0, bytes));  // flags, and slot entries whose stale epoch tags could match
   cudaIpcMemHandle_t h;
   cudaError_t e = cudaIpcGetMemHandle(&h, p);
   if (e != cudaSuccess) {
@@ -1060,36 +1154,63 @@ int ssi_b200_dp_status(const void* own_buf, int* timed_out) {
   return 0;
 }
 
-int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, uint32_t epoch,
-                         const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW, void* stream) {
-  SSI_CHECK_ARG(peer_bufs && grad_out && grad_hint && dW, "null pointer argument");
+namespace {
+int dp_peers(void* const* peer_bufs, int rank, int world, ssi::DpPeers* peers) {
+  SSI_CHECK_ARG(peer_bufs, "null pointer argument");
   SSI_CHECK_ARG(world >= 1 && world <= ssi::DP_MAX_WORLD && rank >= 0 && rank < world, "bad rank %d / world %d", rank,
                 world);
+  memset(peers, 0, sizeof(*peers));
+  for (int p = 0; p < world; ++p) {
+    SSI_CHECK_ARG(peer_bufs[p], "null exchange buffer for rank %d", p);
+    peers->buf[p] = static_cast<char*>(peer_bufs[p]);
+  }
+  return 0;
+}
+}  // namespace
+
+int ssi_b200_dp_counts(void* const* peer_bufs, int rank, int world, uint32_t epoch, const int64_t* local_counts,
+                       int64_t* global_counts, float* hint_out, void* host_flag, void* stream) {
+  SSI_CHECK_ARG(local_counts && global_counts, "null pointer argument");
+  ssi::DpPeers peers;
+  if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_EXCHANGE, st);
+  ssi::dp_counts_kernel<<<1, 32, 0, st>>>(peers, rank, world, epoch, local_counts, global_counts, hint_out,
+                                          static_cast<unsigned int*>(host_flag));
+  SSI_LAUNCH_OK("dp_counts");
+  return 0;
+}
+
+int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,
+                         uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW,
+                         void* host_flag, void* stream) {
+  SSI_CHECK_ARG(grad_out && grad_hint && dW, "null pointer argument");
+  ssi::DpPeers peers;
+  if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
   SSI_CHECK_ARG(V >= 1 && D >= 8 && D % 8 == 0, "bad shape V=%lld D=%lld", (long long)V, (long long)D);
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be 16-byte aligned");
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  ssi::DpPeers peers;
-  memset(&peers, 0, sizeof(peers));
-  for (int p = 0; p < world; ++p) {
-    SSI_CHECK_ARG(peer_bufs[p], "null exchange buffer for rank %d", p);
-    peers.buf[p] = static_cast<char*>(peer_bufs[p]);
-  }
+  const ssi::DpLayout lay = ssi::dp_layout(V, D, world, max_rows);
   const long long total_f4 = static_cast<long long>(V) * D / 4;
   const long long slice_f4 = static_cast<long long>(ceil_div(V, world)) * D / 4;
   const int grid = di->sms * 2;
   uint2* out = static_cast<uint2*>(dW);
+  unsigned int* hf = static_cast<unsigned int*>(host_flag);
   ProfScope ps(CAT_EXCHANGE, st);
-#define SSI_DP_CASE(W_)                                                                                          \
-  case W_:                                                                                                       \
-    ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, rank, slice_f4, total_f4, epoch, grad_out, \
-                                                                grad_hint, accumulate_dW ? 1 : 0, out);          \
-    SSI_LAUNCH_OK("dp_reduce");                                                                                  \
-    if (W_ > 1) {                                                                                                \
-      ssi::dp_gather_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, rank, slice_f4, total_f4, epoch, out);  \
-      SSI_LAUNCH_OK("dp_gather");                                                                                \
-    }                                                                                                            \
+#define SSI_DP_CASE(W_)                                                                                               \
+  case W_:                                                                                                            \
+    ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, grad_out, \
+                                                                grad_hint, accumulate_dW ? 1 : 0, out, hf);           \
+    SSI_LAUNCH_OK("dp_reduce");                                                                                       \
+    if (W_ > 1) {                                                                                                     \
+      ssi::dp_gather_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, out,   \
+                                                                  hf);                                                \
+      SSI_LAUNCH_OK("dp_gather");                                                                                     \
+    }                                                                                                                 \
     break;
   switch (world) {
     SSI_DP_CASE(1)
@@ -1107,6 +1228,59 @@ int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V,
   return 0;
 }
 
+int ssi_b200_dp_embedding_exchange(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
+                                   size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world, int64_t max_rows,
+                                   uint32_t epoch, void* dW, void* host_flag, void* stream) {
+  SSI_CHECK_ARG(dH && sort_ws && dW, "null pointer argument");
+  ssi::DpPeers peers;
+  if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
+  SSI_CHECK_ARG(N >= 1 && N <= max_rows, "N=%lld token rows do not fit the exchange buffer (max_rows=%lld)",
+                (long long)N, (long long)max_rows);
+  SSI_CHECK_ARG(V >= 1 && V < (int64_t(1) << 31) - 1 && D >= 8 && D % 8 == 0, "bad shape V=%lld D=%lld", (long long)V,
+                (long long)D);
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const ssi::DpLayout lay = ssi::dp_layout(V, D, world, max_rows);
+  // 1. this rank's dH rows, summed per distinct id, into its peer-visible compact list
+  ssi::ScatOut o;
+  memset(&o, 0, sizeof(o));
+  char* own = peers.buf[rank];
+  o.rows = reinterpret_cast<__nv_bfloat16*>(own + lay.off_rows);
+  o.ids = reinterpret_cast<int*>(own + lay.off_ids);
+  o.slot = reinterpret_cast<unsigned long long*>(own + lay.off_slot);
+  o.epoch = epoch;
+  o.cap = static_cast<int>(max_rows);
+  if (int r = embedding_grad_scatter_impl<ssi::SCAT_COMPACT>(dH, nullptr, N, V, D, o, sort_ws, sort_ws_bytes, stream, 2))
+    return r;
+  // 2. every id present on any rank: the ranks' rows added in rank order to the bf16 gradient row
+  unsigned int* hf = static_cast<unsigned int*>(host_flag);
+  const int grid = di->sms * 4;
+  __nv_bfloat16* g = static_cast<__nv_bfloat16*>(dW);
+  ProfScope ps(CAT_EXCHANGE, st);
+#define SSI_DP_CASE(W_)                                                                                        \
+  case W_:                                                                                                     \
+    ssi::dp_sparse_add_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),     \
+                                                                    static_cast<int>(D), epoch, g, hf);        \
+    break;
+  switch (world) {
+    SSI_DP_CASE(1)
+    SSI_DP_CASE(2)
+    SSI_DP_CASE(3)
+    SSI_DP_CASE(4)
+    SSI_DP_CASE(5)
+    SSI_DP_CASE(6)
+    SSI_DP_CASE(7)
+    SSI_DP_CASE(8)
+    default:
+      return fail(-1, "unsupported world size %d", world);
+  }
+#undef SSI_DP_CASE
+  SSI_LAUNCH_OK("dp_sparse_add");
+  return 0;
+}
+
 int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int64_t ignore_index,
                                int64_t* labels_out, int64_t* counts, void* stream) {
   SSI_CHECK_ARG(labels && labels_out && counts, "null pointer argument");
@@ -1121,6 +1295,21 @@ int ssi_b200_label_shift_count(const int64_t* labels, int64_t B, int64_t S, int6
   ssi::label_shift_count_kernel<<<grid, 256, 0, st>>>(labels, B, S, ignore_index, labels_out,
                                                       reinterpret_cast<unsigned long long*>(counts));
   SSI_LAUNCH_OK("label_shift_count");
+  return 0;
+}
+
+int ssi_b200_count_valid(const int64_t* labels, int64_t n, int64_t ignore_index, int64_t* counts, void* stream) {
+  SSI_CHECK_ARG(labels && counts, "null pointer argument");
+  SSI_CHECK_ARG(n >= 1, "bad length %lld", (long long)n);
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  SSI_CUDA(cudaMemsetAsync(counts, 0, 2 * sizeof(int64_t), st));
+  int grid = static_cast<int>(ceil_div(n, 1024));
+  if (grid > di->sms * 4) grid = di->sms * 4;
+  ProfScope ps(CAT_AUX, st);
+  ssi::count_valid_kernel<<<grid, 256, 0, st>>>(labels, n, ignore_index, reinterpret_cast<unsigned long long*>(counts));
+  SSI_LAUNCH_OK("count_valid");
   return 0;
 }
 
@@ -1250,6 +1439,34 @@ int ssi_b200_grad_scale_sqnorm(void* grad, int64_t n_elems, const float* scale, 
   return 0;
 }
 
+int ssi_b200_grad_add(void* dst, const void* src, int64_t n_elems, void* stream) {
+  SSI_CHECK_ARG(dst && src, "null pointer argument");
+  SSI_CHECK_ARG(n_elems >= 8 && n_elems % 8 == 0, "element count %lld must be a positive multiple of 8",
+                (long long)n_elems);
+  SSI_CHECK_ARG(((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15) == 0,
+                "dst / src must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_AUX, st);
+  ssi::grad_add_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(dst), static_cast<const uint4*>(src),
+                                                    static_cast<size_t>(n_elems) / 8);
+  SSI_LAUNCH_OK("grad_add");
+  return 0;
+}
+
+int ssi_b200_single_pass_lockstep_status(const void* ws, int64_t N, int64_t V, int64_t D, int* gave_up) {
+  TuneScope tune_scope_;
+  SSI_CHECK_ARG(ws && gave_up, "null pointer argument");
+  SpPlan f;
+  if (int r = plan_single_pass(N, V, D, &f)) return r;
+  unsigned int v = 0;
+  SSI_CUDA(cudaMemcpy(&v, static_cast<const char*>(ws) + f.off_sync + 1023 * sizeof(unsigned int), sizeof(v),
+                      cudaMemcpyDeviceToHost));
+  *gave_up = static_cast<int>(v);
+  return 0;
+}
+
 int ssi_b200_embedding_gather(const void* W, const int64_t* ids, int64_t N, int64_t V, int64_t D, void* out,
                               void* stream) {
   SSI_CHECK_ARG(W && ids && out, "null pointer argument");
@@ -1268,6 +1485,7 @@ int ssi_b200_embedding_gather(const void* W, const int64_t* ids, int64_t N, int6
 }
 
 int ssi_b200_plan_info(int64_t N, int64_t V, int64_t D, int64_t* out) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(out, "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 64 && D % 64 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
@@ -1307,6 +1525,7 @@ int ssi_b200_profile_end(double* ms_by_class, int64_t* launches_by_class) {
 
 int ssi_b200_debug_gemm(const void* A, const void* B, float* C, int64_t M, int64_t N, int64_t K, int a_mn_major,
                         int b_mn_major, int accumulate, void* stream) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(A && B && C, "null pointer argument");
   SSI_CHECK_ARG(M >= 1 && N >= 1 && K >= 1, "bad shape");
   SSI_CHECK_ARG(K % 8 == 0 && M % 8 == 0 && N % 8 == 0, "M, N, K must be multiples of 8 (16-byte TMA strides)");

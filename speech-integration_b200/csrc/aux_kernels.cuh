@@ -1,7 +1,6 @@
 // Small HBM-bound helper kernels around the tensor-core stages: split-V log-sum-exp combine and loss
-// reduction (fixed order, deterministic), fp32 -> bf16 cast of the dX accumulator, label shift + counts,
-// and the tied-embedding gradient scatter-add (stable LSD radix sort of ids + warp-level segmented
-// reduction in sorted order, no floating-point atomics).
+// reduction (fixed order, deterministic), fp32 -> bf16 cast of the dX accumulator, label shift + counts.
+// (The tied-embedding gradient scatter-add lives in scatter.cuh.)
 #pragma once
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
@@ -378,6 +377,24 @@ __global__ void __launch_bounds__(256) softmax_grad_kernel(uint4* __restrict__ S
   }
 }
 
+__device__ __forceinline__ void bf16x8_to_f32(const uint4& u, float (&f)[8]) {
+  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    f[2 * i] = __uint_as_float(w[i] << 16);
+    f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
+  }
+}
+
+__device__ __forceinline__ uint4 f32x8_to_bf16(const float (&f)[8]) {
+  uint4 o;
+  o.x = pack_bf16x2(f[0], f[1]);
+  o.y = pack_bf16x2(f[2], f[3]);
+  o.z = pack_bf16x2(f[4], f[5]);
+  o.w = pack_bf16x2(f[6], f[7]);
+  return o;
+}
+
 // lse[row] / per-block loss partials over ORIGINAL rows from the compact lse_c / loss_c (fixed order).
 __global__ void __launch_bounds__(COMBINE_THREADS) stash_finish_kernel(const float* __restrict__ lse_c,
                                                                        const float* __restrict__ loss_c,
@@ -506,295 +523,20 @@ __global__ void __launch_bounds__(256) label_shift_count_kernel(const int64_t* _
   if (threadIdx.x < 2 && s_c[threadIdx.x]) atomicAdd(&counts[threadIdx.x], static_cast<unsigned long long>(s_c[threadIdx.x]));
 }
 
-// ---------------------------------------------------------------------------------------------------
-// Embedding-gradient scatter-add: stable LSD radix sort of (id, row) then warp-segmented reduction.
-// ---------------------------------------------------------------------------------------------------
-constexpr int SORT_THREADS = 256;
-constexpr int SORT_ROUNDS = 8;
-constexpr int SORT_CHUNK = SORT_THREADS * SORT_ROUNDS;  // keys per block
-constexpr uint32_t KEY_NONE = 0xFFFFFFFFu;
-
-__global__ void __launch_bounds__(256) sort_prepare_kernel(const int64_t* __restrict__ ids, int n, long long V,
-                                                           uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i < n) {
-    const long long id = ids[i];
-    keys[i] = (id >= 0 && id < V) ? static_cast<uint32_t>(id) : static_cast<uint32_t>(V);  // out-of-range -> sentinel V
-    vals[i] = static_cast<uint32_t>(i);
-  }
-}
-
-// hist[d * B + b] = number of keys of block b whose digit is d
-__global__ void __launch_bounds__(SORT_THREADS) sort_hist_kernel(const uint32_t* __restrict__ keys, int n, int shift,
-                                                                 uint32_t* __restrict__ hist, int B) {
-  __shared__ uint32_t s_h[256];
-  s_h[threadIdx.x] = 0;
-  __syncthreads();
-  const int base = blockIdx.x * SORT_CHUNK;
+// counts[0] = counts[1] = #(labels != ignore_index) over a flat label array (labels that are already shifted: the
+// data-parallel loss module posts this as its local count when the trainer did not announce one)
+__global__ void __launch_bounds__(256) count_valid_kernel(const int64_t* __restrict__ labels, long long n,
+                                                          long long ignore_index,
+                                                          unsigned long long* __restrict__ counts) {
+  unsigned int c = 0;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    c += (labels[i] != ignore_index);
 #pragma unroll
-  for (int r = 0; r < SORT_ROUNDS; ++r) {
-    const int i = base + r * SORT_THREADS + threadIdx.x;
-    if (i < n) atomicAdd(&s_h[(keys[i] >> shift) & 255u], 1u);
-  }
-  __syncthreads();
-  hist[threadIdx.x * B + blockIdx.x] = s_h[threadIdx.x];
-}
-
-// in-place exclusive scan of `n` counters by one block
-__global__ void __launch_bounds__(1024) sort_scan_kernel(uint32_t* __restrict__ data, int n) {
-  __shared__ uint32_t s_sum[1024];
-  const int per = (n + 1023) / 1024;
-  const int b = threadIdx.x * per;
-  const int e = min(b + per, n);
-  uint32_t a = 0;
-  for (int i = b; i < e; ++i) a += data[i];
-  s_sum[threadIdx.x] = a;
-  __syncthreads();
-  // Hillis-Steele inclusive scan over the 1024 per-thread sums
-  for (int off = 1; off < 1024; off <<= 1) {
-    uint32_t v = 0;
-    if (threadIdx.x >= off) v = s_sum[threadIdx.x - off];
-    __syncthreads();
-    s_sum[threadIdx.x] += v;
-    __syncthreads();
-  }
-  uint32_t run = (threadIdx.x == 0) ? 0u : s_sum[threadIdx.x - 1];
-  for (int i = b; i < e; ++i) {
-    const uint32_t v = data[i];
-    data[i] = run;
-    run += v;
-  }
-}
-
-// stable scatter of one 8-bit digit pass
-__global__ void __launch_bounds__(SORT_THREADS) sort_scatter_kernel(const uint32_t* __restrict__ kin,
-                                                                    const uint32_t* __restrict__ vin,
-                                                                    uint32_t* __restrict__ kout,
-                                                                    uint32_t* __restrict__ vout, int n, int shift,
-                                                                    const uint32_t* __restrict__ offs, int B) {
-  __shared__ uint32_t s_base[256];
-  __shared__ uint32_t s_wc[SORT_THREADS / 32][256];
-  const int warp = threadIdx.x >> 5;
-  const uint32_t lane = threadIdx.x & 31;
-  s_base[threadIdx.x] = offs[threadIdx.x * B + blockIdx.x];
-  const int base = blockIdx.x * SORT_CHUNK;
-  for (int r = 0; r < SORT_ROUNDS; ++r) {
-    for (int i = threadIdx.x; i < (SORT_THREADS / 32) * 256; i += SORT_THREADS) (&s_wc[0][0])[i] = 0;
-    __syncthreads();
-    const int idx = base + r * SORT_THREADS + threadIdx.x;
-    const bool active = idx < n;
-    uint32_t key = 0, d = 0, rank = 0;
-    const unsigned amask = __ballot_sync(0xffffffffu, active);
-    if (active) {
-      key = kin[idx];
-      d = (key >> shift) & 255u;
-      const unsigned peers = __match_any_sync(amask, d);
-      rank = __popc(peers & ((1u << lane) - 1u));
-      if (rank == 0) s_wc[warp][d] = __popc(peers);
-    }
-    __syncthreads();
-    if (active) {
-      uint32_t pos = s_base[d] + rank;
-      for (int w = 0; w < warp; ++w) pos += s_wc[w][d];
-      kout[pos] = key;
-      vout[pos] = vin[idx];
-    }
-    __syncthreads();
-    uint32_t tot = 0;
-#pragma unroll
-    for (int w = 0; w < SORT_THREADS / 32; ++w) tot += s_wc[w][threadIdx.x];
-    s_base[threadIdx.x] += tot;
-    __syncthreads();
-  }
-}
-
-// One warp per 32 consecutive sorted positions. Runs of equal ids that lie strictly inside the warp's range
-// are reduced in fp32 (sorted order) and added to dW[id] with a single read-modify-write; runs that cross
-// the range boundary leave an fp32 partial row (slot 0 = continues from the previous warp, slot 1 =
-// continues into the next warp) which scatter_fixup_kernel chains together in order.
-constexpr int SCAT_COLS = 2048;  // columns handled per pass: 32 lanes x 8 groups x 8 bf16
-struct ScatInfo {
-  uint32_t slot0_key;  // KEY_NONE if no left-open run
-  uint32_t slot0_open_right;
-  uint32_t slot1_key;  // KEY_NONE if no right-open run that starts inside
-  uint32_t pad;
-};
-
-__device__ __forceinline__ void bf16x8_to_f32(const uint4& u, float (&f)[8]) {
-  const uint32_t w[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    f[2 * i] = __uint_as_float(w[i] << 16);
-    f[2 * i + 1] = __uint_as_float(w[i] & 0xFFFF0000u);
-  }
-}
-
-__device__ __forceinline__ void rmw_row(__nv_bfloat16* __restrict__ dst, int dcols, uint32_t lane,
-                                        const float (&acc)[8][8]) {
-#pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    const int col = g * 256 + lane * 8;
-    if (col < dcols) {
-      uint4* ptr = reinterpret_cast<uint4*>(dst + col);
-      const uint4 old = *ptr;
-      float f[8];
-      bf16x8_to_f32(old, f);
-      uint4 o;
-      o.x = pack_bf16x2(f[0] + acc[g][0], f[1] + acc[g][1]);
-      o.y = pack_bf16x2(f[2] + acc[g][2], f[3] + acc[g][3]);
-      o.z = pack_bf16x2(f[4] + acc[g][4], f[5] + acc[g][5]);
-      o.w = pack_bf16x2(f[6] + acc[g][6], f[7] + acc[g][7]);
-      *ptr = o;
-    }
-  }
-}
-
-// fp32 destination (data-parallel mode adds the embedding gradient to the fp32 dW sum before the exchange)
-__device__ __forceinline__ void rmw_row(float* __restrict__ dst, int dcols, uint32_t lane, const float (&acc)[8][8]) {
-#pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    const int col = g * 256 + lane * 8;
-    if (col < dcols) {
-      float4* ptr = reinterpret_cast<float4*>(dst + col);
-      float4 a = ptr[0], b = ptr[1];
-      a.x += acc[g][0], a.y += acc[g][1], a.z += acc[g][2], a.w += acc[g][3];
-      b.x += acc[g][4], b.y += acc[g][5], b.z += acc[g][6], b.w += acc[g][7];
-      ptr[0] = a, ptr[1] = b;
-    }
-  }
-}
-
-template <typename OutT>
-__global__ void __launch_bounds__(256) scatter_reduce_kernel(const __nv_bfloat16* __restrict__ dH,
-                                                             const uint32_t* __restrict__ skeys,
-                                                             const uint32_t* __restrict__ srows, int n, uint32_t V,
-                                                             int D, OutT* __restrict__ dW,
-                                                             float* __restrict__ partial,
-                                                             ScatInfo* __restrict__ info) {
-  const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t lane = threadIdx.x & 31;
-  const int p0 = wg * 32;
-  if (p0 >= n) return;
-  const int cnt = min(32, n - p0);
-  const uint32_t my_key = (static_cast<int>(lane) < cnt) ? skeys[p0 + lane] : KEY_NONE;
-  const uint32_t my_row = (static_cast<int>(lane) < cnt) ? srows[p0 + lane] : 0u;
-  const uint32_t prev_key = (p0 > 0) ? skeys[p0 - 1] : KEY_NONE;
-  const uint32_t next_key = (p0 + cnt < n) ? skeys[p0 + cnt] : KEY_NONE;
-  ScatInfo inf;
-  inf.slot0_key = KEY_NONE;
-  inf.slot0_open_right = 0;
-  inf.slot1_key = KEY_NONE;
-  inf.pad = 0;
-
-  for (int d0 = 0; d0 < D; d0 += SCAT_COLS) {
-    const int dcols = min(SCAT_COLS, D - d0);
-    float acc[8][8];
-#pragma unroll
-    for (int g = 0; g < 8; ++g)
-#pragma unroll
-      for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
-    int run_start = 0;
-    // software pipeline: the 8 x 16-byte loads of row i + 1 are in flight while row i is accumulated
-    uint4 u[8], un[8];
-    auto load_row = [&](int i, uint4 (&dst)[8]) {
-      const uint32_t row = __shfl_sync(0xffffffffu, my_row, i & 31);
-      const __nv_bfloat16* src = dH + static_cast<size_t>(row) * D + d0;
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        const int col = g * 256 + lane * 8;
-        dst[g] = (col < dcols) ? __ldg(reinterpret_cast<const uint4*>(src + col)) : make_uint4(0, 0, 0, 0);
-      }
-    };
-    load_row(0, u);
-    for (int i = 0; i < cnt; ++i) {
-      const uint32_t key = __shfl_sync(0xffffffffu, my_key, i);
-      const uint32_t nkey = (i + 1 < cnt) ? __shfl_sync(0xffffffffu, my_key, (i + 1) & 31) : KEY_NONE;
-      if (i + 1 < cnt) load_row(i + 1, un);
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        float f[8];
-        bf16x8_to_f32(u[g], f);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) acc[g][e] += f[e];
-      }
-#pragma unroll
-      for (int g = 0; g < 8; ++g) u[g] = un[g];
-      const bool end_of_run = (i == cnt - 1) || (nkey != key);
-      if (end_of_run) {
-        const bool open_left = (run_start == 0) && (prev_key == key);
-        const bool open_right = (i == cnt - 1) && (next_key == key);
-        if (!open_left && !open_right) {
-          if (key < V) rmw_row(dW + static_cast<size_t>(key) * D + d0, dcols, lane, acc);
-        } else {
-          const int slot = open_left ? 0 : 1;
-          float* pr = partial + (static_cast<size_t>(wg) * 2 + slot) * D + d0;
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            const int col = g * 256 + lane * 8;
-            if (col < dcols) {
-              *reinterpret_cast<float4*>(pr + col) = make_float4(acc[g][0], acc[g][1], acc[g][2], acc[g][3]);
-              *reinterpret_cast<float4*>(pr + col + 4) = make_float4(acc[g][4], acc[g][5], acc[g][6], acc[g][7]);
-            }
-          }
-          if (open_left) {
-            inf.slot0_key = key;
-            inf.slot0_open_right = open_right ? 1u : 0u;
-          } else {
-            inf.slot1_key = key;
-          }
-        }
-#pragma unroll
-        for (int g = 0; g < 8; ++g)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
-        run_start = i + 1;
-      }
-    }
-  }
-  if (lane == 0) info[wg] = inf;
-}
-
-// One warp per range whose last run continues into the next range(s): sum the chain of partials in order.
-template <typename OutT>
-__global__ void __launch_bounds__(256) scatter_fixup_kernel(const float* __restrict__ partial,
-                                                            const ScatInfo* __restrict__ info, int nwarps, uint32_t V,
-                                                            int D, OutT* __restrict__ dW) {
-  const int wg = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t lane = threadIdx.x & 31;
-  if (wg >= nwarps) return;
-  const uint32_t key = info[wg].slot1_key;
-  if (key == KEY_NONE) return;
-  for (int d0 = 0; d0 < D; d0 += SCAT_COLS) {
-    const int dcols = min(SCAT_COLS, D - d0);
-    float acc[8][8];
-    const float* pr = partial + (static_cast<size_t>(wg) * 2 + 1) * D + d0;
-#pragma unroll
-    for (int g = 0; g < 8; ++g) {
-      const int col = g * 256 + lane * 8;
-      float4 a = make_float4(0, 0, 0, 0), b = a;
-      if (col < dcols) {
-        a = *reinterpret_cast<const float4*>(pr + col);
-        b = *reinterpret_cast<const float4*>(pr + col + 4);
-      }
-      acc[g][0] = a.x, acc[g][1] = a.y, acc[g][2] = a.z, acc[g][3] = a.w;
-      acc[g][4] = b.x, acc[g][5] = b.y, acc[g][6] = b.z, acc[g][7] = b.w;
-    }
-    for (int w = wg + 1; w < nwarps; ++w) {
-      if (info[w].slot0_key != key) break;  // defensive: chain must continue with the same id
-      const float* q = partial + (static_cast<size_t>(w) * 2) * D + d0;
-#pragma unroll
-      for (int g = 0; g < 8; ++g) {
-        const int col = g * 256 + lane * 8;
-        if (col < dcols) {
-          const float4 a = *reinterpret_cast<const float4*>(q + col);
-          const float4 b = *reinterpret_cast<const float4*>(q + col + 4);
-          acc[g][0] += a.x, acc[g][1] += a.y, acc[g][2] += a.z, acc[g][3] += a.w;
-          acc[g][4] += b.x, acc[g][5] += b.y, acc[g][6] += b.z, acc[g][7] += b.w;
-        }
-      }
-      if (!info[w].slot0_open_right) break;
-    }
-    if (key < V) rmw_row(dW + static_cast<size_t>(key) * D + d0, dcols, lane, acc);
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c) {
+    atomicAdd(&counts[0], static_cast<unsigned long long>(c));
+    atomicAdd(&counts[1], static_cast<unsigned long long>(c));
   }
 }
 

@@ -1,12 +1,25 @@
 // Data-parallel exchange of the tied LM-head / embedding gradient over NVLink peer memory (one process per GPU,
 // one NVSwitch node).  Every rank exposes one exchange buffer to its peers (CUDA IPC):
 //
-//   [ctrl 4 KiB: arrive_a[8] | arrive_b[8] | local block counter]  [dW_acc fp32 V x D]  [stage bf16 Vs x D]
+//   [ctrl 4 KiB: flags, token counts]  [dW_acc fp32 V x D]  [stage bf16 Vs x D]
+//   [slot u64 V]  [emb_ids int32 cap]  [emb_rows bf16 cap x D]
 //
-// dW_acc is where the rank's own dW contraction (and its embedding scatter-add) accumulate in fp32; Vs =
-// ceil(V / world) is the height of the vocabulary slice a rank owns.  The exchange is two small-footprint kernels
-// (no shared memory, 256 threads per block) that co-reside with the persistent tensor-core CTAs of the dX
-// contraction still running on the main stream, so the transfer hides behind math:
+// dW_acc is where the rank's own dW contractions accumulate in fp32; Vs = ceil(V / world) is the height of the
+// vocabulary slice a rank owns.  The step has THREE exchanges, in the order a training step produces their inputs:
+//
+//   dp_counts_kernel   (start of the step) every rank stores its two token counts into every peer's ctrl block and
+//                      sums the `world` pairs: the global counts without a collective call on the critical path.
+//   dense exchange     (LM-head part, as soon as the last dW contraction is done -- behind the last dX contraction
+//                      and, in a full model, behind the decoder backward): dp_reduce_kernel + dp_gather_kernel below.
+//   sparse exchange    (embedding part; it only exists after the decoder backward has produced dH0): every rank
+//                      segment-reduces its dH0 rows by id into a compact list (scatter.cuh, SCAT_COMPACT: emb_rows,
+//                      emb_ids, slot[id] = epoch | index) and dp_sparse_add_kernel then adds, for every id present
+//                      on any rank, the ranks' rows in rank order (fp32) to the bf16 gradient row -- U x D x 2 bytes
+//                      per rank instead of a second dense V x D pass.
+//
+// The dense exchange is two small-footprint kernels (no shared memory, 256 threads per block) that co-reside with the
+// persistent tensor-core CTAs of the dX contraction still running on the main stream, so the transfer hides behind
+// math:
 //
 //   dp_reduce_kernel   rank r pulls slice r of every peer's fp32 dW_acc through NVLink, sums the `world` terms in
 //                      rank order in fp32 (bit-identical on every rank and run to run), applies the single-pass
@@ -34,14 +47,38 @@ constexpr int DP_THREADS = 256;
 struct DpCtrl {
   unsigned int arrive_a[DP_MAX_WORLD];  // written by peers: epoch of their last "dW_acc complete"
   unsigned int arrive_b[DP_MAX_WORLD];  // written by peers: epoch of their last "slice reduced"
+  unsigned int arrive_c[DP_MAX_WORLD];  // written by peers: epoch of their last "compact embedding rows published"
+  unsigned int arrive_n[DP_MAX_WORLD];  // written by peers: epoch of their last "token counts posted"
+  unsigned long long counts[2][DP_MAX_WORLD][2];  // [epoch & 1][rank] = {unshifted, shifted} valid-token counts
   unsigned int blocks_done;             // local: blocks of dp_reduce_kernel that finished (reset by the last one)
   unsigned int timed_out;               // local: set when a wait gave up (a peer never arrived): results are invalid
 };
+static_assert(sizeof(DpCtrl) <= DP_CTRL_BYTES, "ctrl block too large");
 constexpr unsigned long long DP_WAIT_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;  // a dead peer must not hang the GPU
+constexpr uint32_t BF16X2_NAN = 0x7FC07FC0u;
 
 struct DpPeers {
   char* buf[DP_MAX_WORLD];  // exchange buffer of every rank as mapped in THIS process (own buffer included)
 };
+
+// byte offsets inside an exchange buffer (identical on every rank)
+struct DpLayout {
+  size_t off_acc, off_stage, off_slot, off_ids, off_rows, bytes;
+  long long cap;  // rows of the compact embedding list
+};
+__host__ __device__ inline DpLayout dp_layout(long long V, long long D, int world, long long cap) {
+  DpLayout l;
+  auto up = [](size_t x) { return (x + 255) / 256 * 256; };
+  const long long vs = (V + world - 1) / world;
+  size_t o = DP_CTRL_BYTES;
+  l.off_acc = o, o += up(static_cast<size_t>(V) * D * 4);
+  l.off_stage = o, o += up(static_cast<size_t>(vs) * D * 2);
+  l.off_slot = o, o += up(static_cast<size_t>(V) * 8);
+  l.off_ids = o, o += up(static_cast<size_t>(cap) * 4);
+  l.off_rows = o, o += up(static_cast<size_t>(cap) * D * 2);
+  l.bytes = o, l.cap = cap;
+  return l;
+}
 
 __device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
   asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -75,9 +112,10 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
 }
 
 // wait until every peer's slot in `flags` (this rank's own ctrl block) has reached `epoch`; gives up after
-// DP_WAIT_TIMEOUT_NS and records it in *timed_out (checked by the host with ssi_b200_dp_status)
+// DP_WAIT_TIMEOUT_NS and records it in *timed_out and in the pinned host word `host_flag` (the host polls that
+// word without synchronising; the kernels then write NaN instead of sums so that no optimizer step can use them)
 __device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world, int rank, unsigned int epoch,
-                                            unsigned int* timed_out) {
+                                            unsigned int* timed_out, unsigned int* host_flag) {
   if (threadIdx.x < static_cast<unsigned>(world) && static_cast<int>(threadIdx.x) != rank) {
     // epochs only grow; the signed difference keeps the comparison valid across 32-bit wrap-around
     const unsigned long long t0 = global_timer_ns();
@@ -86,6 +124,8 @@ __device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world
       __nanosleep(64);
       if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > DP_WAIT_TIMEOUT_NS) {
         *timed_out = 1u;
+        if (host_flag) *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;  // pinned host word: no sync to read
+        __threadfence_system();
         break;
       }
     }
@@ -93,27 +133,83 @@ __device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world
   __syncthreads();
 }
 
+// timed_out is sticky: once a wait gave up nothing this rank exchanges can be trusted until the set-up is redone
+__device__ __forceinline__ bool dp_is_bad(const DpCtrl* ctrl) {
+  return *reinterpret_cast<const volatile unsigned int*>(&ctrl->timed_out) != 0u;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Token counts: one warp.  Lane p stores this rank's pair into rank p's ctrl block (own block included) and
+// releases arrive_n; then lane p waits for rank p's pair in the own block; out[0..1] = the sums over ranks,
+// hint_out (optional) = float(out[0]), the multiplier of ssi/trainer.py:393 on the global batch.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) dp_counts_kernel(DpPeers peers, int rank, int world, unsigned int epoch,
+                                                       const int64_t* __restrict__ local, int64_t* __restrict__ out,
+                                                       float* __restrict__ hint_out, unsigned int* host_flag) {
+  DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
+  const int p = threadIdx.x;
+  const int par = epoch & 1u;
+  if (p < world) {
+    DpCtrl* pc = reinterpret_cast<DpCtrl*>(peers.buf[p]);
+    volatile unsigned long long* dst = pc->counts[par][rank];
+    dst[0] = static_cast<unsigned long long>(local[0]);
+    dst[1] = static_cast<unsigned long long>(local[1]);
+    __threadfence_system();
+    st_release_sys(&pc->arrive_n[rank], epoch);
+  }
+  unsigned long long c0 = 0, c1 = 0;
+  if (p < world) {
+    const unsigned long long t0 = global_timer_ns();
+    unsigned int spins = 0;
+    while (static_cast<int>(ld_acquire_sys(&ctrl->arrive_n[p]) - epoch) < 0) {
+      __nanosleep(64);
+      if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > DP_WAIT_TIMEOUT_NS) {
+        ctrl->timed_out = 1u;
+        if (host_flag) *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;
+        __threadfence_system();
+        break;
+      }
+    }
+    const volatile unsigned long long* src = ctrl->counts[par][p];
+    c0 = src[0], c1 = src[1];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    c0 += __shfl_xor_sync(0xffffffffu, c0, o);
+    c1 += __shfl_xor_sync(0xffffffffu, c1, o);
+  }
+  if (p == 0) {
+    out[0] = static_cast<int64_t>(c0);
+    out[1] = static_cast<int64_t>(c1);
+    if (hint_out) hint_out[0] = static_cast<float>(static_cast<long long>(c0));
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Dense exchange of the fp32 LM-head sums
+// ---------------------------------------------------------------------------------------------------
 template <int WORLD>
-__global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, int rank, long long slice_f4,
-                                                               long long total_f4, unsigned int epoch,
-                                                               const float* __restrict__ grad_out,
+__global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, DpLayout lay, int rank,
+                                                               long long slice_f4, long long total_f4,
+                                                               unsigned int epoch, const float* __restrict__ grad_out,
                                                                const float* __restrict__ grad_hint, int accumulate,
-                                                               uint2* __restrict__ dW) {
+                                                               uint2* __restrict__ dW, unsigned int* host_flag) {
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
   // ---- announce: everything this rank contributes (its dW_acc) was finished by earlier kernels of this stream
   if (blockIdx.x == 0 && threadIdx.x < WORLD && static_cast<int>(threadIdx.x) != rank) {
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_a[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_a, WORLD, rank, epoch, &ctrl->timed_out);
+  dp_wait_all(ctrl->arrive_a, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  const bool bad = dp_is_bad(ctrl);  // a peer never arrived: NaN out, so that no optimizer step can use the result
 
   const float ratio = grad_ratio(grad_out, grad_hint);
   const long long begin = static_cast<long long>(rank) * slice_f4;
   const long long end = min(begin + slice_f4, total_f4);
   const float4* src[WORLD];
 #pragma unroll
-  for (int p = 0; p < WORLD; ++p) src[p] = reinterpret_cast<const float4*>(peers.buf[p] + DP_CTRL_BYTES);
-  uint2* stage = reinterpret_cast<uint2*>(peers.buf[rank] + DP_CTRL_BYTES + static_cast<size_t>(total_f4) * 16);
+  for (int p = 0; p < WORLD; ++p) src[p] = reinterpret_cast<const float4*>(peers.buf[p] + lay.off_acc);
+  uint2* stage = reinterpret_cast<uint2*>(peers.buf[rank] + lay.off_stage);
   constexpr int UNROLL = (WORLD <= 2) ? 4 : 2;
   const long long stride = static_cast<long long>(gridDim.x) * DP_THREADS;
   for (long long i0 = begin + blockIdx.x * static_cast<long long>(DP_THREADS) + threadIdx.x; i0 < end;
@@ -142,6 +238,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, in
       uint2 o;
       o.x = pack_bf16x2(a.x, a.y);
       o.y = pack_bf16x2(a.z, a.w);
+      if (bad) o.x = o.y = BF16X2_NAN;
       dW[i] = o;
       stage[i - begin] = o;
     }
@@ -162,19 +259,20 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, in
 }
 
 template <int WORLD>
-__global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, int rank, long long slice_f4,
-                                                               long long total_f4, unsigned int epoch,
-                                                               uint2* __restrict__ dW) {
+__global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, DpLayout lay, int rank,
+                                                               long long slice_f4, long long total_f4,
+                                                               unsigned int epoch, uint2* __restrict__ dW,
+                                                               unsigned int* host_flag) {
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
-  dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch, &ctrl->timed_out);
+  dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  const bool bad = dp_is_bad(ctrl);
   // bf16 slices move as 16-byte words: 2 of the fp32-quad units per word (slice_f4 is even, see the host side)
   const long long slice_u4 = slice_f4 / 2, total_u4 = total_f4 / 2;
   const long long stride = static_cast<long long>(gridDim.x) * DP_THREADS;
   uint4* out = reinterpret_cast<uint4*>(dW);
   for (int q = 1; q < WORLD; ++q) {
     const int p = (rank + q) % WORLD;  // start with a different peer on every rank
-    const uint4* stage =
-        reinterpret_cast<const uint4*>(peers.buf[p] + DP_CTRL_BYTES + static_cast<size_t>(total_f4) * 16);
+    const uint4* stage = reinterpret_cast<const uint4*>(peers.buf[p] + lay.off_stage);
     const long long begin = static_cast<long long>(p) * slice_u4;
     const long long n = min(slice_u4, total_u4 - begin);
     for (long long i0 = blockIdx.x * static_cast<long long>(DP_THREADS) + threadIdx.x; i0 < n; i0 += stride * 4) {
@@ -184,7 +282,115 @@ __global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, in
         if (i0 + u * stride < n) v[u] = ld_peer_u4(stage + i0 + u * stride);
 #pragma unroll
       for (int u = 0; u < 4; ++u)
-        if (i0 + u * stride < n) out[begin + i0 + u * stride] = v[u];
+        if (i0 + u * stride < n) {
+          if (bad) v[u] = make_uint4(BF16X2_NAN, BF16X2_NAN, BF16X2_NAN, BF16X2_NAN);
+          out[begin + i0 + u * stride] = v[u];
+        }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Sparse exchange of the embedding part.  Every rank has published (earlier kernels of this stream: scatter.cuh in
+// SCAT_COMPACT form) its compact list: emb_rows[u, :] = bf16 sum of its dH0 rows with the u-th distinct id and
+// slot[id] = (epoch << 32 | u).  Here every rank adds, for every vocabulary id present on ANY rank, the ranks' rows in
+// rank order in fp32 to its bf16 gradient row: one read-modify-write (one rounding) per touched row, the same
+// arithmetic in the same order on every rank, so the gradients stay bit-identical across ranks.
+// A warp looks at 32 / WP2 ids x WP2 ranks per iteration (one 8-byte peer load per lane).
+// ---------------------------------------------------------------------------------------------------
+constexpr int SPARSE_G = 4;                      // 16-byte column groups per lane and pass
+constexpr int SPARSE_COLS = 32 * SPARSE_G * 8;   // 1024 columns per pass
+
+template <int WORLD>
+__global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers, DpLayout lay, int rank, int V, int D,
+                                                                   unsigned int epoch, __nv_bfloat16* __restrict__ dW,
+                                                                   unsigned int* host_flag) {
+  constexpr int WP2 = WORLD <= 1 ? 1 : WORLD <= 2 ? 2 : WORLD <= 4 ? 4 : 8;
+  constexpr int PER = 32 / WP2;  // ids per warp iteration
+  DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
+  if (blockIdx.x == 0 && threadIdx.x < WORLD && static_cast<int>(threadIdx.x) != rank) {
+    __threadfence_system();
+    st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_c[rank], epoch);
+  }
+  dp_wait_all(ctrl->arrive_c, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  if (dp_is_bad(ctrl)) {  // poison the first gradient row: grad-norm and loss checks trip at once
+    if (blockIdx.x == 0)
+      for (int j = threadIdx.x; j < D / 2; j += DP_THREADS) reinterpret_cast<uint32_t*>(dW)[j] = BF16X2_NAN;
+    return;
+  }
+  const uint32_t lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * DP_THREADS + threadIdx.x) >> 5;
+  const int nw = (gridDim.x * DP_THREADS) >> 5;
+  const int sub = lane / WP2, pl = lane % WP2;
+  const unsigned long long* slot_p =
+      (pl < WORLD) ? reinterpret_cast<const unsigned long long*>(peers.buf[pl] + lay.off_slot) : nullptr;
+  for (long long v0 = static_cast<long long>(gw) * PER; v0 < V; v0 += static_cast<long long>(nw) * PER) {
+    const long long v = v0 + sub;
+    unsigned long long s = 0;
+    if (slot_p != nullptr && v < V) {
+      asm volatile("ld.global.L1::no_allocate.u64 %0, [%1];" : "=l"(s) : "l"(slot_p + v));
+    }
+    const bool present = (static_cast<unsigned int>(s >> 32) == epoch) && slot_p != nullptr && v < V &&
+                         static_cast<long long>(s & 0xFFFFFFFFull) < lay.cap;
+    const unsigned pm = __ballot_sync(0xffffffffu, present);
+    if (pm == 0) continue;
+    const unsigned int my_idx = static_cast<unsigned int>(s & 0xFFFFFFFFull);
+    for (int q = 0; q < PER; ++q) {
+      const unsigned m = (pm >> (q * WP2)) & ((1u << WP2) - 1u);
+      if (m == 0) continue;
+      __nv_bfloat16* drow = dW + static_cast<size_t>(v0 + q) * D;
+      for (int d0 = 0; d0 < D; d0 += SPARSE_COLS) {
+        const int dcols = min(SPARSE_COLS, D - d0);
+        float acc[SPARSE_G][8];
+#pragma unroll
+        for (int g = 0; g < SPARSE_G; ++g)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
+#pragma unroll
+        for (int pb = 0; pb < WORLD; pb += 4) {  // 4 peers' loads in flight, summed in rank order
+          uint4 u[4][SPARSE_G];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int p = pb + k;
+            if (p >= WORLD) break;
+            const unsigned int idx = __shfl_sync(0xffffffffu, my_idx, q * WP2 + p);
+            const bool has = (m >> p) & 1u;
+            const __nv_bfloat16* src =
+                reinterpret_cast<const __nv_bfloat16*>(peers.buf[p] + lay.off_rows) + static_cast<size_t>(idx) * D + d0;
+#pragma unroll
+            for (int g = 0; g < SPARSE_G; ++g) {
+              const int col = g * 256 + static_cast<int>(lane) * 8;
+              u[k][g] = (has && col < dcols) ? ld_peer_u4(reinterpret_cast<const uint4*>(src + col))
+                                             : make_uint4(0, 0, 0, 0);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            if (pb + k >= WORLD) break;
+#pragma unroll
+            for (int g = 0; g < SPARSE_G; ++g) {
+              acc[g][0] += bf16lo(u[k][g].x), acc[g][1] += bf16hi(u[k][g].x);
+              acc[g][2] += bf16lo(u[k][g].y), acc[g][3] += bf16hi(u[k][g].y);
+              acc[g][4] += bf16lo(u[k][g].z), acc[g][5] += bf16hi(u[k][g].z);
+              acc[g][6] += bf16lo(u[k][g].w), acc[g][7] += bf16hi(u[k][g].w);
+            }
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < SPARSE_G; ++g) {
+          const int col = g * 256 + static_cast<int>(lane) * 8;
+          if (col < dcols) {
+            uint4* ptr = reinterpret_cast<uint4*>(drow + d0 + col);
+            const uint4 old = *ptr;
+            uint4 o;
+            o.x = pack_bf16x2(bf16lo(old.x) + acc[g][0], bf16hi(old.x) + acc[g][1]);
+            o.y = pack_bf16x2(bf16lo(old.y) + acc[g][2], bf16hi(old.y) + acc[g][3]);
+            o.z = pack_bf16x2(bf16lo(old.z) + acc[g][4], bf16hi(old.z) + acc[g][5]);
+            o.w = pack_bf16x2(bf16lo(old.w) + acc[g][6], bf16hi(old.w) + acc[g][7]);
+            *ptr = o;
+          }
+        }
+      }
     }
   }
 }

@@ -76,7 +76,10 @@ struct GemmParams {
   // Lockstep throttle (EPI_BF16 / EPI_F32 only, uniform K loops): every `sync_every` k-blocks the producers of
   // all co-running tiles meet at a split-phase counter barrier, so the tiles of one wave stream the same
   // K window of their shared operands through L2 together instead of drifting apart.  nullptr = off.
+  // The throttle is a performance hint only: a wait that is not satisfied within LOCKSTEP_TIMEOUT_NS (part of the
+  // grid not resident: MPS, a debugger, a smaller device) sets *sync_err and the CTA runs un-throttled from then on.
   unsigned int* sync_ctr;
+  unsigned int* sync_err;
   int sync_every;
   // Device-side schedule (row compaction): when set, token-dependent sizes are read from *dplan at kernel start
   const DevPlan* dplan;
@@ -104,6 +107,26 @@ struct GemmParams {
 struct TileItem {
   int m, n0, ncount;
 };
+
+constexpr unsigned long long LOCKSTEP_TIMEOUT_NS = 2ull * 1000 * 1000;  // normal waits are a few microseconds
+
+// bounded spin of the lockstep throttle; returns false (and raises *err) when it gave up
+__device__ __forceinline__ bool lockstep_wait(const unsigned int* ctr, unsigned int target, unsigned int* err) {
+  unsigned int spins = 0;
+  unsigned long long t0 = 0;
+  while (static_cast<int>(ld_acquire_gpu(ctr) - target) < 0) {
+    if ((++spins & 255u) == 0) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > LOCKSTEP_TIMEOUT_NS) {
+        if (err) atomicExch(err, 1u);
+        return false;
+      }
+    }
+  }
+  return true;
+}
 
 struct Sched {
   int tiles_m, tiles_n, group_m, k_blocks, vtiles_per_split, vtiles_total, part_stride;
@@ -289,6 +312,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       const bool throttle_v = is_lse_epi<EPI>() && p.sync_ctr != nullptr && p.sync_every > 0 && cta_rank == 0 &&
                               workers > 1 && sc.k_blocks >= 2;
       const int v_pts = throttle_v ? sc.vtiles_per_split - 1 : 0;
+      bool wait_ok = true;  // false once a wait timed out: keep posting arrivals (others may still wait), stop waiting
       for (int item = worker; item < total_items; item += workers) {
         int h0, nh;
         const TileItem it = get_item(item, h0, nh);
@@ -301,10 +325,9 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
           for (int kb = 0; kb < sc.k_blocks; ++kb) {
             if (throttle_v && t >= 1) {
               if (kb == 0) atomicAdd(p.sync_ctr, 1u);
-              if (kb == (sc.k_blocks >> 1)) {
+              if (kb == (sc.k_blocks >> 1) && wait_ok) {
                 const unsigned int target = sync_base + static_cast<unsigned int>(t) * round_workers;
-                while (ld_acquire_gpu(p.sync_ctr) < target) {
-                }
+                wait_ok = lockstep_wait(p.sync_ctr, target, p.sync_err);
               }
             }
             if (throttle) {
@@ -315,8 +338,7 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               }
               if (kb == next_wait) {
                 const unsigned int target = sync_base + static_cast<unsigned int>(sync_j + 1) * round_workers;
-                while (ld_acquire_gpu(p.sync_ctr) < target) {
-                }
+                if (wait_ok) wait_ok = lockstep_wait(p.sync_ctr, target, p.sync_err);
                 ++sync_j;
                 next_wait = 0x7fffffff;
               }

@@ -245,6 +245,21 @@ __global__ void __launch_bounds__(256) grad_scale_sqnorm_kernel(uint4* __restric
   }
 }
 
+// dst = bf16(float(dst) + float(src)): one micro-batch's all-reduced contribution joins an existing gradient
+// (NCCL exchange with gradient accumulation: only the NEW contribution may be summed over ranks)
+__global__ void __launch_bounds__(256) grad_add_kernel(uint4* __restrict__ dst, const uint4* __restrict__ src,
+                                                       size_t n_u4) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_u4;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    float a[8], b[8];
+    bf16x8_to_f32(dst[i], a);
+    bf16x8_to_f32(src[i], b);
+#pragma unroll
+    for (int e = 0; e < 8; ++e) a[e] += b[e];
+    dst[i] = f32x8_to_bf16(a);
+  }
+}
+
 __global__ void __launch_bounds__(256) sqnorm_finalize_kernel(const float* __restrict__ partial, int n,
                                                               float* __restrict__ out) {
   __shared__ double s[256];

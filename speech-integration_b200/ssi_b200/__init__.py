@@ -6,8 +6,9 @@ Public surface (mirrors the reference's loss-module call signature, ssi/trainer.
 * :class:`HiddenPassthroughOutput` / :class:`TiedEmbeddingB200` / :func:`install` — model-side hooks
 * :mod:`ssi_b200.ops` — tensor-level wrappers over the C ABI in ``include/ssi_b200.h``
 * :class:`RMSNormB200` — the final norm in front of the path
-* :mod:`ssi_b200.dist` / :mod:`ssi_b200.peer` — data-parallel helpers (token-count all-reduce; exchange of the tied
-  gradient over NVLink peer memory or NCCL)
+* :mod:`ssi_b200.sync` / :mod:`ssi_b200.peer` / :mod:`ssi_b200.dist` — data parallelism behind ``install(model,
+  process_group=...)``: token counts, LM-head part and embedding part of the tied gradient exchanged over NVLink peer
+  memory (or NCCL) in the order a training step produces them
 
 Everything computes in ``libssi_b200.so`` (hand-written CUDA, tcgen05/TMEM/TMA); there is no CPU fallback.
 """

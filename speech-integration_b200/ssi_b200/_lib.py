@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 105
+ABI_VERSION = 110
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -51,6 +51,12 @@ SYMBOLS = {
          c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_int, c_void_p, c_void_p, c_void_p,
          ctypes.c_float, c_void_p],
     ),
+    "ssi_b200_lmhead_ce_fwd_grad_ex": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_void_p, c_void_p,
+         c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p],
+    ),
+    "ssi_b200_single_pass_lockstep_status": (c_int, [c_void_p, c_int64, c_int64, c_int64, POINTER(c_int)]),
     "ssi_b200_lmhead_ce_apply_grad": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p],
@@ -68,18 +74,33 @@ SYMBOLS = {
         c_int,
         [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
-    "ssi_b200_dp_buffer_bytes": (c_int, [c_int64, c_int64, c_int, POINTER(c_size_t), POINTER(c_size_t)]),
+    "ssi_b200_embedding_grad_scatter_sorted": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_dp_buffer_bytes": (c_int, [c_int64, c_int64, c_int, c_int64, POINTER(c_size_t), POINTER(c_size_t)]),
     "ssi_b200_dp_alloc": (c_int, [c_size_t, POINTER(c_void_p), c_void_p]),
     "ssi_b200_dp_open": (c_int, [c_void_p, POINTER(c_void_p)]),
     "ssi_b200_dp_close": (c_int, [c_void_p]),
     "ssi_b200_dp_free": (c_int, [c_void_p]),
     "ssi_b200_dp_status": (c_int, [c_void_p, POINTER(c_int)]),
+    "ssi_b200_dp_counts": (
+        c_int,
+        [POINTER(c_void_p), c_int, c_int, ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
+    ),
     "ssi_b200_dp_exchange": (
         c_int,
-        [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_int,
-         c_void_p],
+        [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p,
+         c_int, c_void_p, c_void_p],
     ),
+    "ssi_b200_dp_embedding_exchange": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, POINTER(c_void_p), c_int, c_int, c_int64,
+         ctypes.c_uint32, c_void_p, c_void_p, c_void_p],
+    ),
+    "ssi_b200_grad_add": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "ssi_b200_label_shift_count": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
+    "ssi_b200_count_valid": (c_int, [c_void_p, c_int64, c_int64, c_void_p, c_void_p]),
     "ssi_b200_rmsnorm_fwd": (c_int, [c_void_p, c_void_p, ctypes.c_float, c_int64, c_int64, c_void_p, c_void_p, c_void_p]),
     "ssi_b200_rmsnorm_bwd_workspace_bytes": (c_int, [c_int64, c_int64, POINTER(c_size_t)]),
     "ssi_b200_rmsnorm_bwd": (
@@ -101,6 +122,22 @@ SYMBOLS = {
         [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_void_p],
     ),
 }
+
+
+
+class FwdGradOpts(ctypes.Structure):
+    """``ssi_b200_fwd_grad_opts`` of include/ssi_b200.h."""
+
+    _fields_ = [
+        ("accumulate_dW_acc", c_int),
+        ("dw_acc_init_event", c_void_p),
+        ("dw_ready_event", c_void_p),
+        ("pre_grad_event", c_void_p),
+        ("norm_scale", c_void_p),
+        ("norm_eps", ctypes.c_float),
+        ("dscale", c_void_p),
+    ]
+
 
 _lib = None
 

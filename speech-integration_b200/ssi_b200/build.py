@@ -9,7 +9,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(os.path.dirname(_HERE), "csrc")
 OUT = os.path.join(_HERE, "libssi_b200.so")
 SOURCES = ["api.cu"]
-HEADERS = ["ptx.cuh", "gemm.cuh", "aux_kernels.cuh", "dp_exchange.cuh", "next_rows.cuh", os.path.join("..", "..", "include", "ssi_b200.h")]
+HEADERS = ["ptx.cuh", "gemm.cuh", "aux_kernels.cuh", "dp_exchange.cuh", "next_rows.cuh", "scatter.cuh", os.path.join("..", "..", "include", "ssi_b200.h")]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-lineinfo", "-std=c++17", "-shared", "-Xcompiler", "-fPIC",

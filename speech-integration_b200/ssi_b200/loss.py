@@ -9,7 +9,7 @@ the final normed HIDDEN states in those positions and this module does projectio
 from __future__ import annotations
 
 import os
-from typing import List, Sequence, Union
+from typing import Sequence, Union
 
 import torch
 from torch import nn
@@ -18,18 +18,24 @@ from . import ops
 
 
 class _FusedLinearCE(torch.autograd.Function):
-    """loss = mean_{valid rows} CE(X W^T, labels). Saves only X, W, labels and the per-row logsumexp."""
+    """Recompute mode.  loss = mean (or sum) over valid rows of CE(X W^T, labels); saves only X, W, labels and the
+    per-row logsumexp; backward recomputes the logits tiles."""
 
     @staticmethod
-    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override):
+    def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, reduction="mean"):
         loss_out, lse, n_valid = ops.lmhead_ce_fwd(X, W, labels, ignore_index)
         ctx.ignore_index = ignore_index
         ctx.holder = holder
-        n_div = n_valid if n_valid_override is None else n_valid_override
+        if reduction == "sum":
+            n_div = _ones_i64(X.device)
+        else:
+            n_div = n_valid if n_valid_override is None else n_valid_override
         ctx.save_for_backward(X, W, labels, lse, n_div)
         if holder is not None:
             holder.last_loss_sum = loss_out[0:1]
             holder.last_n_valid = n_valid
+        if reduction == "sum":
+            return loss_out[0]
         if n_valid_override is None:
             return loss_out[1]
         # data parallel: mean over the GLOBAL number of valid tokens (this rank's share of it)
@@ -44,6 +50,12 @@ class _FusedLinearCE(torch.autograd.Function):
         write_into_grad = (
             wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == W.data_ptr()
         )
+        sync = getattr(holder, "sync", None) if write_into_grad else None
+        if sync is not None:
+            # data parallel: this micro-batch's dW goes where it can be all-reduced alone (ssi_b200.sync)
+            target, acc = sync.recompute_target()
+            dX, _ = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index, dW=target, accumulate_dW=acc)
+            return dX, None, None, None, None, None, None
         if write_into_grad:
             # Write the LM-head gradient straight into the tied weight's .grad buffer (the buffer the
             # embedding scatter-add and the DP all-reduce also use) and hand autograd nothing to accumulate.
@@ -54,19 +66,27 @@ class _FusedLinearCE(torch.autograd.Function):
             else:
                 dX, _ = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index, dW=wparam.grad,
                                           accumulate_dW=True)
-            return dX, None, None, None, None, None
+            return dX, None, None, None, None, None, None
         dX, dW = ops.lmhead_ce_bwd(X, W, labels, lse, g, n_div, ctx.ignore_index)
-        return dX, dW, None, None, None, None
+        return dX, dW, None, None, None, None, None
 
 
-_ONES: dict = {}
+_CONST: dict = {}
 
 
 def _one(device: torch.device) -> torch.Tensor:
-    t = _ONES.get(device)
+    t = _CONST.get(("f", device))
     if t is None:
         t = torch.ones(1, dtype=torch.float32, device=device)
-        _ONES[device] = t
+        _CONST[("f", device)] = t
+    return t
+
+
+def _ones_i64(device: torch.device) -> torch.Tensor:
+    t = _CONST.get(("i", device))
+    if t is None:
+        t = torch.ones(1, dtype=torch.int64, device=device)
+        _CONST[("i", device)] = t
     return t
 
 
@@ -77,26 +97,46 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, X, W, labels, ignore_index, holder, n_valid_override, grad_hint, grad_enabled=True,
-                norm_scale=None, norm_eps=1e-6):
+                norm_scale=None, norm_eps=1e-6, reduction="mean"):
         ctx.holder = holder
         ctx.dscale = None
+        ctx.sync = None
         # `grad_enabled` is sampled by the caller: inside Function.forward grad mode is always off, and under
         # torch.no_grad() / inference_mode() (the eval path, ssi/eval.py:27-33) needs_input_grad still reports the
         # Parameter -- forming gradients there would triple the work of a forward-only call
         ctx.with_grad = bool(grad_enabled and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]
                                                or (norm_scale is not None and ctx.needs_input_grad[8])))
+        gcounts = None
         if ctx.with_grad:
             hint = _one(X.device) if grad_hint is None else grad_hint.detach().to(torch.float32).reshape(1)
+            announced = grad_hint is not None
+            kw = {}
+            sync = getattr(holder, "sync", None)
+            if sync is not None and reduction == "mean" and W.data_ptr() == holder.tied_module.weight.data_ptr():
+                # Data parallel (ssi_b200.sync): the local token counts are summed over ranks beside the first logits
+                # contraction; the divisor of the mean -- and the announced multiplier when it is "the global token
+                # count" -- are device scalars that the first softmax-grad pass reads.
+                local = getattr(holder, "local_counts", None)
+                if local is None:
+                    local = ops.count_valid(labels, ignore_index)
+                gcounts, ghint, ev = sync.global_counts(local)
+                n_valid_override = gcounts[1:2]
+                if getattr(holder, "hint_is_global_count", False):
+                    hint, announced = ghint, True
+                kw["pre_grad_event"] = ev
+                if sync.peer is not None:
+                    kw["dW_acc"], kw["dw_ready_event"] = sync.dw_acc, sync.dw_ready
+                ctx.sync = sync
+            nvt = _ones_i64(X.device) if reduction == "sum" else n_valid_override
             out = ops.lmhead_ce_fwd_grad(
-                X, W, labels, hint, n_valid_override, ignore_index,
-                dW_acc=getattr(holder, "dw_acc_buffer", None), dw_ready_event=getattr(holder, "dw_ready_event", None),
-                accumulate_dW_acc=getattr(holder, "dw_acc_initialised", False),
-                dw_acc_init_event=getattr(holder, "dw_acc_init_event", None),
-                norm_scale=norm_scale.detach() if norm_scale is not None else None, norm_eps=norm_eps)
+                X, W, labels, hint, nvt, ignore_index,
+                norm_scale=norm_scale.detach() if norm_scale is not None else None, norm_eps=norm_eps, **kw)
             loss_out, lse, n_valid, dX, dW_acc = out[:5]
             if norm_scale is not None:  # X was the PRE-norm state: dX is its gradient, dscale the scale's
                 ctx.dscale, ctx.scale_dtype = out[5], norm_scale.dtype
             ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
+            if ctx.sync is not None:
+                ctx.sync.after_forward(hint, announced)
         else:
             if norm_scale is not None:  # forward only (eval): the stand-alone norm kernel, then K1
                 X = ops.rmsnorm_fwd(X, norm_scale.detach(), norm_eps, want_rstd=False)[0]
@@ -104,6 +144,9 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         if holder is not None:
             holder.last_loss_sum = loss_out[0:1]
             holder.last_n_valid = n_valid
+            holder.last_global_counts = gcounts
+        if reduction == "sum":
+            return loss_out[0]
         if n_valid_override is None:
             return loss_out[1]
         return loss_out[0] / n_valid_override[0].to(torch.float32)
@@ -120,47 +163,112 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         if ctx.dscale is not None:  # gradient of the fused norm's scale, formed for `hint` like dX and dW_acc
             dscale = (ctx.dscale * (g / hint)).to(ctx.scale_dtype)
             ctx.dscale = None
+        nones = (None,) * 6
         wparam = holder.weight_param() if holder is not None else None
-        if holder is not None and getattr(holder, "defer_dw", False):
-            # data-parallel peer exchange (ssi_b200.peer / PathStep): the SUMMED fp32 dW is rounded into .grad by
-            # the exchange, which already runs behind the last dX contraction with the announced multiplier;
-            # here only dX is rescaled, and a wrong announcement is left visible instead of silently ignored.
-            ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
-            holder.grad_hint_mismatch = (g != hint)
-            return dX, None, None, None, None, None, None, None, dscale, None
-        if wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr:
+        tied = wparam is not None and holder.accumulate_into_grad and wparam.data_ptr() == ctx.w_ptr
+        sync = getattr(holder, "sync", None) if tied else None
+        if sync is not None:
+            # data parallel: dX is rescaled here; the LM-head gradient is summed over ranks by the exchange -- already
+            # running behind the last dX contraction when the multiplier was announced, started now otherwise
+            if ctx.sync is None and sync.peer is not None:
+                # formed outside the exchange buffer (compute_cross_entropy): move it there before it is exchanged
+                sync.dw_acc.copy_(dW_acc)
+                dW_acc = sync.dw_acc
+            sync.in_backward(dX, dW_acc, g, hint)
+            return (dX, None) + nones + (dscale, None, None)
+        if tied:
             acc = wparam.grad is not None
             if not acc:
                 wparam.grad = torch.empty_like(wparam)
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc)
-            return dX, None, None, None, None, None, None, None, dscale, None
+            return (dX, None) + nones + (dscale, None, None)
         _, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint)
-        return dX, dW, None, None, None, None, None, None, dscale, None
+        return (dX, dW) + nones + (dscale, None, None)
 
 
+class _ChunkAlias(torch.autograd.Function):
+    """The chunks a model hands over (``h.chunk(n, dim=1)``, tt/torchtune/modules/transformer.py:499-502) are adjacent
+    views of one contiguous ``[b, s, d]`` tensor: forward returns that tensor again as an alias of the chunks' memory
+    (no ``torch.cat`` copy), backward hands each chunk its slice of the gradient."""
+
+    @staticmethod
+    def forward(ctx, *chunks):
+        c0 = chunks[0]
+        ctx.sizes = [c.size(1) for c in chunks]
+        total = sum(ctx.sizes)
+        return torch.as_strided(c0.detach(), (c0.size(0), total, c0.size(2)), c0.stride(), c0.storage_offset())
+
+    @staticmethod
+    def backward(ctx, g):
+        out, o = [], 0
+        for n in ctx.sizes:
+            out.append(g[:, o:o + n])
+            o += n
+        return tuple(out)
+
+
+def _adjacent_chunks(chunks: Sequence[torch.Tensor]) -> bool:
+    """True if the ``[b, s_i, d]`` chunks are consecutive slices along dim 1 of one contiguous ``[b, sum s_i, d]``."""
+    c0 = chunks[0]
+    if c0.dim() != 3:
+        return False
+    b, _, d = c0.shape
+    total = sum(c.size(1) for c in chunks if c.dim() == 3)
+    if c0.stride() != (total * d, d, 1):
+        return False
+    base = c0.untyped_storage().data_ptr()
+    off = c0.storage_offset()
+    for c in chunks:
+        if (c.dim() != 3 or c.size(0) != b or c.size(2) != d or c.dtype != c0.dtype or c.device != c0.device
+                or c.stride() != c0.stride() or c.untyped_storage().data_ptr() != base or c.storage_offset() != off):
+            return False
+        off += c.size(1) * d
+    return True
+
+
+@torch.compiler.disable
 def fused_linear_cross_entropy(hidden: torch.Tensor, weight: torch.Tensor, labels: torch.Tensor,
                                ignore_index: int = -100, n_valid_total: torch.Tensor | None = None,
                                _holder=None, mode: str = "single_pass",
                                grad_hint: torch.Tensor | None = None, norm_scale: torch.Tensor | None = None,
-                               norm_eps: float = 1e-6) -> torch.Tensor:
+                               norm_eps: float = 1e-6, reduction: str = "mean") -> torch.Tensor:
     """Functional form: ``hidden [N, D]`` bf16, ``weight [V, D]`` bf16, ``labels [N]`` int64 -> fp32 0-dim loss.
 
     ``mode``: ``"single_pass"`` (default; gradients formed during forward, 6 N V D flop) or ``"recompute"``
     (forward keeps only the per-row logsumexp, backward recomputes the logits tiles, 8 N V D flop, no stash).
 
+    ``reduction``: ``"mean"`` over the valid rows (``n_valid_total``, an int64 device scalar, replaces the divisor:
+    data parallelism) or ``"sum"`` (0 when every row is ignored; ce_chunked_output_loss.py:41-43).
+
     ``norm_scale`` (bf16 ``[D]`` Parameter) / ``norm_eps``: ``hidden`` is the PRE-norm state and the final RMSNorm
     (tt/torchtune/modules/rms_norm.py:38-43) runs inside the path (single-pass mode: fused into its row gather and
-    dX scatter), with gradients for ``hidden`` and for the scale."""
+    dX scatter), with gradients for ``hidden`` and for the scale.
+
+    The call is opaque to ``torch.compile`` (``torch.compiler.disable``): the kernels are reached through ctypes, so
+    a compiled caller (``training.compile_loss`` wraps ``compute_cross_entropy``) runs it eagerly between graphs."""
+    if reduction not in ("mean", "sum"):
+        raise ValueError(f"ssi_b200: unknown reduction {reduction!r} (expected 'mean' or 'sum')")
     if mode == "recompute":
         if norm_scale is not None:  # no fused form in recompute mode: the stand-alone norm kernels in front
             from .model_hooks import _RMSNormFn
 
             hidden = _RMSNormFn.apply(hidden, norm_scale, norm_eps)
-        return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total)
+        sync = getattr(_holder, "sync", None)
+        if sync is not None and reduction == "mean" and torch.is_grad_enabled():
+            # data parallel: the divisor of the mean is the GLOBAL valid count (ssi_b200.sync, NCCL exchange)
+            local = getattr(_holder, "local_counts", None)
+            if local is None:
+                local = ops.count_valid(labels, ignore_index)
+            gcounts, _, ev = sync.global_counts(local)
+            if ev is not None:
+                torch.cuda.current_stream(hidden.device).wait_event(ev)
+            n_valid_total = gcounts[1:2]
+            _holder.last_global_counts = gcounts
+        return _FusedLinearCE.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, reduction)
     if mode != "single_pass":
         raise ValueError(f"ssi_b200: unknown mode {mode!r} (expected 'single_pass' or 'recompute')")
     return _FusedLinearCESinglePass.apply(hidden, weight, labels, ignore_index, _holder, n_valid_total, grad_hint,
-                                          torch.is_grad_enabled(), norm_scale, norm_eps)
+                                          torch.is_grad_enabled(), norm_scale, norm_eps, reduction)
 
 
 class FusedLinearCrossEntropyLoss(nn.Module):
@@ -182,6 +290,14 @@ class FusedLinearCrossEntropyLoss(nn.Module):
     loss before ``backward()`` (ssi/trainer.py:393 uses ``num_tokens_iter``). Purely an optimisation: with the
     right hint single-pass gradients are rounded to bf16 once; any other upstream gradient is still exact up to
     one extra bf16 rounding of dX.
+
+    Data parallelism (``install(model, process_group=...)`` sets ``sync``, see :mod:`ssi_b200.sync`): the training
+    forward returns ``local loss sum / GLOBAL valid count`` (the rank's share of the global mean) and the tied gradient
+    is summed over ranks.  ``local_counts`` (int64 ``[2]`` device tensor {unshifted, shifted} or None) lets the trainer
+    hand over counts it already has; ``hint_is_global_count = True`` announces the multiplier "global number of
+    unshifted valid tokens" (ssi/trainer.py:391-393 on the global batch), which the counts exchange produces on the
+    device; ``last_global_counts`` holds the summed counts of the last training forward.  Forward-only calls (eval,
+    ssi/eval.py:27-33) never use any of this: every rank gets the mean over ITS batch.
     """
 
     def __init__(self, tied_module: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
@@ -200,22 +316,21 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         if self.mode not in ("single_pass", "recompute"):
             raise ValueError(f"ssi_b200: unknown mode {self.mode!r} (expected 'single_pass' or 'recompute')")
         self.grad_hint: torch.Tensor | None = None
-        self.n_valid_total: torch.Tensor | None = None  # set by ssi_b200.dist for data parallelism
         self.last_loss_sum: torch.Tensor | None = None
         self.last_n_valid: torch.Tensor | None = None
-        # data-parallel peer exchange hooks (set by ssi_b200.step.PathStep): the fp32 accumulator to write into,
-        # the event to record once it is final, and "leave dW to the exchange" for backward
-        self.dw_acc_buffer: torch.Tensor | None = None
-        self.dw_ready_event: torch.cuda.Event | None = None
-        self.dw_acc_initialised: bool = False  # the caller pre-fills dw_acc_buffer (embedding gradient) every step
-        self.dw_acc_init_event: torch.cuda.Event | None = None
-        self.defer_dw: bool = False
-        self.grad_hint_mismatch: torch.Tensor | None = None
+        self.last_global_counts: torch.Tensor | None = None
+        object.__setattr__(self, "sync", None)  # ssi_b200.sync.TiedGradSync (data parallelism); not a submodule
+        self.local_counts: torch.Tensor | None = None
+        self.hint_is_global_count: bool = False
         object.__setattr__(self, "_norm", None)  # fused final RMSNorm (set_fused_norm); not a registered submodule
 
     @property
     def tied_module(self) -> nn.Module:
         return self._tied
+
+    @property
+    def grad_hint_mismatch(self):
+        return self.sync.grad_hint_mismatch if self.sync is not None else None
 
     def set_fused_norm(self, norm: nn.Module | None) -> None:
         """Take over the model's final RMSNorm (``model.norm``, applied at tt/torchtune/modules/transformer.py:653):
@@ -235,18 +350,25 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         return w if isinstance(w, nn.Parameter) else None
 
     def compute_cross_entropy(self, hidden: torch.Tensor, labels: torch.Tensor, normalize: bool = True):
-        """Sum-reduced CE of one chunk of hidden states (mirrors ce_chunked_output_loss.py:35-43, which takes
-        logits): returned so that ``training.compile_loss``-style wrappers that call it keep working."""
-        loss = fused_linear_cross_entropy(hidden.reshape(-1, hidden.size(-1)), self._tied.weight,
-                                          labels.reshape(-1), self.ignore_index, None, self, self.mode, self.grad_hint,
-                                          *self._norm_args())
-        return loss * self.last_n_valid[0].to(torch.float32)
+        """SUM-reduced CE of one chunk (ce_chunked_output_loss.py:35-43: ``F.cross_entropy(logits.float(), labels,
+        ignore_index, reduction="sum")``; 0 -- not NaN -- when every label of the chunk is ignored).  The reference
+        passes the chunk's logits; with the passthrough output installed the model hands over HIDDEN states and the
+        projection happens here.  ``training.compile_loss`` wraps exactly this method
+        (tt/torchtune/training/_compile.py:74-77); the fused call inside is opaque to ``torch.compile``."""
+        return fused_linear_cross_entropy(hidden.reshape(-1, hidden.size(-1)), self._tied.weight,
+                                          labels.reshape(-1).contiguous(), self.ignore_index, None, self, self.mode,
+                                          None, *self._norm_args(), reduction="sum")
 
     def forward(self, hidden: Union[torch.Tensor, Sequence[torch.Tensor]], labels: torch.Tensor) -> torch.Tensor:
         W = self._tied.weight
         if isinstance(hidden, (list, tuple)):
             # list of [b, s_c, D] chunks along dim 1 (tt/torchtune/modules/transformer.py:499-502)
-            h = hidden[0] if len(hidden) == 1 else torch.cat(list(hidden), dim=1)
+            if len(hidden) == 1:
+                h = hidden[0]
+            elif _adjacent_chunks(hidden):
+                h = _ChunkAlias.apply(*hidden)  # adjacent views of one contiguous tensor: no copy
+            else:
+                h = torch.cat(list(hidden), dim=1)
         else:
             h = hidden
         D = h.size(-1)
@@ -258,8 +380,8 @@ class FusedLinearCrossEntropyLoss(nn.Module):
             lab = lab.contiguous()
         if lab.numel() != X.size(0):
             raise ValueError(f"labels ({tuple(labels.shape)}) do not match hidden rows ({X.size(0)})")
-        return fused_linear_cross_entropy(X, W, lab, self.ignore_index, self.n_valid_total, self, self.mode,
-                                          self.grad_hint, *self._norm_args())
+        return fused_linear_cross_entropy(X, W, lab, self.ignore_index, None, self, self.mode, self.grad_hint,
+                                          *self._norm_args())
 
 
 def make_torchtune_subclass():

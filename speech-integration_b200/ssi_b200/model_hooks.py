@@ -37,15 +37,16 @@ class _EmbeddingFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, weight, tokens, module):
         ctx.module = module
-        ctx.save_for_backward(tokens)
-        ctx.wshape = weight.shape
-        if weight.dtype == torch.bfloat16 and weight.is_contiguous():
-            return ops.embedding_gather(weight, tokens)  # the library's own row gather
-        return torch.nn.functional.embedding(tokens, weight)
+        ids = tokens.reshape(-1)
+        if not ids.is_contiguous():
+            ids = ids.contiguous()
+        # the radix sort of the ids that the backward's segmented reduction needs depends on the ids only: start it
+        # here, so that nothing but the reduction itself is left for the tail of the step
+        ctx.sort_ws = ops.embedding_grad_sort(ids, weight.size(0), weight.size(1))
+        return ops.embedding_gather(weight, tokens)  # the library's own row gather
 
     @staticmethod
     def backward(ctx, grad_out):
-        (tokens,) = ctx.saved_tensors
         module = ctx.module
         w = module.weight
         D = grad_out.size(-1)
@@ -54,21 +55,30 @@ class _EmbeddingFn(torch.autograd.Function):
             dH = dH.to(torch.bfloat16)
         if not dH.is_contiguous():
             dH = dH.contiguous()
-        ids = tokens.reshape(-1)
-        if not ids.is_contiguous():
-            ids = ids.contiguous()
+        sort_ws, ctx.sort_ws = ctx.sort_ws, None
+        sync = getattr(module, "sync", None)
+        if sync is not None:
+            # data parallel: the LAST contribution of the micro-batch to the tied gradient (ssi_b200.sync)
+            sync.embedding_backward(dH, sort_ws)
+            return None, None, None
         if w.grad is None:
             w.grad = torch.zeros_like(w)
-        ops.embedding_grad_scatter(dH, ids, w.grad)
+        ops.embedding_grad_scatter_sorted(dH, sort_ws, w.grad)
         return None, None, None
 
 
 class TiedEmbeddingB200(nn.Embedding):
-    """``nn.Embedding`` (same parameter name ``weight``, same forward) with the B200 scatter-add backward."""
+    """``nn.Embedding`` (same parameter name ``weight``, same forward) with the B200 row gather forward and the
+    sorted-id segmented scatter-add backward.  bf16 CUDA weights only (anything else is ``nn.Embedding``'s job)."""
+
+    sync = None  # ssi_b200.sync.TiedGradSync when install() was given a process group
 
     def forward(self, tokens: torch.Tensor) -> torch.Tensor:
-        if self.weight.requires_grad and torch.is_grad_enabled() and self.weight.is_cuda:
-            return _EmbeddingFn.apply(self.weight, tokens, self)
+        w = self.weight
+        if w.is_cuda and w.dtype == torch.bfloat16 and w.is_contiguous() and self.max_norm is None:
+            if w.requires_grad and torch.is_grad_enabled():
+                return _EmbeddingFn.apply(w, tokens, self)
+            return ops.embedding_gather(w.detach(), tokens)  # eval / frozen: the same gather, nothing saved
         return super().forward(tokens)
 
     @classmethod
@@ -143,7 +153,8 @@ class FusedNormPassthrough(nn.Module):
 
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
             replace_embedding: bool = True, mode: str | None = None,
-            replace_norm: bool = False, fuse_norm: bool = False) -> FusedLinearCrossEntropyLoss:
+            replace_norm: bool = False, fuse_norm: bool = False, process_group=None,
+            exchange: str | None = None, max_tokens_per_rank: int = 65536) -> FusedLinearCrossEntropyLoss:
     """Mirror of ``Trainer._setup_loss`` (ssi/trainer.py:299-304) for the fused path.
 
     Replaces ``model.output`` by a hidden passthrough, optionally swaps ``model.tok_embeddings`` for
@@ -153,7 +164,13 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     ``model.norm`` (tt/torchtune/modules/transformer.py:653) for :class:`RMSNormB200`, sharing its ``scale``.
     ``fuse_norm``: instead, fuse that norm into the loss (row gather / dX scatter of single-pass mode):
     ``model.norm`` becomes a :class:`FusedNormPassthrough` and the model hands pre-norm hidden states to the loss.
-    """
+
+    ``process_group`` (one process per GPU; the reference's data-level scaffold is ``DistributedSampler``,
+    ssi/data/__init__.py:82-83): the tied gradient — and nothing else — is summed over the group's ranks, in the order
+    a training step produces its parts (:mod:`ssi_b200.sync`; semantics of tt/recipes/full_finetune_distributed.py:
+    844-851: losses are this rank's share of the global mean, gradients those of the global mean).  ``exchange``:
+    ``"peer"`` (default: the library's own NVLink peer-memory kernels) or ``"nccl"`` (bf16 all-reduce baseline);
+    ``max_tokens_per_rank`` sizes the compact-row area of the peer exchange (most token rows of one micro-batch)."""
     norm = getattr(model, "norm", None)
     fused_norm = None
     if fuse_norm:
@@ -175,4 +192,18 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
         loss_fn.set_fused_norm(fused_norm)
     if hasattr(model, "set_num_output_chunks"):
         model.set_num_output_chunks(loss_fn.num_output_chunks)
+    if process_group is not None:
+        if not isinstance(emb, TiedEmbeddingB200):
+            raise ValueError("ssi_b200.install(process_group=...): needs replace_embedding=True (the embedding "
+                             "backward is where a micro-batch's exchange of the tied gradient is completed)")
+        from .sync import TiedGradSync
+
+        if loss_fn.mode != "single_pass":
+            # the peer exchange sums the fp32 dW_acc that only single-pass mode forms
+            if exchange == "peer":
+                raise ValueError("ssi_b200: exchange='peer' needs mode='single_pass'")
+            exchange = exchange or "nccl"
+        sync = TiedGradSync(emb.weight, process_group, exchange=exchange, max_rows=max_tokens_per_rank)
+        object.__setattr__(loss_fn, "sync", sync)
+        object.__setattr__(emb, "sync", sync)
     return loss_fn

@@ -116,7 +116,8 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
                        n_valid_total: torch.Tensor | None = None, ignore_index: int = -100,
                        dW_acc: torch.Tensor | None = None, dw_ready_event: torch.cuda.Event | None = None,
                        accumulate_dW_acc: bool = False, dw_acc_init_event: torch.cuda.Event | None = None,
-                       norm_scale: torch.Tensor | None = None, norm_eps: float = 1e-6):
+                       norm_scale: torch.Tensor | None = None, norm_eps: float = 1e-6,
+                       pre_grad_event: torch.cuda.Event | None = None):
     """Single-pass mode: fused projection + CE forward that also forms the gradients (each logits tile is
     computed once). Returns ``(loss_out, lse, n_valid, dX, dW_acc)``; ``dX`` bf16 ``[N, D]`` and ``dW_acc`` fp32
     ``[V, D]`` are the gradients for an upstream gradient of ``grad_hint`` (fp32 device scalar);
@@ -125,7 +126,9 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     ``dW_acc``: optional existing fp32 ``[V, D]`` buffer to write into (data-parallel mode passes the view of its
     peer-visible exchange buffer); ``dw_ready_event``: recorded right after the last dW contraction;
     ``accumulate_dW_acc``: the caller initialised ``dW_acc`` and every dW contraction adds to it;
-    ``dw_acc_init_event``: the stream waits for it right before the first dW contraction.
+    ``dw_acc_init_event``: the stream waits for it right before the first dW contraction;
+    ``pre_grad_event``: the stream waits for it right before the first softmax-grad pass, the first reader of
+    ``grad_hint`` / ``n_valid_total`` (data parallel: both come from the counts exchange on another stream).
 
     ``norm_scale`` (bf16 ``[D]``): ``X`` holds the PRE-norm hidden states and the final RMSNorm
     (tt/torchtune/modules/rms_norm.py:38-43) is fused into the row gather / dX scatter of the path; ``dX`` is then
@@ -154,7 +157,7 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     if accumulate_dW_acc and dW_acc is None:
         raise ValueError("ssi_b200: accumulate_dW_acc needs an initialised dW_acc buffer")
     evs = []
-    for e in (dw_acc_init_event, dw_ready_event):
+    for e in (dw_acc_init_event, dw_ready_event, pre_grad_event):
         h = None
         if e is not None:
             h = e.cuda_event
@@ -167,14 +170,17 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
                 or norm_scale.device != dev):
             raise ValueError("ssi_b200: norm_scale must be a contiguous bf16 [D] tensor on the same device")
         dscale = torch.empty(D, dtype=torch.float32, device=dev)
+    import ctypes
+
+    opts = _lib.FwdGradOpts(1 if accumulate_dW_acc else 0, evs[0], evs[1], evs[2],
+                            norm_scale.data_ptr() if norm_scale is not None else None, float(norm_eps),
+                            dscale.data_ptr() if dscale is not None else None)
     with torch.cuda.device(dev):
-        rc = lib.ssi_b200_lmhead_ce_fwd_grad_norm(
+        rc = lib.ssi_b200_lmhead_ce_fwd_grad_ex(
             X.data_ptr(), W.data_ptr(), labels.data_ptr(), grad_hint.data_ptr(),
             n_valid_total.data_ptr() if n_valid_total is not None else None, N, V, D, int(ignore_index),
             lse.data_ptr(), loss_out.data_ptr(), n_valid.data_ptr(), dX.data_ptr(), dW_acc.data_ptr(),
-            ws.data_ptr(), ws.numel(), _stream(dev), 1 if accumulate_dW_acc else 0, evs[0], evs[1],
-            norm_scale.data_ptr() if norm_scale is not None else None, float(norm_eps),
-            dscale.data_ptr() if dscale is not None else None)
+            ws.data_ptr(), ws.numel(), _stream(dev), ctypes.byref(opts))
     _lib.check(rc, "lmhead_ce_fwd_grad")
     if norm_scale is not None:
         return loss_out, lse, n_valid, dX, dW_acc, dscale
@@ -262,16 +268,17 @@ def embedding_grad_scatter_f32(dH: torch.Tensor, ids: torch.Tensor, dW_acc: torc
 
 
 def embedding_grad_sort(ids: torch.Tensor, V: int, D: int) -> torch.Tensor:
-    """First half of :func:`embedding_grad_scatter_f32`: radix-sort the token ids on the current stream. Returns
-    the workspace holding the order; pass it to :func:`embedding_grad_scatter_sorted_f32` (any stream that is
-    ordered after this call)."""
+    """First half of the embedding-gradient scatter: radix-sort the token ids on the current stream (one launch; it
+    needs only the ids, so the embedding FORWARD can start it).  Returns a fresh workspace holding the order; pass it
+    to :func:`embedding_grad_scatter_sorted` / ``_sorted_f32`` / ``TiedGradExchange.embedding_exchange`` (any
+    stream that is ordered after this call)."""
     dev = _require_cuda(ids)
     if ids.dtype != torch.int64 or not ids.is_contiguous():
         raise ValueError("ssi_b200: ids must be contiguous int64")
     N = ids.numel()
     lib = _lib.load()
     _, _, sc_b = _lib.workspace_bytes(N, V, D, "scatter")
-    ws = _workspace("scatter_sorted", sc_b, dev)
+    ws = torch.empty(max(sc_b, 256), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         rc = lib.ssi_b200_embedding_grad_sort(ids.data_ptr(), N, V, D, ws.data_ptr(), ws.numel(), _stream(dev))
     _lib.check(rc, "embedding_grad_sort")
@@ -295,6 +302,36 @@ def embedding_grad_scatter_sorted_f32(dH: torch.Tensor, ws: torch.Tensor, dW_acc
     return dW_acc
 
 
+def embedding_grad_scatter_sorted(dH: torch.Tensor, ws: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
+    """``dW[id] += sum of the dH rows with that id`` (bf16 ``[V, D]``, the tied weight's ``.grad``) in the order
+    :func:`embedding_grad_sort` left in ``ws``."""
+    dev = _require_cuda(dH, ws, dW)
+    if dH.dtype != torch.bfloat16 or dW.dtype != torch.bfloat16 or dH.dim() != 2 or dW.dim() != 2:
+        raise TypeError("ssi_b200: expected bf16 dH [N, D] and bf16 dW [V, D]")
+    if dH.size(1) != dW.size(1) or not (dH.is_contiguous() and dW.is_contiguous()):
+        raise ValueError("ssi_b200: dH and dW must be contiguous with the same row length")
+    N, D = dH.shape
+    V = dW.size(0)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_embedding_grad_scatter_sorted(dH.data_ptr(), N, V, D, dW.data_ptr(), ws.data_ptr(),
+                                                                ws.numel(), _stream(dev))
+    _lib.check(rc, "embedding_grad_scatter_sorted")
+    return dW
+
+
+def grad_add(dst: torch.Tensor, src: torch.Tensor) -> torch.Tensor:
+    """``dst = bf16(float(dst) + float(src))`` in place for two contiguous bf16 tensors of the same shape."""
+    dev = _require_cuda(dst, src)
+    if dst.dtype != torch.bfloat16 or src.dtype != torch.bfloat16 or dst.shape != src.shape:
+        raise ValueError("ssi_b200: dst and src must be bf16 tensors of the same shape")
+    if not (dst.is_contiguous() and src.is_contiguous()) or dst.numel() % 8:
+        raise ValueError("ssi_b200: dst and src must be contiguous with a multiple of 8 elements")
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_grad_add(dst.data_ptr(), src.data_ptr(), dst.numel(), _stream(dev))
+    _lib.check(rc, "grad_add")
+    return dst
+
+
 def label_shift_count(labels: torch.Tensor, ignore_index: int = -100):
     """Shift labels left by one (ssi/loss.py:16) and count non-ignored tokens before/after the shift.
 
@@ -313,6 +350,19 @@ def label_shift_count(labels: torch.Tensor, ignore_index: int = -100):
                                             counts.data_ptr(), _stream(dev))
     _lib.check(rc, "label_shift_count")
     return out, counts
+
+
+def count_valid(labels: torch.Tensor, ignore_index: int = -100) -> torch.Tensor:
+    """int64 ``[2]`` device tensor, both entries = number of labels != ignore_index (flat, already shifted labels)."""
+    dev = _require_cuda(labels)
+    if labels.dtype != torch.int64 or not labels.is_contiguous():
+        raise ValueError("ssi_b200: labels must be a contiguous int64 tensor")
+    counts = torch.empty(2, dtype=torch.int64, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_count_valid(labels.data_ptr(), labels.numel(), int(ignore_index), counts.data_ptr(),
+                                              _stream(dev))
+    _lib.check(rc, "count_valid")
+    return counts
 
 
 def debug_gemm(A: torch.Tensor, B: torch.Tensor, a_mn_major: bool = False, b_mn_major: bool = False,

@@ -1,13 +1,20 @@
 """Peer-memory exchange of the tied LM-head / embedding gradient for one process per GPU on one
 NVSwitch node.
 
-Each rank owns one exchange buffer (ctrl flags | fp32 ``dW_acc [V, D]`` | bf16 stage slice) allocated by the
-library and mapped into every peer through CUDA IPC (``ssi_b200_dp_alloc`` / ``ssi_b200_dp_open``); the handles
-travel through ``torch.distributed`` (any backend: NCCL on the GPUs, gloo in tests).  ``exchange()`` enqueues the
-two kernels of ``csrc/dp_exchange.cuh``: rank r sums vocabulary slice r of all ranks' fp32 ``dW_acc`` over NVLink
-P2P loads in rank order, rounds ONCE to bf16, and every rank then pulls the finished slices — the result is
-bit-identical on every rank and run to run, and the whole exchange co-resides with the tensor-core CTAs of the
-last dX contraction (no shared memory), so it hides behind math instead of following it.
+Each rank owns one exchange buffer (ctrl flags + token counts | fp32 ``dW_acc [V, D]`` | bf16 stage slice | slot
+table | compact embedding rows) allocated by the library and mapped into every peer through CUDA IPC
+(``ssi_b200_dp_alloc`` / ``ssi_b200_dp_open``); the handles travel through ``torch.distributed`` (any backend: NCCL on
+the GPUs, gloo in tests).  Three exchanges per step, in the order a training step produces their inputs
+(``csrc/dp_exchange.cuh``):
+
+* ``counts()`` — the two token counts summed over ranks through 8-byte peer stores (no collective call);
+* ``exchange()`` — the LM-head part: rank r sums vocabulary slice r of all ranks' fp32 ``dW_acc`` over NVLink P2P
+  loads in rank order, rounds ONCE to bf16, and every rank then pulls the finished slices; it co-resides with the
+  tensor-core CTAs of the last dX contraction (no shared memory), so it hides behind math instead of following it;
+* ``embedding_exchange()`` — the embedding part, which only exists after the decoder backward: every rank publishes
+  its dH0 rows summed per distinct id (compact list) and adds all ranks' rows, in rank order, to its gradient rows.
+
+The result is bit-identical on every rank and run to run.
 
 There is no reference counterpart (the reference trains on one GPU); semantics are those of torchtune's
 distributed recipe (tt/recipes/full_finetune_distributed.py:844-851,867): gradients of the global mean.
@@ -36,11 +43,11 @@ class TiedGradExchange:
     """Owns this rank's exchange buffer and the mappings of its peers' buffers.
 
     Attributes:
-        dw_acc: fp32 ``[V, D]`` tensor view of the peer-visible accumulator; hand it to the single-pass forward
-            (``FusedLinearCrossEntropyLoss.dw_acc_buffer``) and to ``ops.embedding_grad_scatter_f32``.
+        dw_acc: fp32 ``[V, D]`` tensor view of the peer-visible accumulator; hand it to the single-pass forward.
+        max_rows: most token rows one ``embedding_exchange`` call may carry (sizes the compact-row area).
     """
 
-    def __init__(self, V: int, D: int, group=None, device: torch.device | None = None):
+    def __init__(self, V: int, D: int, group=None, device: torch.device | None = None, max_rows: int = 0):
         if not dist.is_initialized():
             raise RuntimeError("ssi_b200.peer: torch.distributed is not initialised")
         self.group = group
@@ -50,11 +57,12 @@ class TiedGradExchange:
             raise RuntimeError(f"ssi_b200.peer: world size {self.world} > {MAX_WORLD} (one NVSwitch node)")
         self.device = device or torch.device("cuda", torch.cuda.current_device())
         self.V, self.D = int(V), int(D)
-        self.epoch = 0
+        self.max_rows = int(max_rows)
+        self.epoch_dense = self.epoch_sparse = self.epoch_counts = 0
         lib = _lib.load()
         nbytes, off = ctypes.c_size_t(0), ctypes.c_size_t(0)
-        _lib.check(lib.ssi_b200_dp_buffer_bytes(self.V, self.D, self.world, ctypes.byref(nbytes), ctypes.byref(off)),
-                   "dp_buffer_bytes")
+        _lib.check(lib.ssi_b200_dp_buffer_bytes(self.V, self.D, self.world, self.max_rows, ctypes.byref(nbytes),
+                                                ctypes.byref(off)), "dp_buffer_bytes")
         self.nbytes, self._acc_off = nbytes.value, off.value
         own = ctypes.c_void_p(0)
         handle = (ctypes.c_ubyte * 64)()
@@ -103,26 +111,76 @@ class TiedGradExchange:
         self._ptr_array = (ctypes.c_void_p * self.world)(*self._peer_ptrs)
         self.dw_acc = torch.as_tensor(_DevicePtr(self._own + self._acc_off, (self.V, self.D), "<f4"),
                                       device=self.device)
+        # pinned host word a timed-out wait sets to 1: polled by check() without any device synchronisation
+        self._host_flag = torch.zeros(1, dtype=torch.int32).pin_memory()
         # every rank must have mapped (and zero-initialised) its buffers before the first exchange touches them
         torch.cuda.synchronize(self.device)
         dist.barrier(group=group)
+
+    # ------------------------------------------------------------------------------------------------ exchanges
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def check(self) -> None:
+        """Raise if an earlier exchange timed out waiting for a peer (reads a pinned host word: no device sync)."""
+        if self._host_flag is not None and int(self._host_flag[0]) != 0:
+            raise RuntimeError("ssi_b200.peer: an exchange timed out waiting for a peer; the gradients of that step "
+                               "were replaced by NaN")
+
+    def counts(self, local_counts: torch.Tensor):
+        """Enqueue on the current stream: returns ``(global_counts int64 [2], hint fp32 [1])`` = the int64 ``[2]``
+        ``local_counts`` summed over ranks, and ``float(global_counts[0])``."""
+        if local_counts.dtype != torch.int64 or local_counts.numel() != 2 or local_counts.device != self.device:
+            raise ValueError("ssi_b200.peer: local_counts must be an int64 [2] tensor on the exchange device")
+        self.check()
+        self.epoch_counts += 1
+        out = torch.empty(2, dtype=torch.int64, device=self.device)
+        hint = torch.empty(1, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = _lib.load().ssi_b200_dp_counts(self._ptr_array, self.rank, self.world,
+                                                self.epoch_counts & 0xFFFFFFFF, local_counts.data_ptr(), out.data_ptr(),
+                                                hint.data_ptr(), self._host_flag.data_ptr(), self._stream())
+        _lib.check(rc, "dp_counts")
+        return out, hint
 
     def exchange(self, dW: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
                  accumulate: bool = False) -> torch.Tensor:
         """Enqueue on the current stream: ``dW = bf16((accumulate ? dW : 0) + grad_out / grad_hint * sum_ranks
         dw_acc)`` on every rank.  Every rank must call it the same number of times."""
+        self._check_dw(dW)
+        self.epoch_dense += 1
+        with torch.cuda.device(self.device):
+            rc = _lib.load().ssi_b200_dp_exchange(self._ptr_array, self.rank, self.world, self.V, self.D,
+                                                  self.max_rows, self.epoch_dense & 0xFFFFFFFF, grad_out.data_ptr(),
+                                                  grad_hint.data_ptr(), dW.data_ptr(), 1 if accumulate else 0,
+                                                  self._host_flag.data_ptr(), self._stream())
+        _lib.check(rc, "dp_exchange")
+        return dW
+
+    def embedding_exchange(self, dH: torch.Tensor, sort_ws: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
+        """Enqueue on the current stream: ``dW[id] += sum over ranks (rank order) of that rank's dH rows with this
+        id`` on every rank; ``sort_ws`` from :func:`ssi_b200.ops.embedding_grad_sort` of this rank's ids.  Must be
+        stream-ordered after this step's :meth:`exchange`."""
+        self._check_dw(dW)
+        if dH.dtype != torch.bfloat16 or dH.dim() != 2 or dH.size(1) != self.D or not dH.is_contiguous():
+            raise ValueError("ssi_b200.peer: dH must be a contiguous bf16 [N, D] tensor")
+        if dH.size(0) > self.max_rows:
+            raise RuntimeError(f"ssi_b200.peer: {dH.size(0)} token rows exceed max_rows={self.max_rows} of the "
+                               "exchange buffer; pass a larger max_rows (install(..., max_tokens_per_rank=...))")
+        self.epoch_sparse += 1
+        with torch.cuda.device(self.device):
+            rc = _lib.load().ssi_b200_dp_embedding_exchange(
+                dH.data_ptr(), dH.size(0), self.V, self.D, sort_ws.data_ptr(), sort_ws.numel(), self._ptr_array,
+                self.rank, self.world, self.max_rows, self.epoch_sparse & 0xFFFFFFFF, dW.data_ptr(),
+                self._host_flag.data_ptr(), self._stream())
+        _lib.check(rc, "dp_embedding_exchange")
+        return dW
+
+    def _check_dw(self, dW: torch.Tensor) -> None:
         if tuple(dW.shape) != (self.V, self.D) or dW.dtype != torch.bfloat16 or not dW.is_contiguous():
             raise ValueError("ssi_b200.peer: dW must be a contiguous bf16 [V, D] tensor")
         if dW.device != self.device:
             raise ValueError("ssi_b200.peer: dW is on another device than the exchange buffer")
-        self.epoch += 1
-        with torch.cuda.device(self.device):
-            rc = _lib.load().ssi_b200_dp_exchange(self._ptr_array, self.rank, self.world, self.V, self.D,
-                                                  self.epoch & 0xFFFFFFFF, grad_out.data_ptr(), grad_hint.data_ptr(),
-                                                  dW.data_ptr(), 1 if accumulate else 0,
-                                                  torch.cuda.current_stream(self.device).cuda_stream)
-        _lib.check(rc, "dp_exchange")
-        return dW
 
     def timed_out(self) -> bool:
         """True if a wait inside an exchange gave up because a peer never arrived (synchronises)."""

@@ -139,3 +139,21 @@ def make_inputs(cfg: PathConfig, rank: int = 0, batch: int | None = None, seq: i
     X = torch.randn(B, S, hidden, generator=g).to(torch.bfloat16)
     dH0 = (torch.randn(B, S, hidden, generator=g) * 1e-3).to(torch.bfloat16)
     return {"W": W, "X": X, "dH0": dH0, "tokens": tokens, "labels": labels}
+
+
+def global_batch_rows(cfg: PathConfig, b0: int, b1: int, device, hidden: int = HIDDEN, seed: int = SEED):
+    """Sequences ``[b0, b1)`` of the GLOBAL batch of ``cfg`` (generated once with the global seed
+    and sliced contiguously by rank): tokens / labels come from one global CPU generator and are sliced; X and dH0 are
+    drawn on ``device`` with one generator seed PER SEQUENCE (seed + 1000 + b), so every world size sees the same
+    global batch without any rank materialising all of it.  Returns ``(tokens, labels)`` on the CPU (int64) and
+    ``(X, dH0)`` on the device (bf16)."""
+    g = torch.Generator().manual_seed(seed + 1)
+    tokens, labels = make_tokens_labels(cfg, g)
+    gd = torch.Generator(device=device)
+    X = torch.empty(b1 - b0, cfg.seq, hidden, dtype=torch.bfloat16, device=device)
+    dH0 = torch.empty_like(X)
+    for b in range(b0, b1):
+        gd.manual_seed(seed + 1000 + b)
+        X[b - b0] = torch.randn(cfg.seq, hidden, generator=gd, device=device).to(torch.bfloat16)
+        dH0[b - b0] = (torch.randn(cfg.seq, hidden, generator=gd, device=device) * 1e-3).to(torch.bfloat16)
+    return tokens[b0:b1].contiguous(), labels[b0:b1].contiguous(), X, dH0

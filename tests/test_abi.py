@@ -58,12 +58,21 @@ def test_data_parallel_and_next_row_entry_points_validate_on_the_host():
     lib = _lib.load()
     nbytes, off = c_size_t(0), c_size_t(0)
     V, D = 133258, 2048
-    assert lib.ssi_b200_dp_buffer_bytes(V, D, 8, byref(nbytes), byref(off)) == 0
+    R = 16384  # token rows per rank of c5 at 8 GPUs
+    assert lib.ssi_b200_dp_buffer_bytes(V, D, 8, R, byref(nbytes), byref(off)) == 0
     slice_rows = -(-V // 8)
-    assert off.value == 4096 and nbytes.value == 4096 + V * D * 4 + slice_rows * D * 2
-    assert lib.ssi_b200_dp_buffer_bytes(V, D, 9, byref(nbytes), byref(off)) < 0  # one NVSwitch node: <= 8 ranks
+    up = lambda x: -(-x // 256) * 256  # noqa: E731
+    # [ctrl][dW_acc fp32][stage bf16 slice][slot u64 V][ids i32 R][rows bf16 R x D]
+    assert off.value == 4096 and nbytes.value == (4096 + up(V * D * 4) + up(slice_rows * D * 2) + up(V * 8)
+                                                  + up(R * 4) + up(R * D * 2))
+    assert lib.ssi_b200_dp_buffer_bytes(V, D, 9, R, byref(nbytes), byref(off)) < 0  # one NVSwitch node: <= 8 ranks
     assert b"world size" in lib.ssi_b200_last_error()
-    assert lib.ssi_b200_dp_exchange(None, 0, 2, V, D, 1, None, None, None, 0, None) < 0
+    assert lib.ssi_b200_dp_exchange(None, 0, 2, V, D, R, 1, None, None, None, 0, None, None) < 0
+    assert lib.ssi_b200_dp_counts(None, 0, 2, 1, None, None, None, None, None) < 0
+    assert lib.ssi_b200_dp_embedding_exchange(None, 8, V, D, None, 0, None, 0, 2, R, 1, None, None, None) < 0
+    assert lib.ssi_b200_grad_add(None, None, 8, None) < 0 and lib.ssi_b200_count_valid(None, 8, -100, None, None) < 0
+    assert lib.ssi_b200_lmhead_ce_fwd_grad_ex(None, None, None, None, None, 1, 1, 64, -100, None, None, None, None,
+                                              None, None, 0, None, None) < 0
     b = c_size_t(0)
     assert lib.ssi_b200_rmsnorm_bwd_workspace_bytes(32768, D, byref(b)) == 0 and b.value >= 148 * 2 * 8 * D * 4
     assert lib.ssi_b200_rmsnorm_fwd(None, None, 1e-6, 8, 64, None, None, None) < 0

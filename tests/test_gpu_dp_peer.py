@@ -1,6 +1,8 @@
-"""GPU tests of the data-parallel exchange of the tied gradient over peer memory (csrc/dp_exchange.cuh,
-ssi_b200.peer, PathStep(exchange="peer")): the fp32 embedding scatter-add, the reduce + gather kernels and the
-side-stream overlap, against the fp32 oracle on the CONCATENATED batch (tolerances as in test_gpu_parity.py).
+"""GPU tests of the data-parallel exchange of the tied gradient (csrc/dp_exchange.cuh, ssi_b200.peer,
+ssi_b200.sync) in the CAUSAL order of a training step -- token counts through the peers' ctrl blocks, the LM-head part
+behind the last dX contraction, the embedding part (compact rows) after the embedding backward -- through PathStep and
+through install() on a tiny model whose embedding gradient arrives by autograd, against the fp32 oracle on the
+CONCATENATED batch (tolerances as in test_gpu_parity.py).
 
 world = 1 runs in-process on any GPU box (the kernels' own-rank path); world = 2 spawns one process per GPU over
 NCCL and needs two GPUs (skipped otherwise; `gpurun --gpus 2`)."""
@@ -81,6 +83,41 @@ def test_peer_exchange_world1_matches_oracle_and_plain_path():
         dist.destroy_process_group()
 
 
+class TinyDecoder(torch.nn.Module):
+    """The reference model's shape of interface (tok_embeddings / norm-free / output, chunked output list,
+    tt/torchtune/modules/transformer.py:499-502,628) with one mixing parameter, so that the embedding gradient reaches
+    ``tok_embeddings`` through autograd AFTER the loss backward -- the causal order of a real step."""
+
+    def __init__(self, V, D):
+        super().__init__()
+        self.tok_embeddings = torch.nn.Embedding(V, D, dtype=torch.bfloat16)
+        self.output = None
+        self.num_output_chunks = 0
+        self.mix = torch.nn.Parameter(torch.tensor(0.5, dtype=torch.bfloat16))
+
+    def set_num_output_chunks(self, n):
+        self.num_output_chunks = n
+
+    def forward(self, tokens, extra):
+        h = self.tok_embeddings(tokens) * self.mix + extra
+        return [self.output(c) for c in h.chunk(self.num_output_chunks, dim=1)]
+
+
+def _oracle_tiny(inp, mbs):
+    """fp32 CPU oracle of TinyDecoder on the CONCATENATED batch, micro-batches accumulated."""
+    Wf = inp["W"].float().clone().requires_grad_(True)
+    mix = torch.tensor(0.5, requires_grad=True)
+    total = 0.0
+    for sl in mbs:
+        tok, lab, X = inp["tokens"][sl], inp["labels"][sl], inp["X"][sl]
+        n_iter = oracle.count_valid(lab)
+        h = torch.nn.functional.embedding(tok, Wf) * mix + X.float()
+        loss = oracle.lmhead_ce(h, Wf, oracle.shift_labels(lab)) * n_iter
+        loss.backward()
+        total += loss.item()
+    return total, Wf.grad, mix.grad
+
+
 def _worker(rank, world, port, out):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
@@ -88,38 +125,91 @@ def _worker(rank, world, port, out):
     dev = torch.device("cuda", rank)
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     try:
+        import ssi_b200
         from ssi_b200 import dist as ddist
+        from ssi_b200 import ops
         from ssi_b200.step import PathStep
 
+        pg = dist.group.WORLD
+        # ---------------- (1) PathStep: the bench's flow, both exchanges, against the oracle on the whole batch
         inp = _inputs(B=6, S=200, V=9001, D=512, cfg="c3", seed=9)
         b0, b1 = ddist.shard_rows(inp["tokens"].size(0), rank, world)
         args = [inp[k][b0:b1].contiguous().to(dev) for k in ("tokens", "labels", "X", "dH0")]
         res = {}
         for ex in ("peer", "nccl"):
-            step = PathStep(inp["W"].to(dev), process_group=dist.group.WORLD, exchange=ex)
+            step = PathStep(inp["W"].to(dev), process_group=pg, exchange=ex)
             for _ in range(2):
                 step.zero_grad()
                 loss_batch, dX, counts = step(*args)
             torch.cuda.synchronize()
-            total = ddist.allreduce_loss(loss_batch, dist.group.WORLD)
+            total = ddist.allreduce_loss(loss_batch, pg)
             res[ex] = (total.item(), dX.cpu(), step.weight.grad.cpu())
+            # a second micro-batch WITHOUT zero_grad: only the new contribution may be summed over ranks
+            step(*args)
+            torch.cuda.synchronize()
+            res[ex + "_acc"] = step.weight.grad.cpu()
+            # eval after a training step: this rank's own mean, not a stale global count
+            ev = step.forward_only(args[2], args[1])
+            res[ex + "_eval"] = ev.item()
             step.close()
         # every rank must hold the bit-identical summed gradient
-        g = res["peer"][2].cuda().view(torch.int16).to(torch.int32)
-        lo, hi = g.clone(), g.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
-        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        same = bool((lo == hi).all().item())
+        same = {}
+        for ex in ("peer", "nccl"):
+            g = res[ex][2].cuda().view(torch.int16).to(torch.int32)
+            lo, hi = g.clone(), g.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            same[ex] = bool((lo == hi).all().item())
+
+        # ---------------- (2) through install() on a tiny model, two micro-batches, multiplier NOT announced
+        V, D, B, S = 3001, 256, 4, 96
+        tin = _inputs(B=2 * B, S=S, V=V, D=D, cfg="c2", seed=13)
+        model = TinyDecoder(V, D).to(dev)
+        with torch.no_grad():
+            model.tok_embeddings.weight.copy_(tin["W"])
+        tiny = {}
+        for ex in ("peer", "nccl"):
+            model.zero_grad(set_to_none=True)
+            loss_fn = ssi_b200.install(model, process_group=pg, exchange=ex, max_tokens_per_rank=B * S)
+            tot = 0.0
+            for mb in range(2):  # micro-batch mb = global rows [mb*B, (mb+1)*B), split over the ranks
+                r0, r1 = ddist.shard_rows(B, rank, world)
+                sl = slice(mb * B + r0, mb * B + r1)
+                tok, lab, X = (tin[k][sl].to(dev) for k in ("tokens", "labels", "X"))
+                shifted, cnt = ops.label_shift_count(lab.contiguous())
+                loss = loss_fn(model(tok, X), shifted)  # local loss sum / GLOBAL valid count
+                n_iter = ddist.global_counts(cnt, pg)[0]  # the trainer's own all-reduced multiplier
+                lb = loss * n_iter
+                lb.backward()
+                tot += ddist.allreduce_loss(lb, pg).item()
+            torch.cuda.synchronize()
+            mixg = model.mix.grad.float().clone()
+            dist.all_reduce(mixg)  # an ordinary parameter: the trainer's (DDP's) job, summed here by hand
+            tiny[ex] = (tot, model.tok_embeddings.weight.grad.cpu().clone(), mixg.item())
+            loss_fn.sync.check()
+            loss_fn.sync.close()
+
         if rank == 0:
             ref_loss, n_iter, ref_dH, ref_dW = oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"],
                                                                       inp["dH0"], inp["W"])
             want = ref_loss.item() * n_iter
-            out["same_on_all_ranks"] = same
-            out["loss_ok"] = abs(res["peer"][0] - want) <= LOSS_RTOL * abs(want)
+            out["same_on_all_ranks"] = same["peer"] and same["nccl"]
+            out["loss_ok"] = (abs(res["peer"][0] - want) <= LOSS_RTOL * abs(want)
+                              and abs(res["nccl"][0] - want) <= LOSS_RTOL * abs(want))
+            lab_loc = inp["labels"][b0:b1]
+            ev_want = oracle.lmhead_ce(inp["X"][b0:b1].float(), inp["W"].float(), oracle.shift_labels(lab_loc)).item()
+            out["eval_ok"] = all(abs(res[k + "_eval"] - ev_want) <= LOSS_RTOL * abs(ev_want) for k in ("peer", "nccl"))
             try:
                 assert_grad_close(res["peer"][2], ref_dW, "dW peer")
                 assert_grad_close(res["nccl"][2], ref_dW, "dW nccl")
+                assert_grad_close(res["peer_acc"], 2 * ref_dW, "dW peer, two micro-batches accumulated")
+                assert_grad_close(res["nccl_acc"], 2 * ref_dW, "dW nccl, two micro-batches accumulated")
                 assert_grad_close(res["peer"][1].reshape(ref_dH[b0:b1].shape), ref_dH[b0:b1], "dH")
+                t_loss, t_dW, t_mix = _oracle_tiny(tin, [slice(0, B), slice(B, 2 * B)])
+                for ex in ("peer", "nccl"):
+                    assert abs(tiny[ex][0] - t_loss) <= 2e-3 * abs(t_loss), (ex, tiny[ex][0], t_loss)
+                    assert_grad_close(tiny[ex][1], t_dW, f"tied dW through install(), {ex}")
+                    assert abs(tiny[ex][2] - t_mix.item()) <= 2e-2 * abs(t_mix.item()) + 1e-3, (ex, tiny[ex][2])
                 out["grads_ok"] = True
             except AssertionError as e:  # pragma: no cover
                 out["grads_ok"] = False
@@ -135,4 +225,5 @@ def test_peer_exchange_world2_matches_single_process_oracle():
     mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
     assert out.get("same_on_all_ranks") is True
     assert out.get("loss_ok") is True
+    assert out.get("eval_ok") is True
     assert out.get("grads_ok") is True, out.get("why")
