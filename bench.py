@@ -428,7 +428,7 @@ def run_ours(args):
         per_rank_ms = [None] * world
         dist.all_gather_object(per_rank_ms, round(mine, 3))
     if path.sync is not None:
-        path.sync.check()  # raises if the exchange ran with a multiplier that backward did not confirm / timed out
+        path.sync.check(confirm_multiplier=True)  # raises if the exchange ran with a multiplier that backward did not confirm / timed out
     exchange = path.exchange
     path.close()
     if rank != 0:

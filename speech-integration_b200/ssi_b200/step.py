@@ -108,5 +108,5 @@ class PathStep:
     def close(self) -> None:
         """Release the peer exchange buffers (collective: every rank must call it)."""
         if self.sync is not None:
-            self.sync.check()
+            self.sync.check(confirm_multiplier=True)
             self.sync.close()

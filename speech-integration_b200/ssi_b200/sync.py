@@ -178,12 +178,13 @@ class TiedGradSync:
             ops.grad_add(self.weight.grad, target)
         self._target = None
 
-    def check(self) -> None:
-        """Raise if an exchange timed out or ran with a multiplier that backward did not confirm (synchronises on
-        the mismatch flag only when one was recorded)."""
+    def check(self, confirm_multiplier: bool = False) -> None:
+        """Raise if an exchange timed out (a pinned host word: no device synchronisation).  ``confirm_multiplier``:
+        also raise if the dense exchange ran with a multiplier that backward did not confirm (reads a device flag:
+        synchronises; meant for the end of a run or an accumulation boundary)."""
         if self.peer is not None:
             self.peer.check()
-        m = self.grad_hint_mismatch
+        m = self.grad_hint_mismatch if confirm_multiplier else None
         if m is not None and bool(m.any().item()):
             raise RuntimeError("ssi_b200.sync: the dense exchange ran with the announced loss multiplier, but "
                                "backward received a different upstream gradient; announce the right one "

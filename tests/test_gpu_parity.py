@@ -15,12 +15,14 @@ LOSS_RTOL = 1e-3
 FRO_TOL = 4e-3
 
 
-def assert_grad_close(got: torch.Tensor, ref: torch.Tensor, name: str):
+def assert_grad_close(got: torch.Tensor, ref: torch.Tensor, name: str, roundings: float = 1.0):
+    """``roundings`` > 1 widens both bounds for results that were ACCUMULATED in bf16 that many times (the NCCL
+    baseline sums micro-batches and ranks in bf16, as the reference's autograd sums its chunks in bf16)."""
     got = got.float().cpu()
     ref = ref.float().cpu()
     fro = (got - ref).norm().item() / (ref.norm().item() + 1e-30)
-    assert fro <= FRO_TOL, f"{name}: relative Frobenius error {fro:.3e} > {FRO_TOL}"
-    bound = ref.abs() * 2.0 ** -7 + ref.abs().max() * 2.0 ** -8
+    assert fro <= FRO_TOL * roundings, f"{name}: relative Frobenius error {fro:.3e} > {FRO_TOL * roundings}"
+    bound = (ref.abs() * 2.0 ** -7 + ref.abs().max() * 2.0 ** -8) * roundings
     bad = ((got - ref).abs() > bound).sum().item()
     assert bad == 0, f"{name}: {bad} elements outside bf16 tolerance (fro {fro:.3e})"
 
