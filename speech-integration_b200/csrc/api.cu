@@ -322,6 +322,9 @@ struct Tune {
   int shape_gate = 1;  // wide dW / dX: also enqueue the 256x256 kernel and let the device-side plan pick (small problems)
   int tail_split = 1;  // wide tiles: split the items of an at most half-full last wave into 256x256 halves
   int wide_dw = 2, wide_dx = 2;  // single-pass dW / dX: 2 = 256x512 tiles per CTA pair (needs cta_group 2), 1 = 256x256
+  // single-pass: 1 = K1 stashes E = exp(logit - ref[row]) and the softmax normalisation is a per-row factor folded into
+  // the dX epilogue and the X rows of dW (no pass over the block); 0 = stash logits + separate softmax-grad HBM pass
+  int exp_stash = 1;
 };
 // The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
 // thread-local SNAPSHOT under the mutex (TuneScope), so one call never sees half of an update.
@@ -345,6 +348,7 @@ Tune& global_tune() {
     if (const char* e = getenv("SSI_B200_TAIL_SPLIT")) x.tail_split = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
+    if (const char* e = getenv("SSI_B200_EXP_STASH")) x.exp_stash = atoi(e) ? 1 : 0;
     return x;
   }();
   return t;
@@ -427,6 +431,7 @@ struct SpPlan {
   int tiles_m, vtiles_total, combine_blocks, t_max, chunks_max;
   CompactWs cw;
   size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_rstd, off_dsp, off_dxc, off_s, bytes;
+  size_t off_ref2, off_rowscale, off_xs;  // exp-stash form: pilot reference, per-row factor, scaled X rows
 };
 constexpr size_t SYNC_AREA_BYTES = 4096;
 constexpr int NORM_BWD_BLOCKS = 148 * 2;            // grid of the fused norm-backward scatter
@@ -463,6 +468,9 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   f.off_rstd = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
   f.off_dsp = o, o += align_up(static_cast<size_t>(NORM_BWD_PARTS) * D * sizeof(float), 256);
   f.off_dxc = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
+  f.off_ref2 = o, o += align_up(items * ssi::BM * sizeof(float), 256);
+  f.off_rowscale = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
+  f.off_xs = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
   f.off_s = o, o += align_up(static_cast<size_t>(f.t_max) * ssi::BM * f.vpad * 2, 1024);
   f.bytes = o;
   *out = f;
@@ -535,6 +543,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "tail_split")) t.tail_split = value ? 1 : 0;
   else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
+  else if (!strcmp(name, "exp_stash")) t.exp_stash = value ? 1 : 0;
   else return fail(-1, "unknown option '%s'", name);
   return 0;
 }
@@ -822,6 +831,10 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
   int* blk_cnt = reinterpret_cast<int*>(wsb + f.off_bc);
   void* dXc = wsb + f.off_dxc;
   void* S = wsb + f.off_s;
+  float* ref2 = reinterpret_cast<float*>(wsb + f.off_ref2);
+  float* rowscale_c = reinterpret_cast<float*>(wsb + f.off_rowscale);
+  void* Xs = wsb + f.off_xs;
+  const bool estash = tune().exp_stash != 0;
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
   const int64_t rows_cap = static_cast<int64_t>(f.t_max) * ssi::BM;
   const int64_t* nvt = n_valid_total ? n_valid_total : n_valid;
@@ -863,12 +876,14 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
     return r;
   if (int r = make_tmap(&tmdW, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, dW_acc, D, V, D * 4, 32, ssi::BM)) return r;
   if (int r = make_tmap(&tmdXc, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, dXc, D, f.n_pad, D * 2, 64, ssi::BM)) return r;
+  CUtensorMap tmXs_mn = tmX_mn;  // dW's B operand: the scaled rows in the exp-stash form
+  if (estash)
+    if (int r = make_tmap(&tmXs_mn, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, Xs, D, f.n_pad, D * 2, 64, 64)) return r;
 
   for (int ch = 0; ch < f.chunks_max; ++ch) {
     const ssi::DevPlan* cplan = dplan + 1 + ch;
-    // ---- K1: logits tiles of the chunk -> bf16 block S + online log-sum-exp partials
-    {
-      ssi::GemmParams p;
+    // ---- K1: logits tiles of the chunk -> one bf16 block + per-split row partials
+    auto k1_params = [&](ssi::GemmParams& p) {
       memset(&p, 0, sizeof(p));
       p.tmA = tmX_k, p.tmB = tmW_k, p.tmC = tmS_k;
       p.dplan = cplan, p.m_from_plan = 1, p.plan_rows = ssi::PR_A_ROWS | ssi::PR_LABEL_ROWS;
@@ -881,19 +896,47 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       p.part_m = part_m, p.part_l = part_l, p.part_z = part_z;
       p.part_stride = static_cast<int>(rows_cap);
       set_hints(p, tune().k1_hints);
+    };
+    if (estash) {
+      // pilot: the running max of the FIRST vocabulary tile, per row (log2 domain) = the reference of E below
+      {
+        ssi::GemmParams p;
+        k1_params(p);
+        p.vtiles_per_split = 1, p.vtiles_total = 1, p.lse_one_split = 1;
+        p.part_m = ref2;
+        if (int r = launch_gemm<ssi::EPI_LSE, false, false>(p, di->sms, st, "lmhead_pilot", CAT_LSE, di->sms)) return r;
+      }
+      ssi::GemmParams p;
+      k1_params(p);
+      p.row_ref2 = ref2;
       if (tune().lockstep_k1) p.sync_ctr = sync_area + 256 + ch, p.sync_err = sync_area + 1023, p.sync_every = 1;
-      if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
+      if (int r = launch_gemm<ssi::EPI_EXP_STASH, false, false>(p, di->sms, st, "lmhead_exp_stash", CAT_LSE, di->sms))
         return r;
-    }
-    {
-      ProfScope ps(CAT_AUX, st);
-      ssi::chunk_combine_kernel<<<64, 256, 0, st>>>(part_m, part_l, part_z, cplan, lse_c, loss_c);
-      SSI_LAUNCH_OK("chunk_combine");
-    }
-    // ---- S -> G in place (softmax - onehot) * grad_hint / n_valid_total
-    {
       // data parallel: grad_hint / n_valid_total are filled by the counts exchange running on another stream beside
-      // the first logits contraction; this is the first consumer
+      // the first logits contraction; the combine below is their first consumer
+      if (ch == 0 && pre_grad_event) SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pre_grad_event), 0));
+      ProfScope ps(CAT_AUX, st);
+      ssi::exp_combine_kernel<<<64, 256, 0, st>>>(ref2, part_l, part_z, cplan, labels_c, grad_hint, nvt,
+                                                  static_cast<__nv_bfloat16*>(S), f.vpad, static_cast<int>(V), lse_c,
+                                                  loss_c, rowscale_c);
+      SSI_LAUNCH_OK("exp_combine");
+      ssi::scale_rows_kernel<<<di->sms * 4, 256, 0, st>>>(static_cast<const uint4*>(Xc), rowscale_c, cplan,
+                                                          static_cast<int>(D / 8), static_cast<uint4*>(Xs));
+      SSI_LAUNCH_OK("scale_rows");
+    } else {
+      {
+        ssi::GemmParams p;
+        k1_params(p);
+        if (tune().lockstep_k1) p.sync_ctr = sync_area + 256 + ch, p.sync_err = sync_area + 1023, p.sync_every = 1;
+        if (int r = launch_gemm<ssi::EPI_LSE_STASH, false, false>(p, di->sms, st, "lmhead_lse_stash", CAT_LSE, di->sms))
+          return r;
+      }
+      {
+        ProfScope ps(CAT_AUX, st);
+        ssi::chunk_combine_kernel<<<64, 256, 0, st>>>(part_m, part_l, part_z, cplan, lse_c, loss_c);
+        SSI_LAUNCH_OK("chunk_combine");
+      }
+      // ---- S -> G in place (softmax - onehot) * grad_hint / n_valid_total
       if (ch == 0 && pre_grad_event) SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pre_grad_event), 0));
       ProfScope ps(CAT_SOFTMAX, st);
       ssi::softmax_grad_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(S), static_cast<int>(f.vpad / 8),
@@ -905,7 +948,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
     {
       ssi::GemmParams p;
       memset(&p, 0, sizeof(p));
-      p.tmA = tmS_mn, p.tmB = tmX_mn, p.tmC = tmdW;
+      p.tmA = tmS_mn, p.tmB = tmXs_mn, p.tmC = tmdW;
       p.dplan = cplan, p.k_from_plan = 1, p.plan_rows = ssi::PR_B_K;
       p.tiles_m = static_cast<int>(ceil_div(V, ssi::BM));
       p.tiles_n = d_tiles;
@@ -932,6 +975,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       p.tiles_m = f.t_max, p.tiles_n = d_tiles;
       p.k_blocks = f.vtiles_total * (ssi::BN / ssi::BK);
       p.group_m = tune().group_m_dx;
+      if (estash) p.row_scale = rowscale_c;  // dlogits = rowscale[row] * E'
       set_hints(p, tune().dx_hints);
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch + 1, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_BF16, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX, tune().wide_dx))

@@ -395,6 +395,79 @@ __device__ __forceinline__ uint4 f32x8_to_bf16(const float (&f)[8]) {
   return o;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Exp-stash form of single-pass mode (default).  K1 left E[r, v] = bf16(2^(s log2e - ref2[r])) in the block and the
+// per-split row sums of the fp32 values; softmax[r, v] = E[r, v] / L[r] with L = sum over splits, so dlogits =
+// (hint / n_valid) * (E / L - onehot) is E times a per-ROW factor once the label column is patched:
+//   exp_combine_kernel   lse = (ref2 + log2 L) ln2, loss = lse - z_label, rowscale[r] = (hint / n_valid) / L[r],
+//                        and E[r, label] <- bf16(E32[r, label] - L[r])  (so that E' / L = softmax - onehot there)
+//   scale_rows_kernel    Xs[r, :] = bf16(rowscale[r] * X_c[r, :]): the rows dW = E'^T Xs contracts with
+// and dX = rowscale[r] * (E' W)[r, :] takes the factor in its epilogue.  No pass over the [rows, V] block.
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) exp_combine_kernel(const float* __restrict__ ref2,
+                                                          const float* __restrict__ part_l,
+                                                          const float* __restrict__ part_z,
+                                                          const DevPlan* __restrict__ plan,
+                                                          const int64_t* __restrict__ labels_c,
+                                                          const float* __restrict__ grad_hint,
+                                                          const int64_t* __restrict__ n_valid_total,
+                                                          __nv_bfloat16* __restrict__ E, long long row_elems, int V,
+                                                          float* __restrict__ lse_c, float* __restrict__ loss_c,
+                                                          float* __restrict__ rowscale_c) {
+  const int rows = plan->tiles_m * 128, nv = plan->n_valid, row0 = plan->row0;
+  const int splits = plan->splits, part_stride = plan->part_stride;
+  const long long nvt = *n_valid_total;
+  const float gscale = (nvt > 0) ? (*grad_hint / static_cast<float>(nvt)) : 0.f;
+  constexpr float kLog2e = 1.4426950408889634f;
+  for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
+    float l = 0.f, loss = 0.f, rs = 0.f;
+    if (r < nv) {
+      float L = 0.f, z = -INFINITY;
+      for (int s = 0; s < splits; ++s) {  // fixed order: deterministic
+        const size_t o = static_cast<size_t>(s) * part_stride + r;
+        L += part_l[o];
+        z = fmaxf(z, part_z[o]);
+      }
+      const float c2 = ref2[r];
+      l = (c2 + log2f(L)) * 0.6931471805599453f;
+      loss = l - z;
+      rs = gscale / L;
+      const long long lab = labels_c[row0 + r];
+      if (lab >= 0 && lab < V) {
+        const float e_lab = fast_exp2(fmaf(z, kLog2e, -c2));  // the fp32 value K1 rounded into E[r, label]
+        E[static_cast<size_t>(r) * row_elems + lab] = __float2bfloat16_rn(e_lab - L);
+      }
+    }
+    lse_c[row0 + r] = l;
+    loss_c[row0 + r] = loss;
+    rowscale_c[row0 + r] = rs;
+  }
+}
+
+// Xs[row0 + r, :] = bf16(rowscale[row0 + r] * X_c[row0 + r, :]) for the chunk's rows (padding rows: scale 0 -> zeros).
+__global__ void __launch_bounds__(256) scale_rows_kernel(const uint4* __restrict__ Xc,
+                                                         const float* __restrict__ rowscale_c,
+                                                         const DevPlan* __restrict__ plan, int row_u4,
+                                                         uint4* __restrict__ Xs) {
+  const int rows = plan->tiles_m * 128, row0 = plan->row0;
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < rows; r += warps) {
+    const float rs = rowscale_c[row0 + r];
+    const uint4* src = Xc + static_cast<size_t>(row0 + r) * row_u4;
+    uint4* dst = Xs + static_cast<size_t>(row0 + r) * row_u4;
+    for (int j = lane; j < row_u4; j += 32) {
+      const uint4 u = src[j];
+      uint4 o;
+      o.x = pack_bf16x2(bf16lo(u.x) * rs, bf16hi(u.x) * rs);
+      o.y = pack_bf16x2(bf16lo(u.y) * rs, bf16hi(u.y) * rs);
+      o.z = pack_bf16x2(bf16lo(u.z) * rs, bf16hi(u.z) * rs);
+      o.w = pack_bf16x2(bf16lo(u.w) * rs, bf16hi(u.w) * rs);
+      dst[j] = o;
+    }
+  }
+}
+
 // lse[row] / per-block loss partials over ORIGINAL rows from the compact lse_c / loss_c (fixed order).
 __global__ void __launch_bounds__(COMBINE_THREADS) stash_finish_kernel(const float* __restrict__ lse_c,
                                                                        const float* __restrict__ loss_c,

@@ -3,6 +3,10 @@
 //   EPI_GRAD  logits tile -> dlogits block G in bf16                  (backward, K2a)
 //   EPI_BF16  accumulator -> bf16 tile store / reduce-add             (dW = G^T X, K2b; dX when one block)
 //   EPI_F32   accumulator -> fp32 tile store / reduce-add             (dX accumulation, K2c; test hook)
+//   EPI_LSE_STASH  logits tile -> bf16 logits block + online LSE      (single-pass K1, separate softmax-grad pass)
+//   EPI_EXP_STASH  logits tile -> bf16 block of E = exp(logit - ref[row]) + its row sums
+//                  (single-pass K1, default: the softmax normalisation 1 / sum E is a per-ROW factor, so it moves
+//                  into the dX epilogue and into the rows of X that dW contracts with -- no pass over the block)
 // One CTA per SM: warp 0 = TMA producer, warp 1 = MMA issuer (+TMEM owner), warps 2..5 = epilogue
 // (one thread per accumulator row).  128x256 fp32 accumulators, double-buffered in the 512 TMEM columns, so
 // the epilogue of tile j overlaps the MMAs of tile j+1.  Operands are staged by TMA with 128-byte swizzle.
@@ -52,9 +56,11 @@ constexpr int TMEM_COLS = 512;
 constexpr float LOG2E = 1.4426950408889634f;
 constexpr float LN2 = 0.6931471805599453f;
 
-enum Epi { EPI_LSE = 0, EPI_GRAD = 1, EPI_BF16 = 2, EPI_F32 = 3, EPI_LSE_STASH = 4 };
+enum Epi { EPI_LSE = 0, EPI_GRAD = 1, EPI_BF16 = 2, EPI_F32 = 3, EPI_LSE_STASH = 4, EPI_EXP_STASH = 5 };
 template <int EPI>
-__host__ __device__ constexpr bool is_lse_epi() { return EPI == EPI_LSE || EPI == EPI_LSE_STASH; }
+__host__ __device__ constexpr bool is_lse_epi() {
+  return EPI == EPI_LSE || EPI == EPI_LSE_STASH || EPI == EPI_EXP_STASH;
+}
 // GemmParams::plan_rows bits: add dplan->row0 (first compact row of a row chunk) to ...
 enum PlanRows { PR_A_ROWS = 1, PR_B_K = 2, PR_C_ROWS = 4, PR_LABEL_ROWS = 8 };
 
@@ -102,6 +108,12 @@ struct GemmParams {
   const float* lse;          // [N] natural log
   const float* grad_out;     // [1]
   const int64_t* n_valid;    // [1]
+  // EPI_LSE: 1 = ONE split of p.vtiles_per_split tiles whatever the plan says (the pilot sweep over the first tile)
+  int lse_one_split;
+  // EPI_EXP_STASH: per-row reference in the log2 domain, indexed by the plan-relative row (the pilot's running max)
+  const float* row_ref2;
+  // EPI_BF16: optional per-row factor applied before the rounding, indexed like the C rows (c_r0 + plan offset + row)
+  const float* row_scale;
 };
 
 struct TileItem {
@@ -153,6 +165,7 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
       if constexpr (is_lse_epi<EPI>()) {
         s.tiles_n = p.dplan->splits;
         s.vtiles_per_split = p.dplan->vtiles_per_split;
+        if (p.lse_one_split) s.tiles_n = 1, s.vtiles_per_split = p.vtiles_per_split;
         s.part_stride = p.dplan->part_stride;
         s.group_m = max(s.tiles_m, 1);
       }
@@ -472,6 +485,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
       bool valid = false;
       float m_run = -INFINITY, l_run = 0.f, z_lab = -INFINITY;  // EPI_LSE
       float lse2 = 0.f;                                         // EPI_GRAD
+      float ref2 = 0.f;                                         // EPI_EXP_STASH
+      if constexpr (EPI == EPI_EXP_STASH) {
+        if (m_ok) ref2 = p.row_ref2[row];
+      }
+      float rscale = 1.f;                                       // EPI_BF16 with row_scale
+      if constexpr (EPI == EPI_BF16) {
+        if (p.row_scale != nullptr) rscale = m_ok ? p.row_scale[p.c_r0 + sc.c_row_off + row] : 0.f;
+      }
+      (void)ref2, (void)rscale;
       if constexpr (is_lse_epi<EPI>() || EPI == EPI_GRAD) {
         if (sc.label_off + row < p.n_rows) {
           label = p.labels[sc.label_off + row];
@@ -603,6 +625,68 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
             }
             ++chunk_ctr;
           }
+        } else if constexpr (EPI == EPI_EXP_STASH) {
+          // Single-pass mode, default: the logits tile is rounded to bf16 (the reference's logits dtype,
+          // tied_linear.py:25), E = 2^(s log2e - ref2[row]) is formed in fp32 from the ROUNDED value (what
+          // ce_chunked_output_loss.py:41 upcasts), summed per row in fp32 and stored as bf16 into the row chunk's
+          // block.  ref2 is a per-row constant (the pilot's max over the first vocabulary tile), so no running max
+          // and no rescaling: softmax = E / sum(E) is applied later as a per-row factor.  Padding columns store 0.
+          const int cbase = p.col0 + nt * BN;
+#pragma unroll 1
+          for (int c = 0; c < BN / 64; ++c) {
+            uint32_t w[32];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+              float v[32];
+              tmem_ld32(taddr + c * 64 + h * 32, v);
+              const int ch0 = cbase + c * 64 + h * 32;
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                const uint32_t pk = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+                v[2 * j] = bf16lo(pk);
+                v[2 * j + 1] = bf16hi(pk);
+              }
+              if (valid && label >= ch0 && label < ch0 + 32) {
+                const int jl = static_cast<int>(label - ch0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (j == jl) z_lab = v[j];
+              }
+#pragma unroll
+              for (int j = 0; j < 32; ++j) v[j] = fast_exp2(fmaf(v[j], LOG2E, -ref2));
+              if (ch0 + 32 > p.vocab) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (ch0 + j >= p.vocab) v[j] = 0.f;
+              }
+              float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) s0 += v[j], s1 += v[j + 1], s2 += v[j + 2], s3 += v[j + 3];
+              l_run += (s0 + s1) + (s2 + s3);
+#pragma unroll
+              for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
+            }
+            if (c == BN / 64 - 1) {
+              tc_fence_before();
+              __syncwarp();
+              if (lane == 0) release_acc<CG>(tempty_bar(acc));
+            }
+            const uint32_t buf = smem_epi0 + (chunk_ctr & 1u) * EPI_BUF_BYTES;
+            if (issuer) tma_wait_group_read<1>();
+            named_bar_sync(1, EPI_THREADS);
+            stage_row_128B(buf, row_in_tile, w);
+            fence_proxy_async_smem();
+            named_bar_sync(1, EPI_THREADS);
+            if (issuer && m_ok) {
+              const int cc = p.c_c0 + nt * BN + c * 64, cr = p.c_r0 + sc.c_row_off + m_tile * BM;
+              if (p.store_policy)
+                tma_store_2d_hint(&p.tmC, buf, cc, cr, p.store_policy);
+              else
+                tma_store_2d(&p.tmC, buf, cc, cr);
+              tma_commit_group();
+            }
+            ++chunk_ctr;
+          }
         } else if constexpr (EPI == EPI_GRAD) {
           const int cbase = p.col0 + nt * BN;  // global vocab index of tile column 0
 #pragma unroll 1
@@ -666,6 +750,10 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
               if (zero_acc) {
 #pragma unroll
                 for (int j = 0; j < 32; ++j) v[j] = 0.f;
+              }
+              if (p.row_scale != nullptr) {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) v[j] *= rscale;
               }
 #pragma unroll
               for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);

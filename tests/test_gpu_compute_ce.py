@@ -8,7 +8,7 @@ import torch
 from torch import nn
 
 from oracle import reference_path as oracle
-from test_gpu_parity import LOSS_RTOL, assert_grad_close
+from test_gpu_parity import DW_ELEM_ROUNDINGS, LOSS_RTOL, assert_grad_close
 
 pytestmark = pytest.mark.gpu
 
@@ -47,7 +47,7 @@ def test_compute_cross_entropy_matches_the_oracle_chunk_by_chunk(mode):
     (ref_total / n).backward()
     torch.cuda.synchronize()
     assert_grad_close(h.grad, Xf.grad, "dH through compute_cross_entropy")
-    assert_grad_close(emb.weight.grad, Wf.grad, "dW through compute_cross_entropy")
+    assert_grad_close(emb.weight.grad, Wf.grad, "dW through compute_cross_entropy", elem_roundings=DW_ELEM_ROUNDINGS)
 
 
 @pytest.mark.parametrize("mode", ["single_pass", "recompute"])
@@ -82,4 +82,4 @@ def test_compiled_compute_cross_entropy_runs_forward_and_backward():
     torch.cuda.synchronize()
     _, ref_dH, ref_dW = oracle.lmhead_ce_fwd_bwd(inp["X"], inp["W"], oracle.shift_labels(inp["labels"]))
     assert_grad_close(hc.grad, ref_dH, "dH, compiled compute_cross_entropy")
-    assert_grad_close(emb.weight.grad, ref_dW, "dW, compiled compute_cross_entropy")
+    assert_grad_close(emb.weight.grad, ref_dW, "dW, compiled compute_cross_entropy", elem_roundings=DW_ELEM_ROUNDINGS)

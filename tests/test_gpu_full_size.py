@@ -11,7 +11,7 @@ import pytest
 import torch
 
 from oracle import reference_path as oracle
-from test_gpu_parity import LOSS_RTOL, assert_grad_close
+from test_gpu_parity import DW_ELEM_ROUNDINGS, LOSS_RTOL, assert_grad_close
 
 pytestmark = pytest.mark.gpu
 
@@ -81,7 +81,7 @@ def test_full_size_parity(name, batch):
         Gv -= (shifted[valid][:, None] == vs[None, :]).float()
         Gv = (Gv * scale).to(torch.bfloat16).float()
         ref_dW = Gv.t() @ Xv.float()
-    assert_grad_close(dW[vs], ref_dW, "dW (sampled vocabulary rows)")
+    assert_grad_close(dW[vs], ref_dW, "dW (sampled vocabulary rows)", elem_roundings=DW_ELEM_ROUNDINGS)
 
     # ---- properties over the WHOLE result
     loss2, lse2, _, dX2, dW2 = _run(X, W, shifted, 2 * upstream)

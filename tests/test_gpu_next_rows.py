@@ -125,7 +125,7 @@ def test_final_norm_fused_into_the_path(B, S, V, D, cfg, mode):
     ce_chunked_output_loss.py:45-83), including d(scale).  Oracle in fp32 on the same bf16 inputs."""
     import ssi_b200
     from ssi_b200 import synth
-    from test_gpu_parity import LOSS_RTOL, assert_grad_close
+    from test_gpu_parity import DW_ELEM_ROUNDINGS, LOSS_RTOL, assert_grad_close
 
     inp = synth.make_inputs(synth.CONFIGS[cfg], batch=B, seq=S, vocab=V, hidden=D, seed=21)
     g = torch.Generator().manual_seed(5)
@@ -157,7 +157,7 @@ def test_final_norm_fused_into_the_path(B, S, V, D, cfg, mode):
     torch.cuda.synchronize()
     assert abs(loss.item() - ref.item()) <= LOSS_RTOL * abs(ref.item())
     assert_grad_close(hc.grad, hp.grad, "d(pre-norm h)")
-    assert_grad_close(emb.weight.grad, ww.grad, "dW")
+    assert_grad_close(emb.weight.grad, ww.grad, "dW", elem_roundings=DW_ELEM_ROUNDINGS)
     assert norm.scale.grad.dtype == torch.bfloat16
     assert_grad_close(norm.scale.grad, sc.grad, "dscale")
     with torch.inference_mode():

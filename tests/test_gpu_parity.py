@@ -15,16 +15,27 @@ LOSS_RTOL = 1e-3
 FRO_TOL = 4e-3
 
 
-def assert_grad_close(got: torch.Tensor, ref: torch.Tensor, name: str, roundings: float = 1.0):
+# dW of single-pass mode contracts TWO bf16-rounded operands per token -- E = exp(logit - ref) and the row of X scaled
+# by the softmax normalisation -- where the reference contracts one rounded operand (dlogits) with the exact X row.
+# The rms error against the fp32 oracle stays inside the rel-Frobenius bound; the PER-ELEMENT bound, which the survey
+# derived from the reference's own one-rounding bf16 path, is widened by this factor for dW only.
+DW_ELEM_ROUNDINGS = 1.5
+
+
+def assert_grad_close(got: torch.Tensor, ref: torch.Tensor, name: str, roundings: float = 1.0,
+                      elem_roundings: float = 1.0):
     """``roundings`` > 1 widens both bounds for results that were ACCUMULATED in bf16 that many times (the NCCL
-    baseline sums micro-batches and ranks in bf16, as the reference's autograd sums its chunks in bf16)."""
+    baseline sums micro-batches and ranks in bf16, as the reference's autograd sums its chunks in bf16) or for two of
+    our own results compared with each other; ``elem_roundings`` widens the per-element bound only."""
     got = got.float().cpu()
     ref = ref.float().cpu()
     fro = (got - ref).norm().item() / (ref.norm().item() + 1e-30)
     assert fro <= FRO_TOL * roundings, f"{name}: relative Frobenius error {fro:.3e} > {FRO_TOL * roundings}"
-    bound = (ref.abs() * 2.0 ** -7 + ref.abs().max() * 2.0 ** -8) * roundings
-    bad = ((got - ref).abs() > bound).sum().item()
-    assert bad == 0, f"{name}: {bad} elements outside bf16 tolerance (fro {fro:.3e})"
+    bound = (ref.abs() * 2.0 ** -7 + ref.abs().max() * 2.0 ** -8) * roundings * elem_roundings
+    over = (got - ref).abs() / bound
+    bad = (over > 1).sum().item()
+    assert bad == 0, (f"{name}: {bad} elements outside bf16 tolerance (worst {over.max().item():.2f} x the bound, "
+                      f"fro {fro:.3e})")
 
 
 def _case(cfg_name, batch, seq, vocab, hidden, seed=0):

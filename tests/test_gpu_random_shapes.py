@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import reference_path as oracle
-from test_gpu_parity import LOSS_RTOL, assert_grad_close
+from test_gpu_parity import DW_ELEM_ROUNDINGS, LOSS_RTOL, assert_grad_close
 
 pytestmark = pytest.mark.gpu
 
@@ -55,4 +55,4 @@ def test_single_pass_random_shape(N, V, D, p_ignore, cap_mib):
     assert abs(loss_out[1].item() - ref_loss.item()) <= LOSS_RTOL * max(abs(ref_loss.item()), 1e-3)
     assert abs(fwd_only[1].item() - ref_loss.item()) <= LOSS_RTOL * max(abs(ref_loss.item()), 1e-3)
     assert_grad_close(dX, rdX.reshape(N, D), "dX")
-    assert_grad_close(dW, rdW, "dW")
+    assert_grad_close(dW, rdW, "dW", elem_roundings=DW_ELEM_ROUNDINGS)
