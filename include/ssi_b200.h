@@ -312,7 +312,8 @@ int ssi_b200_embedding_gather(const void* W, const int64_t* ids, int64_t N, int6
  * profile_end waits for those events and fills ms_by_class[8] / launches_by_class[8] (either may be NULL):
  *   0 = K1 logits + online-LSE (fwd), 1 = K2a dlogits recompute, 2 = K2b dW contraction, 3 = K2c dX contraction,
  *   4 = K3 embedding scatter (sort + segmented reduce, one entry per call), 5 = small helper kernels,
- *   6 = single-pass softmax-grad pass (S -> dlogits in place, HBM-bound), 7 = data-parallel exchange.
+ *   6 = single-pass work on dlogits outside the contractions (exp-stash form: the label-keyed onehot scatter into
+ *       dW_acc; classic form: the S -> dlogits pass, HBM-bound), 7 = data-parallel exchange.
  * This pair is the only part of the ABI that synchronises (profile_end) or allocates (events, lazily).
  */
 int ssi_b200_profile_begin(void);

@@ -53,7 +53,7 @@ struct ProfState {
 ProfState g_prof;
 const char* const kCatNames[CAT_COUNT] = {"ssi_b200:K1 logits+LSE", "ssi_b200:K2a dlogits", "ssi_b200:K2b dW",
                                           "ssi_b200:K2c dX",        "ssi_b200:K3 embedding scatter",
-                                          "ssi_b200:aux",           "ssi_b200:softmax-grad",
+                                          "ssi_b200:aux",           "ssi_b200:softmax-grad / onehot term",
                                           "ssi_b200:K4 exchange"};
 struct ProfScope {
   cudaStream_t st;
@@ -424,6 +424,38 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   return b;
 }
 
+struct ScatPlan {
+  int nwarps, passes, slabs;
+  size_t off_k0, off_v0, off_k1, off_v1, off_urank, off_nuniq, off_partial, off_info, bytes;
+};
+
+ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
+  ScatPlan s;
+  s.nwarps = static_cast<int>(ceil_div(N, 32));
+  s.slabs = static_cast<int>(ceil_div(D, ssi::SCAT_COLS));
+  int bits = 1;
+  while ((int64_t(1) << bits) <= V) ++bits;  // keys are in [0, V] (V = out-of-range sentinel)
+  s.passes = (bits + ssi::SORT_BITS - 1) / ssi::SORT_BITS;
+  size_t o = 0;
+  const size_t arr = align_up(static_cast<size_t>(N) * 4, 256);
+  s.off_k0 = o, o += arr;
+  s.off_v0 = o, o += arr;
+  s.off_k1 = o, o += arr;
+  s.off_v1 = o, o += arr;
+  s.off_urank = o, o += arr;
+  s.off_nuniq = o, o += 256;
+  s.off_partial = o, o += align_up(static_cast<size_t>(s.nwarps) * 2 * D * sizeof(float), 256);
+  s.off_info = o, o += align_up(static_cast<size_t>(s.nwarps) * sizeof(ssi::ScatInfo), 256);
+  s.bytes = o;
+  return s;
+}
+
+template <int MODE>
+int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
+                                const ssi::ScatOut& out, void* ws, size_t ws_bytes, void* stream, int phases,
+                                int cat = CAT_SCATTER);
+ssi::ScatOut dense_out(void* dW);
+
 // Single-pass ("stash") mode: forward also forms the gradients, one ROW chunk at a time, so the logits are
 // computed once (6 N V D executed instead of 8 N V D).  Scratch: one bf16 block S/G [rows_cap, Vpad].
 struct SpPlan {
@@ -431,7 +463,8 @@ struct SpPlan {
   int tiles_m, vtiles_total, combine_blocks, t_max, chunks_max;
   CompactWs cw;
   size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_rstd, off_dsp, off_dxc, off_s, bytes;
-  size_t off_ref2, off_rowscale, off_xs;  // exp-stash form: pilot reference, per-row factor, scaled X rows
+  // exp-stash form: pilot reference, per-row factor, scaled X rows, workspace of the label-keyed onehot scatter
+  size_t off_ref2, off_rowscale, off_xs, off_lscat, lscat_bytes;
 };
 constexpr size_t SYNC_AREA_BYTES = 4096;
 constexpr int NORM_BWD_BLOCKS = 148 * 2;            // grid of the fused norm-backward scatter
@@ -471,36 +504,12 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   f.off_ref2 = o, o += align_up(items * ssi::BM * sizeof(float), 256);
   f.off_rowscale = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
   f.off_xs = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
+  f.lscat_bytes = plan_scatter(f.n_pad, V, D).bytes;
+  f.off_lscat = o, o += align_up(f.lscat_bytes, 1024);
   f.off_s = o, o += align_up(static_cast<size_t>(f.t_max) * ssi::BM * f.vpad * 2, 1024);
   f.bytes = o;
   *out = f;
   return 0;
-}
-
-struct ScatPlan {
-  int nwarps, passes, slabs;
-  size_t off_k0, off_v0, off_k1, off_v1, off_urank, off_nuniq, off_partial, off_info, bytes;
-};
-
-ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
-  ScatPlan s;
-  s.nwarps = static_cast<int>(ceil_div(N, 32));
-  s.slabs = static_cast<int>(ceil_div(D, ssi::SCAT_COLS));
-  int bits = 1;
-  while ((int64_t(1) << bits) <= V) ++bits;  // keys are in [0, V] (V = out-of-range sentinel)
-  s.passes = (bits + ssi::SORT_BITS - 1) / ssi::SORT_BITS;
-  size_t o = 0;
-  const size_t arr = align_up(static_cast<size_t>(N) * 4, 256);
-  s.off_k0 = o, o += arr;
-  s.off_v0 = o, o += arr;
-  s.off_k1 = o, o += arr;
-  s.off_v1 = o, o += arr;
-  s.off_urank = o, o += arr;
-  s.off_nuniq = o, o += 256;
-  s.off_partial = o, o += align_up(static_cast<size_t>(s.nwarps) * 2 * D * sizeof(float), 256);
-  s.off_info = o, o += align_up(static_cast<size_t>(s.nwarps) * sizeof(ssi::ScatInfo), 256);
-  s.bytes = o;
-  return s;
 }
 
 int check_common(const void* X, const void* W, int64_t N, int64_t V, int64_t D) {
@@ -916,9 +925,8 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       // the first logits contraction; the combine below is their first consumer
       if (ch == 0 && pre_grad_event) SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pre_grad_event), 0));
       ProfScope ps(CAT_AUX, st);
-      ssi::exp_combine_kernel<<<64, 256, 0, st>>>(ref2, part_l, part_z, cplan, labels_c, grad_hint, nvt,
-                                                  static_cast<__nv_bfloat16*>(S), f.vpad, static_cast<int>(V), lse_c,
-                                                  loss_c, rowscale_c);
+      ssi::exp_combine_kernel<<<64, 256, 0, st>>>(ref2, part_l, part_z, cplan, grad_hint, nvt, lse_c, loss_c,
+                                                  rowscale_c);
       SSI_LAUNCH_OK("exp_combine");
       ssi::scale_rows_kernel<<<di->sms * 4, 256, 0, st>>>(static_cast<const uint4*>(Xc), rowscale_c, cplan,
                                                           static_cast<int>(D / 8), static_cast<uint4*>(Xs));
@@ -962,9 +970,20 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       if (lockstep > 0) p.sync_ctr = sync_area + 2 * ch, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
       if (int r = launch_gemm_wide<ssi::EPI_F32, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
         return r;
-      // dW_acc is final after the last round's contraction (the real chunks occupy the last rounds): let the
-      // caller start the gradient exchange on another stream while this stream still runs the last dX
-      if (dw_ready_event && ch == f.chunks_max - 1) SSI_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(dw_ready_event), st));
+      if (ch == f.chunks_max - 1) {
+        if (estash) {
+          // the onehot term of dW, exact in fp32: dW_acc[v, :] -= g * sum of the X_c rows whose label is v
+          ssi::ScatOut o = dense_out(dW_acc);
+          o.scale_num = grad_hint, o.scale_den = reinterpret_cast<const long long*>(nvt), o.scale_sign = -1.f;
+          if (int r = embedding_grad_scatter_impl<ssi::SCAT_DENSE_F32>(Xc, labels_c, f.n_pad, V, D, o,
+                                                                       wsb + f.off_lscat, f.lscat_bytes, stream, 3,
+                                                                       CAT_SOFTMAX))
+            return r;
+        }
+        // dW_acc is final after the last round's contraction (the real chunks occupy the last rounds): let the
+        // caller start the gradient exchange on another stream while this stream still runs the last dX
+        if (dw_ready_event) SSI_CUDA(cudaEventRecord(static_cast<cudaEvent_t>(dw_ready_event), st));
+      }
     }
     // ---- dXc[chunk] = G W   (M = the chunk's token rows, N = D, K = padded vocabulary)
     {
@@ -992,6 +1011,13 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
   if (norm_scale) {
     // backward of the fused norm while the compact dX rows go back to their positions: dX = d(pre-norm h)
     const int row_u4 = static_cast<int>(D / 8);
+    if (estash) {
+      ssi::dx_label_term_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(dXc), labels_c,
+                                                             static_cast<int>(f.n_pad), row_u4,
+                                                             static_cast<const uint4*>(W), static_cast<int>(V),
+                                                             grad_hint, nvt);
+      SSI_LAUNCH_OK("dx_label_term");
+    }
     const int maxj = (row_u4 + 31) / 32;
     float* partial = reinterpret_cast<float*>(wsb + f.off_dsp);
     const float* rstd_c = reinterpret_cast<const float*>(wsb + f.off_rstd);
@@ -1011,8 +1037,9 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
     SSI_LAUNCH_OK("rmsnorm_dscale_reduce");
     return 0;
   }
-  ssi::dx_scatter_bf16_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<const uint4*>(dXc), pos, static_cast<int>(N),
-                                                           static_cast<int>(D / 8), static_cast<uint4*>(dX));
+  ssi::dx_scatter_bf16_kernel<<<di->sms * 8, 256, 0, st>>>(
+      static_cast<const uint4*>(dXc), pos, static_cast<int>(N), static_cast<int>(D / 8), static_cast<uint4*>(dX),
+      estash ? static_cast<const uint4*>(W) : nullptr, labels_c, static_cast<int>(V), grad_hint, nvt);
   SSI_LAUNCH_OK("dx_scatter");
   return 0;
 }
@@ -1048,7 +1075,7 @@ namespace {
 // phases: bit 0 = sort the ids (leaves the order in ws), bit 1 = segmented reduction of the dH rows in that order
 template <int MODE>
 int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, int64_t V, int64_t D,
-                                const ssi::ScatOut& out, void* ws, size_t ws_bytes, void* stream, int phases) {
+                                const ssi::ScatOut& out, void* ws, size_t ws_bytes, void* stream, int phases, int cat) {
   SSI_CHECK_ARG(ws && (!(phases & 1) || ids) && (!(phases & 2) || dH), "null pointer argument");
   SSI_CHECK_ARG(N >= 1 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
@@ -1067,7 +1094,7 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
   int* nuniq = reinterpret_cast<int*>(wsb + s.off_nuniq);
   const int n = static_cast<int>(N);
 
-  ProfScope ps_scat(CAT_SCATTER, st);
+  ProfScope ps_scat(cat, st);
   if (phases & 1) {
     static std::once_flag once[64];
     std::call_once(once[di->dev], [] {

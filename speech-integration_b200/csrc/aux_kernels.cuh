@@ -397,28 +397,36 @@ __device__ __forceinline__ uint4 f32x8_to_bf16(const float (&f)[8]) {
 
 // ---------------------------------------------------------------------------------------------------
 // Exp-stash form of single-pass mode (default).  K1 left E[r, v] = bf16(2^(s log2e - ref2[r])) in the block and the
-// per-split row sums of the fp32 values; softmax[r, v] = E[r, v] / L[r] with L = sum over splits, so dlogits =
-// (hint / n_valid) * (E / L - onehot) is E times a per-ROW factor once the label column is patched:
-//   exp_combine_kernel   lse = (ref2 + log2 L) ln2, loss = lse - z_label, rowscale[r] = (hint / n_valid) / L[r],
-//                        and E[r, label] <- bf16(E32[r, label] - L[r])  (so that E' / L = softmax - onehot there)
-//   scale_rows_kernel    Xs[r, :] = bf16(rowscale[r] * X_c[r, :]): the rows dW = E'^T Xs contracts with
-// and dX = rowscale[r] * (E' W)[r, :] takes the factor in its epilogue.  No pass over the [rows, V] block.
+// per-split row sums of the fp32 values; softmax[r, v] = E[r, v] / L[r] with L = sum over splits, so with
+// g = hint / n_valid:   dlogits = g * softmax - g * onehot = rowscale[r] * E[r, :] - g * onehot,  rowscale = g / L.
+// The two terms are kept apart.  The softmax term goes through the tensor cores as E times a per-ROW factor:
+//   exp_combine_kernel   lse = (ref2 + log2 L) ln2, loss = lse - z_label, rowscale[r] = g / L[r]
+//   scale_rows_kernel    Xs[r, :] = bf16(rowscale[r] * X_c[r, :]): the rows dW = E^T Xs contracts with
+//   dX contraction       rowscale[r] * (E W)[r, :] in its epilogue.
+// The onehot term -- the dominant part of every row of the gradient -- is exact arithmetic on the operands instead
+// of a bf16-rounded matrix element:
+//   dX[r, :] -= g * W[label_r, :]          while the compact rows go back to their positions (dx_scatter_bf16_kernel,
+//                                          or dx_label_term_kernel in place before the fused norm backward)
+//   dW_acc[v, :] -= g * sum_{label_r = v} X_c[r, :]   by the sorted fp32 segmented reduction of scatter.cuh, keyed by
+//                                          the labels (no atomics: bit-identical run to run).
+// No pass over the [rows, V] block.
 // ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float grad_scale(const float* grad_hint, const int64_t* n_valid_total) {
+  const long long nvt = *n_valid_total;
+  return (nvt > 0) ? (*grad_hint / static_cast<float>(nvt)) : 0.f;
+}
+
 __global__ void __launch_bounds__(256) exp_combine_kernel(const float* __restrict__ ref2,
                                                           const float* __restrict__ part_l,
                                                           const float* __restrict__ part_z,
                                                           const DevPlan* __restrict__ plan,
-                                                          const int64_t* __restrict__ labels_c,
                                                           const float* __restrict__ grad_hint,
                                                           const int64_t* __restrict__ n_valid_total,
-                                                          __nv_bfloat16* __restrict__ E, long long row_elems, int V,
                                                           float* __restrict__ lse_c, float* __restrict__ loss_c,
                                                           float* __restrict__ rowscale_c) {
   const int rows = plan->tiles_m * 128, nv = plan->n_valid, row0 = plan->row0;
   const int splits = plan->splits, part_stride = plan->part_stride;
-  const long long nvt = *n_valid_total;
-  const float gscale = (nvt > 0) ? (*grad_hint / static_cast<float>(nvt)) : 0.f;
-  constexpr float kLog2e = 1.4426950408889634f;
+  const float gscale = grad_scale(grad_hint, n_valid_total);
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
     float l = 0.f, loss = 0.f, rs = 0.f;
     if (r < nv) {
@@ -428,15 +436,9 @@ __global__ void __launch_bounds__(256) exp_combine_kernel(const float* __restric
         L += part_l[o];
         z = fmaxf(z, part_z[o]);
       }
-      const float c2 = ref2[r];
-      l = (c2 + log2f(L)) * 0.6931471805599453f;
+      l = (ref2[r] + log2f(L)) * 0.6931471805599453f;
       loss = l - z;
       rs = gscale / L;
-      const long long lab = labels_c[row0 + r];
-      if (lab >= 0 && lab < V) {
-        const float e_lab = fast_exp2(fmaf(z, kLog2e, -c2));  // the fp32 value K1 rounded into E[r, label]
-        E[static_cast<size_t>(r) * row_elems + lab] = __float2bfloat16_rn(e_lab - L);
-      }
     }
     lse_c[row0 + r] = l;
     loss_c[row0 + r] = loss;
@@ -506,21 +508,61 @@ __global__ void __launch_bounds__(COMBINE_THREADS) stash_finish_kernel(const flo
   }
 }
 
-// dX[r, :] = dXc[pos[r], :] for valid rows, zeros for ignored rows (bf16 rows, 16-byte accesses).
+// out = bf16(a - g * w), eight bf16 values at a time
+__device__ __forceinline__ uint4 bf16x8_sub_scaled(const uint4& a, const uint4& w, float g) {
+  float fa[8], fw[8];
+  bf16x8_to_f32(a, fa);
+  bf16x8_to_f32(w, fw);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) fa[e] = fmaf(-g, fw[e], fa[e]);
+  return f32x8_to_bf16(fa);
+}
+
+// dX[r, :] = dXc[pos[r], :] for valid rows, zeros for ignored rows (bf16 rows, 16-byte accesses).  With W (exp-stash
+// form): dX[r, :] = dXc[pos[r], :] - g * W[label, :], the onehot term of the row.
 __global__ void __launch_bounds__(256) dx_scatter_bf16_kernel(const uint4* __restrict__ dXc,
                                                               const int* __restrict__ pos, int n, int row_u4,
-                                                              uint4* __restrict__ dX) {
+                                                              uint4* __restrict__ dX,
+                                                              const uint4* __restrict__ W,
+                                                              const int64_t* __restrict__ labels_c, int V,
+                                                              const float* __restrict__ grad_hint,
+                                                              const int64_t* __restrict__ n_valid_total) {
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float g = W ? grad_scale(grad_hint, n_valid_total) : 0.f;
   for (int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; r < n; r += warps) {
     const int c = pos[r];
     uint4* dst = dX + static_cast<size_t>(r) * row_u4;
     if (c >= 0) {
       const uint4* src = dXc + static_cast<size_t>(c) * row_u4;
-      for (int j = lane; j < row_u4; j += 32) dst[j] = src[j];
+      const long long lab = W ? labels_c[c] : -1;
+      if (lab >= 0 && lab < V) {
+        const uint4* wrow = W + static_cast<size_t>(lab) * row_u4;
+        for (int j = lane; j < row_u4; j += 32) dst[j] = bf16x8_sub_scaled(src[j], __ldg(wrow + j), g);
+      } else {
+        for (int j = lane; j < row_u4; j += 32) dst[j] = src[j];
+      }
     } else {
       for (int j = lane; j < row_u4; j += 32) dst[j] = make_uint4(0, 0, 0, 0);
     }
+  }
+}
+
+// In place on the compact rows: dXc[c, :] -= g * W[labels_c[c], :] (exp-stash form ahead of the fused norm backward).
+__global__ void __launch_bounds__(256) dx_label_term_kernel(uint4* __restrict__ dXc,
+                                                            const int64_t* __restrict__ labels_c, int n_pad,
+                                                            int row_u4, const uint4* __restrict__ W, int V,
+                                                            const float* __restrict__ grad_hint,
+                                                            const int64_t* __restrict__ n_valid_total) {
+  const int lane = threadIdx.x & 31;
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const float g = grad_scale(grad_hint, n_valid_total);
+  for (int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; c < n_pad; c += warps) {
+    const long long lab = labels_c[c];
+    if (lab < 0 || lab >= V) continue;
+    uint4* row = dXc + static_cast<size_t>(c) * row_u4;
+    const uint4* wrow = W + static_cast<size_t>(lab) * row_u4;
+    for (int j = lane; j < row_u4; j += 32) row[j] = bf16x8_sub_scaled(row[j], __ldg(wrow + j), g);
   }
 }
 

@@ -205,6 +205,11 @@ struct ScatOut {
   unsigned long long* slot;  // compact mode: [V], (epoch << 32 | index into rows)
   unsigned int epoch;
   int cap;
+  // fp32 dense mode: rows are multiplied by scale_sign * (*scale_num) / (*scale_den) before they are added
+  // (null scale_num: plain add).  Used for the onehot term of the LM-head gradient, keyed by the labels.
+  const float* scale_num;
+  const long long* scale_den;
+  float scale_sign;
 };
 
 struct ScatInfo {
@@ -247,14 +252,21 @@ __device__ __forceinline__ void emit_run(const ScatOut& o, uint32_t key, int ur,
     }
   } else {
     float* dst = static_cast<float*>(o.dense) + static_cast<size_t>(key) * D + d0;
+    float sc = 1.f;
+    if (o.scale_num) {
+      const long long den = *o.scale_den;
+      sc = (den > 0) ? o.scale_sign * (*o.scale_num / static_cast<float>(den)) : 0.f;
+    }
 #pragma unroll
     for (int g = 0; g < SCAT_G; ++g) {
       const int col = g * 256 + static_cast<int>(lane) * 8;
       if (col < dcols) {
         float4* ptr = reinterpret_cast<float4*>(dst + col);
         float4 a = ptr[0], b = ptr[1];
-        a.x += acc[g][0], a.y += acc[g][1], a.z += acc[g][2], a.w += acc[g][3];
-        b.x += acc[g][4], b.y += acc[g][5], b.z += acc[g][6], b.w += acc[g][7];
+        a.x = fmaf(sc, acc[g][0], a.x), a.y = fmaf(sc, acc[g][1], a.y), a.z = fmaf(sc, acc[g][2], a.z);
+        a.w = fmaf(sc, acc[g][3], a.w);
+        b.x = fmaf(sc, acc[g][4], b.x), b.y = fmaf(sc, acc[g][5], b.y), b.z = fmaf(sc, acc[g][6], b.z);
+        b.w = fmaf(sc, acc[g][7], b.w);
         ptr[0] = a, ptr[1] = b;
       }
     }
