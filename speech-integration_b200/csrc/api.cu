@@ -426,7 +426,7 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
 
 struct ScatPlan {
   int nwarps, passes, slabs;
-  size_t off_k0, off_v0, off_k1, off_v1, off_urank, off_nuniq, off_partial, off_info, bytes;
+  size_t off_k0, off_v0, off_k1, off_v1, off_urank, off_nuniq, off_ghist, off_partial, off_info, bytes;
 };
 
 ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
@@ -443,7 +443,8 @@ ScatPlan plan_scatter(int64_t N, int64_t V, int64_t D) {
   s.off_k1 = o, o += arr;
   s.off_v1 = o, o += arr;
   s.off_urank = o, o += arr;
-  s.off_nuniq = o, o += 256;
+  s.off_nuniq = o, o += 256;  // [0] number of distinct ids, [16] arrival counter of the sort's grid barrier
+  s.off_ghist = o, o += static_cast<size_t>(ssi::SORT_DIGITS) * ssi::SORT_MAX_BLOCKS * sizeof(uint32_t);
   s.off_partial = o, o += align_up(static_cast<size_t>(s.nwarps) * 2 * D * sizeof(float), 256);
   s.off_info = o, o += align_up(static_cast<size_t>(s.nwarps) * sizeof(ssi::ScatInfo), 256);
   s.bytes = o;
@@ -1098,24 +1099,37 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
   if (phases & 1) {
     static std::once_flag once[64];
     std::call_once(once[di->dev], [] {
-      cudaFuncSetAttribute(ssi::sort_block_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::SORT_SMEM_BYTES);
+      cudaFuncSetAttribute(ssi::sort_grid_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ssi::SORT_SMEM_BYTES);
     });
-    ssi::sort_block_kernel<<<1, ssi::SORT_THREADS, ssi::SORT_SMEM_BYTES, st>>>(ids, n, V, s.passes, k[0], v[0], k[1],
-                                                                               v[1], urank, nuniq);
-    SSI_LAUNCH_OK("sort_block");
+    // one block per SORT_KEYS_PER_BLOCK ids; cooperative launch: the blocks synchronise through a counter in ws
+    int G = static_cast<int>(ceil_div(N, ssi::SORT_KEYS_PER_BLOCK));
+    const int g_max = di->sms < ssi::SORT_MAX_BLOCKS ? di->sms : ssi::SORT_MAX_BLOCKS;
+    G = G < 1 ? 1 : (G > g_max ? g_max : G);
+    SSI_CUDA(cudaMemsetAsync(nuniq, 0, 256, st));
+    uint32_t* ghist = reinterpret_cast<uint32_t*>(wsb + s.off_ghist);
+    unsigned int* bar = reinterpret_cast<unsigned int*>(nuniq) + 16;
+    long long v_ll = V;
+    int passes = s.passes;
+    int n_arg = n;
+    void* args[] = {&ids, &n_arg, &v_ll, &passes, &k[0], &v[0], &k[1], &v[1], &urank, &nuniq, &ghist, &bar};
+    SSI_CUDA(cudaLaunchCooperativeKernel(reinterpret_cast<const void*>(ssi::sort_grid_kernel), dim3(G),
+                                         dim3(ssi::SORT_THREADS), args, ssi::SORT_SMEM_BYTES, st));
+    SSI_LAUNCH_OK("sort_grid");
   }
   if (!(phases & 2)) return 0;
   const int cur = (s.passes - 1) & 1;
   float* partial = reinterpret_cast<float*>(wsb + s.off_partial);
   ssi::ScatInfo* info = reinterpret_cast<ssi::ScatInfo*>(wsb + s.off_info);
-  // 128-thread blocks, no shared memory: small enough to co-reside with a persistent tensor-core CTA
-  const dim3 grid(static_cast<unsigned>(ceil_div(s.nwarps, 4)), static_cast<unsigned>(s.slabs));
-  ssi::scatter_reduce_kernel<MODE><<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur], v[cur], urank,
-                                                         n, static_cast<uint32_t>(V), static_cast<int>(D), out,
-                                                         partial, info);
+  // no shared memory, <= 72 registers: co-resides with a persistent tensor-core CTA
+  const int64_t warps_total = static_cast<int64_t>(s.nwarps) * s.slabs;
+  const unsigned grid = static_cast<unsigned>(ceil_div(warps_total, ssi::SCAT_THREADS / 32));
+  ssi::scatter_reduce_kernel<MODE><<<grid, ssi::SCAT_THREADS, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur],
+                                                                      v[cur], urank, n, static_cast<uint32_t>(V),
+                                                                      static_cast<int>(D), s.slabs, out, partial, info);
   SSI_LAUNCH_OK("scatter_reduce");
-  ssi::scatter_fixup_kernel<MODE><<<grid, 128, 0, st>>>(partial, info, s.nwarps, static_cast<uint32_t>(V),
-                                                        static_cast<int>(D), out);
+  ssi::scatter_fixup_kernel<MODE><<<grid, ssi::SCAT_THREADS, 0, st>>>(partial, info, s.nwarps,
+                                                                     static_cast<uint32_t>(V), static_cast<int>(D),
+                                                                     s.slabs, out);
   SSI_LAUNCH_OK("scatter_fixup");
   return 0;
 }

@@ -82,6 +82,13 @@ def main():
     add("embedding_grad_scatter", timed(lambda: ops.embedding_grad_scatter(dY, tokens.reshape(-1), dWg), args.iters,
                                         flush), N * D * 2 + N * 8 + uniq * D * 4,
         f"K3: read dH + ids, RMW of the {uniq} touched rows (sort included)")
+    ids = tokens.reshape(-1)
+    add("embedding_grad_sort", timed(lambda: ops.embedding_grad_sort(ids, V, D), args.iters, flush), N * 8 + N * 12,
+        "K3 sort alone (one block): read ids, write sorted keys + rows + run index")
+    sort_ws = ops.embedding_grad_sort(ids, V, D)
+    add("embedding_grad_scatter_sorted", timed(lambda: ops.embedding_grad_scatter_sorted(dY, sort_ws, dWg),
+                                               args.iters, flush), N * D * 2 + N * 12 + uniq * D * 4,
+        "K3 segmented reduce alone (order given): read dH rows, RMW of the touched rows")
     path = PathStep(W)
     Xb = X.reshape(B, S, D)
     ms = timed(lambda: path.forward_only(Xb, labels), args.iters, flush)
