@@ -325,6 +325,7 @@ struct Tune {
   // single-pass: 1 = K1 stashes E = exp(logit - ref[row]) and the softmax normalisation is a per-row factor folded into
   // the dX epilogue and the X rows of dW (no pass over the block); 0 = stash logits + separate softmax-grad HBM pass
   int exp_stash = 1;
+  int k1_group_m = 0;  // K1: m-tiles (128 rows) per raster group, 0 = the whole row chunk (GemmParams::lse_group_m)
 };
 // The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
 // thread-local SNAPSHOT under the mutex (TuneScope), so one call never sees half of an update.
@@ -349,6 +350,7 @@ Tune& global_tune() {
     if (const char* e = getenv("SSI_B200_WIDE_DW")) x.wide_dw = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_EXP_STASH")) x.exp_stash = atoi(e) ? 1 : 0;
+    if (const char* e = getenv("SSI_B200_K1_GROUP_M")) x.k1_group_m = atoi(e);
     return x;
   }();
   return t;
@@ -378,7 +380,7 @@ struct BwdPlan {
   int tiles_m, vtiles_total, nblocks, vtiles_per_block;
   int64_t vc;  // columns of the dlogits block buffer
   CompactWs cw;
-  size_t off_lse_c, off_g, off_dxacc, bytes;
+  size_t off_lse_c, off_g, off_dxacc, off_sync, bytes;
 };
 
 // SM count of the current device for host-side schedules (148 on B200; queried, not assumed)
@@ -420,6 +422,7 @@ BwdPlan plan_bwd(int64_t N, int64_t V, int64_t D) {
   b.off_lse_c = o, o += align_up(static_cast<size_t>(b.n_pad) * sizeof(float), 256);
   b.off_g = o, o += align_up(static_cast<size_t>(b.n_pad) * b.vc * 2, 1024);
   b.off_dxacc = o, o += align_up(static_cast<size_t>(b.n_pad) * D * sizeof(float), 1024);
+  b.off_sync = o, o += 4096;  // lockstep counters of the dW / dX contractions (two per vocabulary block) + error word
   b.bytes = o;
   return b;
 }
@@ -554,6 +557,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "wide_dw")) t.wide_dw = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "exp_stash")) t.exp_stash = value ? 1 : 0;
+  else if (!strcmp(name, "k1_group_m")) t.k1_group_m = value > 0 ? static_cast<int>(value) : 0;
   else return fail(-1, "unknown option '%s'", name);
   return 0;
 }
@@ -615,6 +619,7 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   p.tiles_n = 1;
   p.k_blocks = static_cast<int>(D / ssi::BK);
   p.group_m = f.tiles_m;  // all m-tiles of one split run together: they stream the same W tiles through L2
+  p.lse_group_m = tune().k1_group_m;
   p.labels = labels_c;
   p.ignore_index = ignore_index;
   p.n_rows = static_cast<int>(f.n_pad);
@@ -667,6 +672,10 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
   void* G = wsb + b.off_g;
   float* dxacc = reinterpret_cast<float*>(wsb + b.off_dxacc);
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
+  // lockstep throttle of the two long-K contractions, as in single-pass mode (one counter per launch)
+  unsigned int* sync_area = reinterpret_cast<unsigned int*>(wsb + b.off_sync);
+  const int lockstep = (b.nblocks <= 500) ? tune().lockstep : 0;
+  if (lockstep > 0) SSI_CUDA(cudaMemsetAsync(sync_area, 0, 4096, st));
 
   // ---- the same compaction as forward (stateless ABI: recomputed from the labels, ~0.1 ms)
   {
@@ -723,11 +732,13 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.tiles_m = static_cast<int>(ceil_div(vrows, ssi::BM));
       p.tiles_n = d_tiles;
       p.k_blocks = static_cast<int>(b.n_pad / ssi::BK);
-      p.group_m = tune().group_m_grad;
+      p.group_m = tune().group_m_dw;
       p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.c_r0 = v0;
       p.c_reduce = accumulate_dW ? 1 : 0;
-      if (int r = launch_gemm<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW)) return r;
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * blk, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
+      if (int r = launch_gemm_wide<ssi::EPI_BF16, true, true>(p, di->sms, st, "lmhead_dW", CAT_DW, tune().wide_dw))
+        return r;
     }
     // ---- K2c: dXacc_c (+)= G W[v0 : v0 + vtn*256)   (M = valid tokens, N = D, K = vocabulary block)
     {
@@ -737,10 +748,12 @@ int ssi_b200_lmhead_ce_bwd(const void* X, const void* W, const int64_t* labels, 
       p.dplan = dplan, p.m_from_plan = 1;
       p.tiles_m = b.tiles_m, p.tiles_n = d_tiles;
       p.k_blocks = vtn * (ssi::BN / ssi::BK);
-      p.group_m = tune().group_m_grad;
+      p.group_m = tune().group_m_dx;
       p.b_k0 = v0;
       p.c_reduce = (blk > 0) ? 1 : 0;
-      if (int r = launch_gemm<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX)) return r;
+      if (lockstep > 0) p.sync_ctr = sync_area + 2 * blk + 1, p.sync_err = sync_area + 1023, p.sync_every = lockstep;
+      if (int r = launch_gemm_wide<ssi::EPI_F32, false, true>(p, di->sms, st, "lmhead_dX", CAT_DX, tune().wide_dx))
+        return r;
     }
   }
   {
@@ -899,6 +912,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       p.dplan = cplan, p.m_from_plan = 1, p.plan_rows = ssi::PR_A_ROWS | ssi::PR_LABEL_ROWS;
       p.tiles_m = f.t_max, p.tiles_n = 1, p.k_blocks = static_cast<int>(D / ssi::BK);
       p.group_m = f.t_max;
+      p.lse_group_m = tune().k1_group_m;
       p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
       p.labels = labels_c, p.ignore_index = ignore_index;
       p.n_rows = static_cast<int>(f.n_pad), p.vocab = static_cast<int>(V), p.col0 = 0;

@@ -110,6 +110,9 @@ struct GemmParams {
   const int64_t* n_valid;    // [1]
   // EPI_LSE: 1 = ONE split of p.vtiles_per_split tiles whatever the plan says (the pilot sweep over the first tile)
   int lse_one_split;
+  // LSE epilogues: m-tiles (128 rows) per raster group; 0 = all of them.  The X rows of one group are re-read from L2
+  // for every vocabulary tile, so a group should fit ONE L2 partition next to the stash write stream.
+  int lse_group_m;
   // EPI_EXP_STASH: per-row reference in the log2 domain, indexed by the plan-relative row (the pilot's running max)
   const float* row_ref2;
   // EPI_BF16: optional per-row factor applied before the rounding, indexed like the C rows (c_r0 + plan offset + row)
@@ -167,7 +170,7 @@ __device__ __forceinline__ Sched make_sched(const GemmParams& p) {
         s.vtiles_per_split = p.dplan->vtiles_per_split;
         if (p.lse_one_split) s.tiles_n = 1, s.vtiles_per_split = p.vtiles_per_split;
         s.part_stride = p.dplan->part_stride;
-        s.group_m = max(s.tiles_m, 1);
+        s.group_m = max(p.lse_group_m > 0 ? min(p.lse_group_m, s.tiles_m) : s.tiles_m, 1);
       }
     }
     if (p.k_from_plan) s.k_blocks = p.dplan->k_blocks_tok;
