@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 110
+#define SSI_B200_ABI_VERSION 111
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -300,6 +300,37 @@ int ssi_b200_label_shift_count_types(const int64_t* labels, const int64_t* token
 int ssi_b200_grad_scale_sqnorm_workspace_bytes(size_t* bytes);
 int ssi_b200_grad_scale_sqnorm(void* grad, int64_t n_elems, const float* scale, float* sqnorm_out, void* ws,
                                size_t ws_bytes, void* stream);
+
+/*
+ * The same two passes FOLDED into the kernels that write the tied gradient anyway (replaces
+ * tt/torchtune/training/_grad_scaler.py:25-31 + the tied weight's share of clip_grad_norm_, ssi/trainer.py:404-408,
+ * on the last micro-batch of an accumulation window): every "_fold" entry point below is its plain namesake plus
+ *   post_scale    fp32 device scalar or NULL: the scaler of scale_grads, applied in fp32 BEFORE the one rounding to
+ *                 bf16 (the dense site also rescales what the gradient buffer already held when it accumulates);
+ *   fold_ws       device scratch (ssi_b200_grad_fold_workspace_bytes, 16-byte aligned) or NULL: receives each
+ *                 kernel's share of sum(g^2) -- block partials of the new values at the dense site, warp partials of
+ *                 new^2 - old^2 at the sparse site.
+ * Order per optimizer step: the dense site first (lmhead_ce_apply_grad_fold or dp_exchange_fold: it zeroes
+ * fold_ws), then the sparse site (embedding_grad_scatter_sorted_fold or dp_embedding_exchange_fold), then
+ * ssi_b200_grad_fold_sqnorm: sqnorm_out[0] = sum over the whole [V, D] gradient of g^2 (partials added in a fixed
+ * order in double: deterministic).  No separate pass over the gradient remains.
+ */
+int ssi_b200_grad_fold_workspace_bytes(int64_t max_rows, int64_t D, size_t* bytes);
+int ssi_b200_grad_fold_sqnorm(const void* fold_ws, size_t fold_ws_bytes, float* sqnorm_out, void* stream);
+int ssi_b200_lmhead_ce_apply_grad_fold(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
+                                       int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW,
+                                       const float* post_scale, void* fold_ws, size_t fold_ws_bytes, void* stream);
+int ssi_b200_embedding_grad_scatter_sorted_fold(const void* dH, int64_t N, int64_t V, int64_t D, void* dW, void* ws,
+                                                size_t ws_bytes, const float* post_scale, void* fold_ws,
+                                                size_t fold_ws_bytes, void* stream);
+int ssi_b200_dp_exchange_fold(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,
+                              uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW,
+                              int accumulate_dW, void* host_flag, const float* post_scale, void* fold_ws,
+                              size_t fold_ws_bytes, void* stream);
+int ssi_b200_dp_embedding_exchange_fold(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
+                                        size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world,
+                                        int64_t max_rows, uint32_t epoch, void* dW, void* host_flag,
+                                        const float* post_scale, void* fold_ws, size_t fold_ws_bytes, void* stream);
 
 /* Forward embedding gather (tt/torchtune/modules/transformer.py:628): out[i, :] = W[ids[i], :], bf16, exact copy;
  * ids outside [0, V) give zero rows. */

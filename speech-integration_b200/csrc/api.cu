@@ -525,6 +525,31 @@ int check_common(const void* X, const void* W, int64_t N, int64_t V, int64_t D) 
   return 0;
 }
 
+// scale_grads / grad-norm fold (aux_kernels.cuh GradFold): float partials in three segments -- [0, 4096) the dense
+// writer's blocks (apply_dw / dp_reduce: the rank's own slice), [4096, 8192) dp_gather's blocks, [8192, end) the
+// warps of the sparse read-modify-write site (embedding scatter / dp_sparse_add)
+constexpr int FOLD_SEG = 4096;
+struct FoldWs {
+  float* base = nullptr;
+  size_t floats = 0;
+  float* seg(int i) const { return base ? base + static_cast<size_t>(i) * FOLD_SEG : nullptr; }
+  size_t sparse_floats() const { return floats > 2 * FOLD_SEG ? floats - 2 * FOLD_SEG : 0; }
+};
+size_t fold_sparse_floats(int64_t max_rows, int64_t D) {
+  const size_t scat = 2 * static_cast<size_t>(ceil_div(max_rows, 32)) * static_cast<size_t>(ceil_div(D, ssi::SCAT_COLS));
+  return scat > 2 * FOLD_SEG ? scat : 2 * FOLD_SEG;
+}
+int fold_ws(void* ws, size_t bytes, FoldWs* out) {
+  FoldWs f;
+  if (ws) {
+    SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(ws) & 15) == 0, "fold workspace must be 16-byte aligned");
+    SSI_CHECK_ARG(bytes >= (2 * FOLD_SEG + 2 * FOLD_SEG) * sizeof(float), "fold workspace too small: %zu", bytes);
+    f.base = static_cast<float*>(ws), f.floats = bytes / sizeof(float);
+  }
+  *out = f;
+  return 0;
+}
+
 }  // namespace
 
 // ===================================================================================================
@@ -1061,15 +1086,27 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
 
 int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
                                   int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW, void* stream) {
+  return ssi_b200_lmhead_ce_apply_grad_fold(dX, dW_acc, grad_out, grad_hint, N, V, D, dW, accumulate_dW, nullptr,
+                                            nullptr, 0, stream);
+}
+
+int ssi_b200_lmhead_ce_apply_grad_fold(void* dX, const float* dW_acc, const float* grad_out, const float* grad_hint,
+                                       int64_t N, int64_t V, int64_t D, void* dW, int accumulate_dW,
+                                       const float* post_scale, void* fold_ws_ptr, size_t fold_ws_bytes,
+                                       void* stream) {
   SSI_CHECK_ARG(grad_out && grad_hint && (dW_acc || !dW), "null pointer argument");
   SSI_CHECK_ARG(N >= 0 && V >= 1 && D >= 8 && D % 8 == 0, "bad shape N=%lld V=%lld D=%lld", (long long)N,
                 (long long)V, (long long)D);
   SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(dX) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW_acc) & 15) == 0 &&
                     (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
                 "dX / dW_acc / dW must be 16-byte aligned");
+  SSI_CHECK_ARG(dW || (!post_scale && !fold_ws_ptr), "the scale_grads fold needs dW");
+  FoldWs fw;
+  if (int r = fold_ws(fold_ws_ptr, fold_ws_bytes, &fw)) return r;
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (fw.base) SSI_CUDA(cudaMemsetAsync(fw.base, 0, fw.floats * sizeof(float), st));  // a fold begins here
   ProfScope ps(CAT_AUX, st);
   if (dX && N > 0) {
     ssi::apply_dx_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(dX), static_cast<size_t>(N) * D / 8,
@@ -1077,11 +1114,32 @@ int ssi_b200_lmhead_ce_apply_grad(void* dX, const float* dW_acc, const float* gr
     SSI_LAUNCH_OK("apply_dx");
   }
   if (dW) {
-    ssi::apply_dw_kernel<<<di->sms * 16, 256, 0, st>>>(reinterpret_cast<const float4*>(dW_acc),
-                                                       static_cast<size_t>(V) * D / 4, grad_out, grad_hint,
-                                                       accumulate_dW ? 1 : 0, static_cast<uint2*>(dW));
+    const int grid = di->sms * 16 < FOLD_SEG ? di->sms * 16 : FOLD_SEG;
+    ssi::GradFold gf;
+    gf.post_scale = post_scale, gf.sq = fw.seg(0);
+    ssi::apply_dw_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(dW_acc),
+                                               static_cast<size_t>(V) * D / 4, grad_out, grad_hint,
+                                               accumulate_dW ? 1 : 0, static_cast<uint2*>(dW), gf);
     SSI_LAUNCH_OK("apply_dw");
   }
+  return 0;
+}
+
+int ssi_b200_grad_fold_workspace_bytes(int64_t max_rows, int64_t D, size_t* bytes) {
+  SSI_CHECK_ARG(bytes && max_rows >= 1 && D >= 8, "bad argument");
+  *bytes = (2 * static_cast<size_t>(FOLD_SEG) + fold_sparse_floats(max_rows, D)) * sizeof(float);
+  return 0;
+}
+
+int ssi_b200_grad_fold_sqnorm(const void* fold_ws_ptr, size_t fold_ws_bytes, float* sqnorm_out, void* stream) {
+  SSI_CHECK_ARG(fold_ws_ptr && sqnorm_out, "null pointer argument");
+  FoldWs fw;
+  if (int r = fold_ws(const_cast<void*>(fold_ws_ptr), fold_ws_bytes, &fw)) return r;
+  SSI_CHECK_ARG(fw.floats < (size_t(1) << 31), "fold workspace too large");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ProfScope ps(CAT_AUX, st);
+  ssi::grad_fold_finalize_kernel<<<1, 256, 0, st>>>(fw.base, static_cast<int>(fw.floats), sqnorm_out);
+  SSI_LAUNCH_OK("grad_fold_finalize");
   return 0;
 }
 
@@ -1137,6 +1195,7 @@ int embedding_grad_scatter_impl(const void* dH, const int64_t* ids, int64_t N, i
   // no shared memory, <= 72 registers: co-resides with a persistent tensor-core CTA
   const int64_t warps_total = static_cast<int64_t>(s.nwarps) * s.slabs;
   const unsigned grid = static_cast<unsigned>(ceil_div(warps_total, ssi::SCAT_THREADS / 32));
+  if (out.fold.sq) SSI_CUDA(cudaMemsetAsync(out.fold.sq, 0, 2 * static_cast<size_t>(warps_total) * sizeof(float), st));
   ssi::scatter_reduce_kernel<MODE><<<grid, ssi::SCAT_THREADS, 0, st>>>(static_cast<const __nv_bfloat16*>(dH), k[cur],
                                                                       v[cur], urank, n, static_cast<uint32_t>(V),
                                                                       static_cast<int>(D), s.slabs, out, partial, info);
@@ -1181,6 +1240,19 @@ int ssi_b200_embedding_grad_scatter_sorted(const void* dH, int64_t N, int64_t V,
   SSI_CHECK_ARG(dW && (reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be a 16-byte aligned device pointer");
   return embedding_grad_scatter_impl<ssi::SCAT_DENSE_BF16>(dH, nullptr, N, V, D, dense_out(dW), ws, ws_bytes, stream,
                                                            2);
+}
+
+int ssi_b200_embedding_grad_scatter_sorted_fold(const void* dH, int64_t N, int64_t V, int64_t D, void* dW, void* ws,
+                                                size_t ws_bytes, const float* post_scale, void* fold_ws_ptr,
+                                                size_t fold_ws_bytes, void* stream) {
+  SSI_CHECK_ARG(dW && (reinterpret_cast<uintptr_t>(dW) & 15) == 0, "dW must be a 16-byte aligned device pointer");
+  FoldWs fw;
+  if (int r = fold_ws(fold_ws_ptr, fold_ws_bytes, &fw)) return r;
+  SSI_CHECK_ARG(!fw.base || fw.sparse_floats() >= fold_sparse_floats(N, D), "fold workspace too small for N=%lld",
+                (long long)N);
+  ssi::ScatOut o = dense_out(dW);
+  o.fold.post_scale = post_scale, o.fold.sq = fw.seg(2);
+  return embedding_grad_scatter_impl<ssi::SCAT_DENSE_BF16>(dH, nullptr, N, V, D, o, ws, ws_bytes, stream, 2);
 }
 
 int ssi_b200_embedding_grad_scatter_sorted_f32(const void* dH, int64_t N, int64_t V, int64_t D, float* dW_acc,
@@ -1285,6 +1357,14 @@ int ssi_b200_dp_counts(void* const* peer_bufs, int rank, int world, uint32_t epo
 int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,
                          uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW, int accumulate_dW,
                          void* host_flag, void* stream) {
+  return ssi_b200_dp_exchange_fold(peer_bufs, rank, world, V, D, max_rows, epoch, grad_out, grad_hint, dW,
+                                   accumulate_dW, host_flag, nullptr, nullptr, 0, stream);
+}
+
+int ssi_b200_dp_exchange_fold(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,
+                              uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW,
+                              int accumulate_dW, void* host_flag, const float* post_scale, void* fold_ws_ptr,
+                              size_t fold_ws_bytes, void* stream) {
   SSI_CHECK_ARG(grad_out && grad_hint && dW, "null pointer argument");
   ssi::DpPeers peers;
   if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
@@ -1293,21 +1373,27 @@ int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V,
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  FoldWs fw;
+  if (int r = fold_ws(fold_ws_ptr, fold_ws_bytes, &fw)) return r;
+  if (fw.base) SSI_CUDA(cudaMemsetAsync(fw.base, 0, fw.floats * sizeof(float), st));  // a fold begins here
+  ssi::GradFold f_own, f_others;
+  f_own.post_scale = post_scale, f_own.sq = fw.seg(0);
+  f_others.post_scale = nullptr, f_others.sq = fw.seg(1);
   const ssi::DpLayout lay = ssi::dp_layout(V, D, world, max_rows);
   const long long total_f4 = static_cast<long long>(V) * D / 4;
   const long long slice_f4 = static_cast<long long>(ceil_div(V, world)) * D / 4;
-  const int grid = di->sms * 2;
+  const int grid = di->sms * 2 < FOLD_SEG ? di->sms * 2 : FOLD_SEG;
   uint2* out = static_cast<uint2*>(dW);
   unsigned int* hf = static_cast<unsigned int*>(host_flag);
   ProfScope ps(CAT_EXCHANGE, st);
 #define SSI_DP_CASE(W_)                                                                                               \
   case W_:                                                                                                            \
     ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, grad_out, \
-                                                                grad_hint, accumulate_dW ? 1 : 0, out, hf);           \
+                                                                grad_hint, accumulate_dW ? 1 : 0, out, hf, f_own);    \
     SSI_LAUNCH_OK("dp_reduce");                                                                                       \
     if (W_ > 1) {                                                                                                     \
       ssi::dp_gather_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, out,   \
-                                                                  hf);                                                \
+                                                                  hf, f_others);                                      \
       SSI_LAUNCH_OK("dp_gather");                                                                                     \
     }                                                                                                                 \
     break;
@@ -1330,6 +1416,15 @@ int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V,
 int ssi_b200_dp_embedding_exchange(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
                                    size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world, int64_t max_rows,
                                    uint32_t epoch, void* dW, void* host_flag, void* stream) {
+  return ssi_b200_dp_embedding_exchange_fold(dH, N, V, D, sort_ws, sort_ws_bytes, peer_bufs, rank, world, max_rows,
+                                             epoch, dW, host_flag, nullptr, nullptr, 0, stream);
+}
+
+int ssi_b200_dp_embedding_exchange_fold(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
+                                        size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world,
+                                        int64_t max_rows, uint32_t epoch, void* dW, void* host_flag,
+                                        const float* post_scale, void* fold_ws_ptr, size_t fold_ws_bytes,
+                                        void* stream) {
   SSI_CHECK_ARG(dH && sort_ws && dW, "null pointer argument");
   ssi::DpPeers peers;
   if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
@@ -1357,11 +1452,18 @@ int ssi_b200_dp_embedding_exchange(const void* dH, int64_t N, int64_t V, int64_t
   unsigned int* hf = static_cast<unsigned int*>(host_flag);
   const int grid = di->sms * 4;
   __nv_bfloat16* g = static_cast<__nv_bfloat16*>(dW);
+  FoldWs fw;
+  if (int r = fold_ws(fold_ws_ptr, fold_ws_bytes, &fw)) return r;
+  const size_t sparse_warps = static_cast<size_t>(grid) * (ssi::DP_THREADS / 32);
+  SSI_CHECK_ARG(!fw.base || fw.sparse_floats() >= sparse_warps, "fold workspace too small");
+  if (fw.base) SSI_CUDA(cudaMemsetAsync(fw.seg(2), 0, fw.sparse_floats() * sizeof(float), st));
+  ssi::GradFold gf;
+  gf.post_scale = post_scale, gf.sq = fw.seg(2);
   ProfScope ps(CAT_EXCHANGE, st);
 #define SSI_DP_CASE(W_)                                                                                        \
   case W_:                                                                                                     \
     ssi::dp_sparse_add_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),     \
-                                                                    static_cast<int>(D), epoch, g, hf);        \
+                                                                    static_cast<int>(D), epoch, g, hf, gf);    \
     break;
   switch (world) {
     SSI_DP_CASE(1)

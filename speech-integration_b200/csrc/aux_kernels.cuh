@@ -590,12 +590,42 @@ __global__ void __launch_bounds__(256) apply_dx_kernel(uint4* __restrict__ dX, s
   }
 }
 
-// dW = bf16((accumulate ? dW : 0) + ratio * acc): the fp32 accumulator over ALL tokens is rounded once.
+// Fold of the trainer's scale_grads + grad-norm passes into the kernels that write the tied gradient anyway
+// (tt/torchtune/training/_grad_scaler.py:25-31, ssi/trainer.py:404-408).  post_scale: the scaler of
+// scale_grads, applied in fp32 BEFORE the one rounding to bf16 (null = 1).  sq: where a kernel leaves its share of
+// sum(g^2) -- dense writers one partial per block (sum of the new values), sparse read-modify-write sites one
+// partial per warp (sum of new^2 - old^2); grad_fold_finalize_kernel adds everything up in double, in order.
+struct GradFold {
+  const float* post_scale;
+  float* sq;
+};
+__device__ __forceinline__ float fold_scale(const GradFold& f) { return f.post_scale ? *f.post_scale : 1.f; }
+__device__ __forceinline__ float sq_of_bf16x2(uint32_t w) {
+  const float a = __uint_as_float(w << 16), b = __uint_as_float(w & 0xFFFF0000u);
+  return fmaf(a, a, b * b);
+}
+// block sum of `v` -> sq[blockIdx.x] (256-thread blocks; s_w: 8 floats of shared memory)
+__device__ __forceinline__ void fold_block_partial(float v, float* sq, float* s_w) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = 0.f;
+    for (int w = 0; w < static_cast<int>(blockDim.x >> 5); ++w) a += s_w[w];
+    sq[blockIdx.x] = a;
+  }
+}
+
+// dW = bf16(post_scale * ((accumulate ? dW : 0) + ratio * acc)): the fp32 accumulator over ALL tokens is rounded once.
 __global__ void __launch_bounds__(256) apply_dw_kernel(const float4* __restrict__ acc, size_t n_f4,
                                                        const float* __restrict__ grad_out,
                                                        const float* __restrict__ grad_hint, int accumulate,
-                                                       uint2* __restrict__ dW) {
+                                                       uint2* __restrict__ dW, GradFold fold) {
+  __shared__ float s_w[8];
   const float ratio = grad_ratio(grad_out, grad_hint);
+  const float ps = fold_scale(fold);
+  float sq = 0.f;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n_f4;
        i += static_cast<size_t>(gridDim.x) * blockDim.x) {
     float4 a = acc[i];
@@ -604,11 +634,29 @@ __global__ void __launch_bounds__(256) apply_dw_kernel(const float4* __restrict_
       const uint2 old = dW[i];
       a.x += bf16lo(old.x), a.y += bf16hi(old.x), a.z += bf16lo(old.y), a.w += bf16hi(old.y);
     }
+    if (fold.post_scale) a.x *= ps, a.y *= ps, a.z *= ps, a.w *= ps;
     uint2 o;
     o.x = pack_bf16x2(a.x, a.y);
     o.y = pack_bf16x2(a.z, a.w);
     dW[i] = o;
+    if (fold.sq) sq += sq_of_bf16x2(o.x) + sq_of_bf16x2(o.y);
   }
+  if (fold.sq) fold_block_partial(sq, fold.sq, s_w);
+}
+
+// sum of the fold partials (fixed order, double) -> out[0]
+__global__ void __launch_bounds__(256) grad_fold_finalize_kernel(const float* __restrict__ partial, int n,
+                                                                 float* __restrict__ out) {
+  __shared__ double s[256];
+  double a = 0.0;
+  for (int i = threadIdx.x; i < n; i += 256) a += static_cast<double>(partial[i]);
+  s[threadIdx.x] = a;
+  __syncthreads();
+  for (int off = 128; off > 0; off >>= 1) {
+    if (threadIdx.x < off) s[threadIdx.x] += s[threadIdx.x + off];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = static_cast<float>(s[0] > 0.0 ? s[0] : 0.0);
 }
 
 // ---------------------------------------------------------------------------------------------------

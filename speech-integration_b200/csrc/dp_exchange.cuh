@@ -193,7 +193,9 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
                                                                long long slice_f4, long long total_f4,
                                                                unsigned int epoch, const float* __restrict__ grad_out,
                                                                const float* __restrict__ grad_hint, int accumulate,
-                                                               uint2* __restrict__ dW, unsigned int* host_flag) {
+                                                               uint2* __restrict__ dW, unsigned int* host_flag,
+                                                               GradFold fold) {
+  __shared__ float s_fold[DP_THREADS / 32];
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
   // ---- announce: everything this rank contributes (its dW_acc) was finished by earlier kernels of this stream
   if (blockIdx.x == 0 && threadIdx.x < WORLD && static_cast<int>(threadIdx.x) != rank) {
@@ -204,6 +206,8 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
   const bool bad = dp_is_bad(ctrl);  // a peer never arrived: NaN out, so that no optimizer step can use the result
 
   const float ratio = grad_ratio(grad_out, grad_hint);
+  const float ps = fold_scale(fold);
+  float sq = 0.f;
   const long long begin = static_cast<long long>(rank) * slice_f4;
   const long long end = min(begin + slice_f4, total_f4);
   const float4* src[WORLD];
@@ -235,14 +239,17 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
         const uint2 old = dW[i];
         a.x += bf16lo(old.x), a.y += bf16hi(old.x), a.z += bf16lo(old.y), a.w += bf16hi(old.y);
       }
+      if (fold.post_scale) a.x *= ps, a.y *= ps, a.z *= ps, a.w *= ps;
       uint2 o;
       o.x = pack_bf16x2(a.x, a.y);
       o.y = pack_bf16x2(a.z, a.w);
       if (bad) o.x = o.y = BF16X2_NAN;
       dW[i] = o;
       stage[i - begin] = o;
+      if (fold.sq) sq += sq_of_bf16x2(o.x) + sq_of_bf16x2(o.y);
     }
   }
+  if (fold.sq) fold_block_partial(sq, fold.sq, s_fold);  // this rank's own slice
   // ---- the last block to finish announces "slice reduced" to every peer
   __threadfence_system();
   __syncthreads();
@@ -262,10 +269,12 @@ template <int WORLD>
 __global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, DpLayout lay, int rank,
                                                                long long slice_f4, long long total_f4,
                                                                unsigned int epoch, uint2* __restrict__ dW,
-                                                               unsigned int* host_flag) {
+                                                               unsigned int* host_flag, GradFold fold) {
+  __shared__ float s_fold[DP_THREADS / 32];
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
   dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
   const bool bad = dp_is_bad(ctrl);
+  float sq = 0.f;
   // bf16 slices move as 16-byte words: 2 of the fp32-quad units per word (slice_f4 is even, see the host side)
   const long long slice_u4 = slice_f4 / 2, total_u4 = total_f4 / 2;
   const long long stride = static_cast<long long>(gridDim.x) * DP_THREADS;
@@ -285,9 +294,12 @@ __global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, Dp
         if (i0 + u * stride < n) {
           if (bad) v[u] = make_uint4(BF16X2_NAN, BF16X2_NAN, BF16X2_NAN, BF16X2_NAN);
           out[begin + i0 + u * stride] = v[u];
+          if (fold.sq)
+            sq += (sq_of_bf16x2(v[u].x) + sq_of_bf16x2(v[u].y)) + (sq_of_bf16x2(v[u].z) + sq_of_bf16x2(v[u].w));
         }
     }
   }
+  if (fold.sq) fold_block_partial(sq, fold.sq, s_fold);  // the other ranks' slices
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -304,7 +316,7 @@ constexpr int SPARSE_COLS = 32 * SPARSE_G * 8;   // 1024 columns per pass
 template <int WORLD>
 __global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers, DpLayout lay, int rank, int V, int D,
                                                                    unsigned int epoch, __nv_bfloat16* __restrict__ dW,
-                                                                   unsigned int* host_flag) {
+                                                                   unsigned int* host_flag, GradFold fold) {
   constexpr int WP2 = WORLD <= 1 ? 1 : WORLD <= 2 ? 2 : WORLD <= 4 ? 4 : 8;
   constexpr int PER = 32 / WP2;  // ids per warp iteration
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
@@ -322,6 +334,8 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers
   const int gw = (blockIdx.x * DP_THREADS + threadIdx.x) >> 5;
   const int nw = (gridDim.x * DP_THREADS) >> 5;
   const int sub = lane / WP2, pl = lane % WP2;
+  const float ps = fold_scale(fold);
+  float dsq = 0.f;
   const unsigned long long* slot_p =
       (pl < WORLD) ? reinterpret_cast<const unsigned long long*>(peers.buf[pl] + lay.off_slot) : nullptr;
   for (long long v0 = static_cast<long long>(gw) * PER; v0 < V; v0 += static_cast<long long>(nw) * PER) {
@@ -383,15 +397,24 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers
             uint4* ptr = reinterpret_cast<uint4*>(drow + d0 + col);
             const uint4 old = *ptr;
             uint4 o;
-            o.x = pack_bf16x2(bf16lo(old.x) + acc[g][0], bf16hi(old.x) + acc[g][1]);
-            o.y = pack_bf16x2(bf16lo(old.y) + acc[g][2], bf16hi(old.y) + acc[g][3]);
-            o.z = pack_bf16x2(bf16lo(old.z) + acc[g][4], bf16hi(old.z) + acc[g][5]);
-            o.w = pack_bf16x2(bf16lo(old.w) + acc[g][6], bf16hi(old.w) + acc[g][7]);
+            // ps = 1 without a fold: the plain sum
+            o.x = pack_bf16x2(fmaf(ps, acc[g][0], bf16lo(old.x)), fmaf(ps, acc[g][1], bf16hi(old.x)));
+            o.y = pack_bf16x2(fmaf(ps, acc[g][2], bf16lo(old.y)), fmaf(ps, acc[g][3], bf16hi(old.y)));
+            o.z = pack_bf16x2(fmaf(ps, acc[g][4], bf16lo(old.z)), fmaf(ps, acc[g][5], bf16hi(old.z)));
+            o.w = pack_bf16x2(fmaf(ps, acc[g][6], bf16lo(old.w)), fmaf(ps, acc[g][7], bf16hi(old.w)));
             *ptr = o;
+            if (fold.sq)
+              dsq += (sq_of_bf16x2(o.x) - sq_of_bf16x2(old.x)) + (sq_of_bf16x2(o.y) - sq_of_bf16x2(old.y)) +
+                     (sq_of_bf16x2(o.z) - sq_of_bf16x2(old.z)) + (sq_of_bf16x2(o.w) - sq_of_bf16x2(old.w));
           }
         }
       }
     }
+  }
+  if (fold.sq) {  // one partial per warp: sum(new^2 - old^2) over the rows it rewrote
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
+    if (lane == 0) fold.sq[gw] = dsq;
   }
 }
 

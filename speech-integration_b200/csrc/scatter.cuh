@@ -293,6 +293,10 @@ struct ScatOut {
   const float* scale_num;
   const long long* scale_den;
   float scale_sign;
+  // bf16 dense mode: scale_grads / grad-norm fold (aux_kernels.cuh GradFold): rows are multiplied by *post_scale
+  // before they are added; fold.sq[warp] (scatter_reduce) and fold.sq[warps + warp] (scatter_fixup) receive
+  // sum(new^2 - old^2) over the elements the warp rewrote
+  GradFold fold;
 };
 
 struct ScatInfo {
@@ -333,7 +337,7 @@ __device__ __forceinline__ float scat_scale(const ScatOut& o) {
 template <int MODE>
 __device__ __forceinline__ void emit_run(const ScatOut& o, uint32_t key, int ur, uint32_t V, int D, int col,
                                          bool active, bool first_slab_lane0, const float (&acc)[8],
-                                         const ScatOld& old, float sc) {
+                                         const ScatOld& old, float sc, float& dsq) {
   if (key >= V) return;  // sentinel run of the out-of-range ids
   if constexpr (MODE == SCAT_COMPACT) {
     if (ur < 0 || ur >= o.cap) return;
@@ -347,9 +351,12 @@ __device__ __forceinline__ void emit_run(const ScatOut& o, uint32_t key, int ur,
     float f[8];
     bf16x8_to_f32(old.a, f);
 #pragma unroll
-    for (int e = 0; e < 8; ++e) f[e] += acc[e];
-    *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(o.dense) + static_cast<size_t>(key) * D + col) =
-        f32x8_to_bf16(f);
+    for (int e = 0; e < 8; ++e) f[e] = fmaf(sc, acc[e], f[e]);  // sc = 1 without a fold: the plain sum
+    const uint4 nw = f32x8_to_bf16(f);
+    *reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(o.dense) + static_cast<size_t>(key) * D + col) = nw;
+    if (o.fold.sq)
+      dsq += (sq_of_bf16x2(nw.x) - sq_of_bf16x2(old.a.x)) + (sq_of_bf16x2(nw.y) - sq_of_bf16x2(old.a.y)) +
+             (sq_of_bf16x2(nw.z) - sq_of_bf16x2(old.a.z)) + (sq_of_bf16x2(nw.w) - sq_of_bf16x2(old.a.w));
   } else {
     if (!active) return;
     float4* ptr = reinterpret_cast<float4*>(static_cast<float*>(o.dense) + static_cast<size_t>(key) * D + col);
@@ -386,7 +393,8 @@ __global__ void __launch_bounds__(SCAT_THREADS) scatter_reduce_kernel(const __nv
   const int my_ur = in ? urank[p0 + lane] : -1;
   const uint32_t prev_key = (p0 > 0) ? skeys[p0 - 1] : KEY_NONE;
   const uint32_t next_key = (p0 + cnt < n) ? skeys[p0 + cnt] : KEY_NONE;
-  const float sc = (MODE == SCAT_DENSE_F32) ? scat_scale(out) : 1.f;
+  const float sc = (MODE == SCAT_DENSE_F32) ? scat_scale(out) : (MODE == SCAT_DENSE_BF16) ? fold_scale(out.fold) : 1.f;
+  float dsq = 0.f;
   ScatInfo inf;
   inf.slot0_key = KEY_NONE;
   inf.slot0_open_right = 0;
@@ -427,7 +435,7 @@ __global__ void __launch_bounds__(SCAT_THREADS) scatter_reduce_kernel(const __nv
     if (end_of_run) {
       const bool open_right = (i == cnt - 1) && (next_key == key);
       if (!open_left && !open_right) {
-        emit_run<MODE>(out, key, ur, V, D, col, active, lead, acc, old, sc);
+        emit_run<MODE>(out, key, ur, V, D, col, active, lead, acc, old, sc, dsq);
       } else {
         const int slot = open_left ? 0 : 1;
         if (active) {
@@ -449,6 +457,13 @@ __global__ void __launch_bounds__(SCAT_THREADS) scatter_reduce_kernel(const __nv
     }
   }
   if (lead) info[wg] = inf;
+  if constexpr (MODE == SCAT_DENSE_BF16) {
+    if (out.fold.sq) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
+      if (lane == 0) out.fold.sq[wid] = dsq;
+    }
+  }
 }
 
 // One warp per range (and column slab) whose last run continues into the next range(s): sum the chain of partials
@@ -468,7 +483,8 @@ __global__ void __launch_bounds__(SCAT_THREADS) scatter_fixup_kernel(const float
   ScatOld old;
   old.a = old.b = make_uint4(0, 0, 0, 0);
   fetch_old<MODE>(out, key, V, D, col, active, old);
-  const float sc = (MODE == SCAT_DENSE_F32) ? scat_scale(out) : 1.f;
+  const float sc = (MODE == SCAT_DENSE_F32) ? scat_scale(out) : (MODE == SCAT_DENSE_BF16) ? fold_scale(out.fold) : 1.f;
+  float dsq = 0.f;
   float acc[8];
   auto add_partial = [&](const float* pr, bool first) {
     float4 a = make_float4(0, 0, 0, 0), b = a;
@@ -498,7 +514,14 @@ __global__ void __launch_bounds__(SCAT_THREADS) scatter_fixup_kernel(const float
     for (int j = 0; j < n_inc; ++j) add_partial(partial + (static_cast<size_t>(base + j) * 2) * D, false);
     if (f < 32) break;
   }
-  emit_run<MODE>(out, key, info[wg].slot1_urank, V, D, col, active, slab == 0 && lane == 0, acc, old, sc);
+  emit_run<MODE>(out, key, info[wg].slot1_urank, V, D, col, active, slab == 0 && lane == 0, acc, old, sc, dsq);
+  if constexpr (MODE == SCAT_DENSE_BF16) {
+    if (out.fold.sq) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
+      if (lane == 0) out.fold.sq[static_cast<size_t>(nwarps) * slabs + wid] = dsq;
+    }
+  }
 }
 
 }  // namespace ssi

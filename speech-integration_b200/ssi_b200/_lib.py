@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 110
+ABI_VERSION = 111
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -114,6 +114,27 @@ SYMBOLS = {
     ),
     "ssi_b200_grad_scale_sqnorm_workspace_bytes": (c_int, [POINTER(c_size_t)]),
     "ssi_b200_grad_scale_sqnorm": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ssi_b200_grad_fold_workspace_bytes": (c_int, [c_int64, c_int64, POINTER(c_size_t)]),
+    "ssi_b200_grad_fold_sqnorm": (c_int, [c_void_p, c_size_t, c_void_p, c_void_p]),
+    "ssi_b200_lmhead_ce_apply_grad_fold": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_void_p, c_void_p,
+         c_size_t, c_void_p],
+    ),
+    "ssi_b200_embedding_grad_scatter_sorted_fold": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p, c_size_t, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_dp_exchange_fold": (
+        c_int,
+        [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p,
+         c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_dp_embedding_exchange_fold": (
+        c_int,
+        [c_void_p, c_int64, c_int64, c_int64, c_void_p, c_size_t, POINTER(c_void_p), c_int, c_int, c_int64,
+         ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
     "ssi_b200_embedding_gather": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_void_p]),
     "ssi_b200_profile_begin": (c_int, []),
     "ssi_b200_profile_end": (c_int, [c_void_p, c_void_p]),

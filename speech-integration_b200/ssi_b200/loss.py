@@ -136,7 +136,7 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
                 ctx.dscale, ctx.scale_dtype = out[5], norm_scale.dtype
             ctx.hint, ctx.dX, ctx.dW_acc, ctx.w_ptr = hint, dX, dW_acc, W.data_ptr()
             if ctx.sync is not None:
-                ctx.sync.after_forward(hint, announced)
+                ctx.sync.after_forward(hint, announced, X.size(0))
         else:
             if norm_scale is not None:  # forward only (eval): the stand-alone norm kernel, then K1
                 X = ops.rmsnorm_fwd(X, norm_scale.detach(), norm_eps, want_rstd=False)[0]
@@ -180,7 +180,10 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
             acc = wparam.grad is not None
             if not acc:
                 wparam.grad = torch.empty_like(wparam)
-            ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc)
+            fold = getattr(holder, "fold", None)
+            ps, fws = fold.dense_args(hint, dX.size(0)) if fold is not None else (None, None)
+            ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, dW=wparam.grad, accumulate_dW=acc, post_scale=ps,
+                                     fold_ws=fws)
             return (dX, None) + nones + (dscale, None, None)
         _, dW = ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint)
         return (dX, dW) + nones + (dscale, None, None)
@@ -320,6 +323,7 @@ class FusedLinearCrossEntropyLoss(nn.Module):
         self.last_n_valid: torch.Tensor | None = None
         self.last_global_counts: torch.Tensor | None = None
         object.__setattr__(self, "sync", None)  # ssi_b200.sync.TiedGradSync (data parallelism); not a submodule
+        object.__setattr__(self, "fold", None)  # ssi_b200.fold.TiedGradFold (install(fold_scale_grads=True))
         self.local_counts: torch.Tensor | None = None
         self.hint_is_global_count: bool = False
         object.__setattr__(self, "_norm", None)  # fused final RMSNorm (set_fused_norm); not a registered submodule

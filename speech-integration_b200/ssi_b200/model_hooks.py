@@ -63,7 +63,9 @@ class _EmbeddingFn(torch.autograd.Function):
             return None, None, None
         if w.grad is None:
             w.grad = torch.zeros_like(w)
-        ops.embedding_grad_scatter_sorted(dH, sort_ws, w.grad)
+        fold = getattr(module, "fold", None)
+        ps, fws = fold.sparse_args(dH.size(0)) if fold is not None else (None, None)
+        ops.embedding_grad_scatter_sorted(dH, sort_ws, w.grad, post_scale=ps, fold_ws=fws)
         return None, None, None
 
 
@@ -72,6 +74,7 @@ class TiedEmbeddingB200(nn.Embedding):
     sorted-id segmented scatter-add backward.  bf16 CUDA weights only (anything else is ``nn.Embedding``'s job)."""
 
     sync = None  # ssi_b200.sync.TiedGradSync when install() was given a process group
+    fold = None  # ssi_b200.fold.TiedGradFold when install(fold_scale_grads=True)
 
     def forward(self, tokens: torch.Tensor) -> torch.Tensor:
         w = self.weight
@@ -154,7 +157,8 @@ class FusedNormPassthrough(nn.Module):
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
             replace_embedding: bool = True, mode: str | None = None,
             replace_norm: bool = False, fuse_norm: bool = False, process_group=None,
-            exchange: str | None = None, max_tokens_per_rank: int = 65536) -> FusedLinearCrossEntropyLoss:
+            exchange: str | None = None, max_tokens_per_rank: int = 65536,
+            fold_scale_grads: bool = False) -> FusedLinearCrossEntropyLoss:
     """Mirror of ``Trainer._setup_loss`` (ssi/trainer.py:299-304) for the fused path.
 
     Replaces ``model.output`` by a hidden passthrough, optionally swaps ``model.tok_embeddings`` for
@@ -170,7 +174,11 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     a training step produces its parts (:mod:`ssi_b200.sync`; semantics of tt/recipes/full_finetune_distributed.py:
     844-851: losses are this rank's share of the global mean, gradients those of the global mean).  ``exchange``:
     ``"peer"`` (default: the library's own NVLink peer-memory kernels) or ``"nccl"`` (bf16 all-reduce baseline);
-    ``max_tokens_per_rank`` sizes the compact-row area of the peer exchange (most token rows of one micro-batch)."""
+    ``max_tokens_per_rank`` sizes the compact-row area of the peer exchange (most token rows of one micro-batch).
+
+    ``fold_scale_grads``: give the loss a :class:`ssi_b200.fold.TiedGradFold` (``loss_fn.fold``): the trainer's
+    ``scale_grads`` and the tied weight's share of ``clip_grad_norm_`` (ssi/trainer.py:404-408) ride along in the kernels
+    that write the tied gradient anyway (single-pass mode; with a process group: the peer exchange)."""
     norm = getattr(model, "norm", None)
     fused_norm = None
     if fuse_norm:
@@ -206,4 +214,20 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
         sync = TiedGradSync(emb.weight, process_group, exchange=exchange, max_rows=max_tokens_per_rank)
         object.__setattr__(loss_fn, "sync", sync)
         object.__setattr__(emb, "sync", sync)
+    if fold_scale_grads:
+        if loss_fn.mode != "single_pass" or not isinstance(emb, TiedEmbeddingB200):
+            raise ValueError("ssi_b200.install(fold_scale_grads=True): needs mode='single_pass' and "
+                             "replace_embedding=True (the fold lives in apply_dw / the peer reduce and in the "
+                             "embedding backward)")
+        sync = getattr(loss_fn, "sync", None)
+        if sync is not None and sync.peer is None:
+            raise ValueError("ssi_b200.install(fold_scale_grads=True): exchange='nccl' all-reduces bf16 gradients "
+                             "after the step; there is no kernel of the library left to fold into")
+        from .fold import TiedGradFold
+
+        fold = TiedGradFold(emb.weight)
+        object.__setattr__(loss_fn, "fold", fold)
+        object.__setattr__(emb, "fold", fold)
+        if sync is not None:
+            sync.fold = fold
     return loss_fn

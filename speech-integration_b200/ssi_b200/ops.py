@@ -4,6 +4,8 @@ PyTorch is used only for device memory and streams; all arithmetic happens in li
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 
 from . import _lib
@@ -187,11 +189,43 @@ def lmhead_ce_fwd_grad(X: torch.Tensor, W: torch.Tensor, labels: torch.Tensor, g
     return loss_out, lse, n_valid, dX, dW_acc
 
 
+def _fold_args(post_scale: torch.Tensor | None, fold_ws: torch.Tensor | None, dev: torch.device):
+    """(post_scale ptr, fold_ws ptr, fold_ws bytes) of the ``_fold`` entry points (include/ssi_b200.h)."""
+    if post_scale is not None and (post_scale.dtype != torch.float32 or post_scale.numel() != 1
+                                   or post_scale.device != dev):
+        raise ValueError("ssi_b200: post_scale must be a single fp32 value on the device")
+    if fold_ws is not None and (fold_ws.dtype != torch.uint8 or fold_ws.device != dev or not fold_ws.is_contiguous()):
+        raise ValueError("ssi_b200: fold_ws must be a contiguous uint8 tensor on the device (grad_fold_workspace)")
+    return (post_scale.data_ptr() if post_scale is not None else None,
+            fold_ws.data_ptr() if fold_ws is not None else None, fold_ws.numel() if fold_ws is not None else 0)
+
+
+def grad_fold_workspace(max_rows: int, D: int, device: torch.device) -> torch.Tensor:
+    """Scratch of the scale_grads / grad-norm fold for micro-batches of at most ``max_rows`` token rows."""
+    b = ctypes.c_size_t(0)
+    _lib.check(_lib.load().ssi_b200_grad_fold_workspace_bytes(int(max_rows), int(D), ctypes.byref(b)),
+               "grad_fold_workspace_bytes")
+    return torch.zeros(b.value, dtype=torch.uint8, device=device)
+
+
+def grad_fold_sqnorm(fold_ws: torch.Tensor) -> torch.Tensor:
+    """fp32 ``[1]``: sum of squares of the whole tied gradient, from the partials the dense and the sparse site of
+    this step left in ``fold_ws`` (no pass over the gradient)."""
+    dev = _require_cuda(fold_ws)
+    out = torch.empty(1, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.load().ssi_b200_grad_fold_sqnorm(fold_ws.data_ptr(), fold_ws.numel(), out.data_ptr(), _stream(dev))
+    _lib.check(rc, "grad_fold_sqnorm")
+    return out
+
+
 def lmhead_ce_apply_grad(dX: torch.Tensor, dW_acc: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
-                         dW: torch.Tensor | None = None, accumulate_dW: bool = False, skip_dW: bool = False):
+                         dW: torch.Tensor | None = None, accumulate_dW: bool = False, skip_dW: bool = False,
+                         post_scale: torch.Tensor | None = None, fold_ws: torch.Tensor | None = None):
     """Backward of single-pass mode: ``dX *= grad_out / grad_hint`` in place (a no-op on the device when the
-    ratio is 1) and ``dW = bf16((accumulate ? dW : 0) + ratio * dW_acc)``. Returns ``(dX, dW)``.
-    ``skip_dW``: only rescale dX (data-parallel mode: the peer exchange rounds the SUMMED dW instead)."""
+    ratio is 1) and ``dW = bf16(post_scale * ((accumulate ? dW : 0) + ratio * dW_acc))``. Returns ``(dX, dW)``.
+    ``skip_dW``: only rescale dX (data-parallel mode: the peer exchange rounds the SUMMED dW instead).
+    ``post_scale`` / ``fold_ws``: the scale_grads / grad-norm fold (``ssi_b200_lmhead_ce_apply_grad_fold``)."""
     dev = _require_cuda(dX, dW_acc, grad_out, grad_hint)
     N, D = dX.shape
     V = dW_acc.size(0)
@@ -208,10 +242,11 @@ def lmhead_ce_apply_grad(dX: torch.Tensor, dW_acc: torch.Tensor, grad_out: torch
     elif tuple(dW.shape) != (V, D) or dW.dtype != torch.bfloat16 or not dW.is_contiguous() or dW.device != dev:
         raise ValueError("ssi_b200: dW must be a contiguous bf16 [V, D] tensor on the same device")
     lib = _lib.load()
+    ps, fw, fwb = _fold_args(post_scale, fold_ws, dev)
     with torch.cuda.device(dev):
-        rc = lib.ssi_b200_lmhead_ce_apply_grad(dX.data_ptr(), dW_acc.data_ptr(), grad_out.data_ptr(),
-                                               grad_hint.data_ptr(), N, V, D, dW.data_ptr(),
-                                               1 if accumulate_dW else 0, _stream(dev))
+        rc = lib.ssi_b200_lmhead_ce_apply_grad_fold(dX.data_ptr(), dW_acc.data_ptr(), grad_out.data_ptr(),
+                                                    grad_hint.data_ptr(), N, V, D, dW.data_ptr(),
+                                                    1 if accumulate_dW else 0, ps, fw, fwb, _stream(dev))
     _lib.check(rc, "lmhead_ce_apply_grad")
     return dX, dW
 
@@ -302,9 +337,11 @@ def embedding_grad_scatter_sorted_f32(dH: torch.Tensor, ws: torch.Tensor, dW_acc
     return dW_acc
 
 
-def embedding_grad_scatter_sorted(dH: torch.Tensor, ws: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
-    """``dW[id] += sum of the dH rows with that id`` (bf16 ``[V, D]``, the tied weight's ``.grad``) in the order
-    :func:`embedding_grad_sort` left in ``ws``."""
+def embedding_grad_scatter_sorted(dH: torch.Tensor, ws: torch.Tensor, dW: torch.Tensor,
+                                  post_scale: torch.Tensor | None = None,
+                                  fold_ws: torch.Tensor | None = None) -> torch.Tensor:
+    """``dW[id] += post_scale * sum of the dH rows with that id`` (bf16 ``[V, D]``, the tied weight's ``.grad``) in the
+    order :func:`embedding_grad_sort` left in ``ws``; ``post_scale`` / ``fold_ws``: the scale_grads / grad-norm fold."""
     dev = _require_cuda(dH, ws, dW)
     if dH.dtype != torch.bfloat16 or dW.dtype != torch.bfloat16 or dH.dim() != 2 or dW.dim() != 2:
         raise TypeError("ssi_b200: expected bf16 dH [N, D] and bf16 dW [V, D]")
@@ -312,9 +349,11 @@ def embedding_grad_scatter_sorted(dH: torch.Tensor, ws: torch.Tensor, dW: torch.
         raise ValueError("ssi_b200: dH and dW must be contiguous with the same row length")
     N, D = dH.shape
     V = dW.size(0)
+    ps, fw, fwb = _fold_args(post_scale, fold_ws, dev)
     with torch.cuda.device(dev):
-        rc = _lib.load().ssi_b200_embedding_grad_scatter_sorted(dH.data_ptr(), N, V, D, dW.data_ptr(), ws.data_ptr(),
-                                                                ws.numel(), _stream(dev))
+        rc = _lib.load().ssi_b200_embedding_grad_scatter_sorted_fold(dH.data_ptr(), N, V, D, dW.data_ptr(),
+                                                                     ws.data_ptr(), ws.numel(), ps, fw, fwb,
+                                                                     _stream(dev))
     _lib.check(rc, "embedding_grad_scatter_sorted")
     return dW
 

@@ -26,7 +26,7 @@ import ctypes
 import torch
 import torch.distributed as dist
 
-from . import _lib
+from . import _lib, ops
 
 MAX_WORLD = 8
 
@@ -144,20 +144,26 @@ class TiedGradExchange:
         return out, hint
 
     def exchange(self, dW: torch.Tensor, grad_out: torch.Tensor, grad_hint: torch.Tensor,
-                 accumulate: bool = False) -> torch.Tensor:
-        """Enqueue on the current stream: ``dW = bf16((accumulate ? dW : 0) + grad_out / grad_hint * sum_ranks
-        dw_acc)`` on every rank.  Every rank must call it the same number of times."""
+                 accumulate: bool = False, post_scale: torch.Tensor | None = None,
+                 fold_ws: torch.Tensor | None = None) -> torch.Tensor:
+        """Enqueue on the current stream: ``dW = bf16(post_scale * ((accumulate ? dW : 0) + grad_out / grad_hint *
+        sum_ranks dw_acc))`` on every rank.  Every rank must call it the same number of times.  ``post_scale`` /
+        ``fold_ws``: the scale_grads / grad-norm fold (``ssi_b200_dp_exchange_fold``)."""
         self._check_dw(dW)
         self.epoch_dense += 1
+        ps, fw, fwb = ops._fold_args(post_scale, fold_ws, self.device)
         with torch.cuda.device(self.device):
-            rc = _lib.load().ssi_b200_dp_exchange(self._ptr_array, self.rank, self.world, self.V, self.D,
-                                                  self.max_rows, self.epoch_dense & 0xFFFFFFFF, grad_out.data_ptr(),
-                                                  grad_hint.data_ptr(), dW.data_ptr(), 1 if accumulate else 0,
-                                                  self._host_flag.data_ptr(), self._stream())
+            rc = _lib.load().ssi_b200_dp_exchange_fold(self._ptr_array, self.rank, self.world, self.V, self.D,
+                                                       self.max_rows, self.epoch_dense & 0xFFFFFFFF,
+                                                       grad_out.data_ptr(), grad_hint.data_ptr(), dW.data_ptr(),
+                                                       1 if accumulate else 0, self._host_flag.data_ptr(), ps, fw, fwb,
+                                                       self._stream())
         _lib.check(rc, "dp_exchange")
         return dW
 
-    def embedding_exchange(self, dH: torch.Tensor, sort_ws: torch.Tensor, dW: torch.Tensor) -> torch.Tensor:
+    def embedding_exchange(self, dH: torch.Tensor, sort_ws: torch.Tensor, dW: torch.Tensor,
+                           post_scale: torch.Tensor | None = None,
+                           fold_ws: torch.Tensor | None = None) -> torch.Tensor:
         """Enqueue on the current stream: ``dW[id] += sum over ranks (rank order) of that rank's dH rows with this
         id`` on every rank; ``sort_ws`` from :func:`ssi_b200.ops.embedding_grad_sort` of this rank's ids.  Must be
         stream-ordered after this step's :meth:`exchange`."""
@@ -168,11 +174,12 @@ class TiedGradExchange:
             raise RuntimeError(f"ssi_b200.peer: {dH.size(0)} token rows exceed max_rows={self.max_rows} of the "
                                "exchange buffer; pass a larger max_rows (install(..., max_tokens_per_rank=...))")
         self.epoch_sparse += 1
+        ps, fw, fwb = ops._fold_args(post_scale, fold_ws, self.device)
         with torch.cuda.device(self.device):
-            rc = _lib.load().ssi_b200_dp_embedding_exchange(
+            rc = _lib.load().ssi_b200_dp_embedding_exchange_fold(
                 dH.data_ptr(), dH.size(0), self.V, self.D, sort_ws.data_ptr(), sort_ws.numel(), self._ptr_array,
                 self.rank, self.world, self.max_rows, self.epoch_sparse & 0xFFFFFFFF, dW.data_ptr(),
-                self._host_flag.data_ptr(), self._stream())
+                self._host_flag.data_ptr(), ps, fw, fwb, self._stream())
         _lib.check(rc, "dp_embedding_exchange")
         return dW
 

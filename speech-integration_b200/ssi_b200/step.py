@@ -37,11 +37,13 @@ class _PathModel(nn.Module):
 class PathStep:
     """``exchange``: how the tied gradient is summed over ranks when a process group is given — ``"peer"`` (default
     for single-pass mode: the library's own NVLink peer-memory kernels) or ``"nccl"`` (bf16 ``all_reduce`` of the
-    micro-batch's contribution after the embedding backward).  Environment override: ``SSI_B200_EXCHANGE``."""
+    micro-batch's contribution after the embedding backward).  Environment override: ``SSI_B200_EXCHANGE``.
+    ``fold_scale_grads``: every call is one optimizer step; ``weight.grad`` then holds the gradient ALREADY scaled by
+    ``1 / num_tokens_step`` (ssi/trainer.py:404) and ``self.fold.sqnorm()`` its sum of squares (:mod:`ssi_b200.fold`)."""
 
     def __init__(self, weight: nn.Parameter | torch.Tensor, ignore_index: int = -100, num_output_chunks: int = 8,
                  process_group=None, mode: str | None = None, exchange: str | None = None,
-                 max_tokens_per_rank: int = 65536):
+                 max_tokens_per_rank: int = 65536, fold_scale_grads: bool = False):
         if not isinstance(weight, nn.Parameter):
             weight = nn.Parameter(weight)
         self.model = _PathModel(weight)
@@ -52,7 +54,12 @@ class PathStep:
             self.world = dist.get_world_size(process_group)
         use_pg = process_group if (process_group is not None and (self.world > 1 or exchange == "peer")) else None
         self.loss_fn = install(self.model, num_output_chunks, ignore_index, mode=mode, process_group=use_pg,
-                               exchange=exchange, max_tokens_per_rank=max_tokens_per_rank)
+                               exchange=exchange, max_tokens_per_rank=max_tokens_per_rank,
+                               fold_scale_grads=fold_scale_grads)
+        # one micro-batch per optimizer step: scale_grads(model, 1 / num_tokens_step) (ssi/trainer.py:404) is the
+        # reciprocal of the announced multiplier and rides in the kernels that write the tied gradient
+        self.fold = self.loss_fn.fold
+        self.fold_every_step = self.fold is not None  # False: the caller arms the fold itself (accumulation windows)
         self.emb = self.model.tok_embeddings
         self.sync = self.loss_fn.sync
         self.exchange = self.sync.mode if self.sync is not None else None
@@ -83,6 +90,8 @@ class PathStep:
         loss_fn = self.loss_fn
         if self.sync is not None:
             self.sync.check()
+        if self.fold_every_step:
+            self.fold.arm()  # post_scale = 1 / num_tokens_iter (global with a process group)
         h0 = self.emb(tokens)                                   # transformer.py:628
         shifted, counts = ops.label_shift_count(labels, self.ignore_index)
         hidden = hidden.detach().requires_grad_(True)

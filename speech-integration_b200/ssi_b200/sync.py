@@ -71,6 +71,8 @@ class TiedGradSync:
         self._target = None           # nccl mode: where this micro-batch's LM-head gradient went
         self._dense_done = False      # peer mode: this micro-batch's dense exchange is enqueued
         self.grad_hint_mismatch: torch.Tensor | None = None
+        self.fold = None              # ssi_b200.fold.TiedGradFold (install(fold_scale_grads=True)), peer mode only
+        self._rows = 0                # token rows of the running micro-batch (sizes the fold scratch)
 
     # --------------------------------------------------------------------------------------------------- counts
     @property
@@ -109,19 +111,23 @@ class TiedGradSync:
         else:
             self.side.wait_stream(main)
         with torch.cuda.stream(self.side):
-            self.peer.exchange(self.weight.grad, grad_out, hint, accumulate=accumulate)
+            # the scale_grads / grad-norm fold rides in the reduce (the side stream is ordered after `hint`)
+            ps, fws = self.fold.dense_args(hint, self._rows) if self.fold is not None else (None, None)
+            self.peer.exchange(self.weight.grad, grad_out, hint, accumulate=accumulate, post_scale=ps, fold_ws=fws)
         self._dense_done = True
 
-    def after_forward(self, hint: torch.Tensor, announced: bool) -> None:
+    def after_forward(self, hint: torch.Tensor, announced: bool, n_rows: int = 0) -> None:
         """Called right after the single-pass forward was enqueued (it recorded ``dw_ready`` behind its last dW
         contraction).  With an announced multiplier the dense exchange starts now, behind the last dX contraction."""
         self._dense_done = False
+        self._rows = n_rows
         if self.peer is not None and announced:
             self._dense(hint, hint, self.dw_ready)
 
     def in_backward(self, dX: torch.Tensor, dW_acc: torch.Tensor, g: torch.Tensor, hint: torch.Tensor) -> None:
         """Backward of the loss: dX is rescaled in place; the LM-head gradient goes to the exchange."""
         if self.peer is not None:
+            self._rows = max(self._rows, dX.size(0))
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
             if self._dense_done:
                 # the exchange already ran with the announced multiplier: leave a wrong announcement visible
@@ -159,7 +165,8 @@ class TiedGradSync:
                 main.wait_stream(self.side)  # the dense exchange wrote .grad; peers are done with last step's rows
             if self.weight.grad is None:
                 self.weight.grad = torch.zeros_like(self.weight)
-            self.peer.embedding_exchange(dH, sort_ws, self.weight.grad)
+            ps, fws = self.fold.sparse_args(dH.size(0)) if self.fold is not None else (None, None)
+            self.peer.embedding_exchange(dH, sort_ws, self.weight.grad, post_scale=ps, fold_ws=fws)
             self._dense_done = False
             return
         target = self._target
