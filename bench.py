@@ -57,6 +57,7 @@ def parse_args():
     ap.add_argument("--no-fwd-only", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="N > 1: skip rank 0's N = 1 re-run of the global batch")
+    ap.add_argument("--no-fold", action="store_true", help="skip the scale_grads / grad-norm fold block (SURVEY 8f-3)")
     return ap.parse_args()
 
 
@@ -230,6 +231,10 @@ def gpu_reference_tokens_per_s(W, tokens, labels, X, dH0, iters: int = 3):
     return rows / (statistics.median(times) * 1e-3), times
 
 
+def exchange_is_foldable(path) -> bool:
+    return path.sync is None or path.sync.peer is not None
+
+
 def workload_name(cfg) -> str:
     return (f"{cfg.name}: {cfg.desc}; V={cfg.vocab}, D=2048, global batch {cfg.batch}x{cfg.seq} "
             f"= {cfg.rows} token rows, bf16 in / fp32 accumulate")
@@ -378,6 +383,49 @@ def run_ours(args):
                     "algorithmic_tflops_per_gpu": 2.0 * n_valid_local * V * D / (ms_f * 1e-3) / 1e12,
                     "loss_rank0": float(lf.item())}
 
+    # ---- scale_grads + the tied weight's grad norm folded into the step, against the step followed by
+    # the library's stand-alone one-pass kernel (the reference runs two passes, ssi/trainer.py:404-408)
+    fold_blk = None
+    if not args.no_fold and mode == "single_pass" and exchange_is_foldable(path):
+        from ssi_b200 import ops as _ops
+
+        kf = max(3, min(args.steps, 5))
+        scaler = torch.full((1,), 1.0 / max(n_valid_global, 1), device=dev)
+
+        def timed(fn):
+            fn()
+            barrier()
+            e0.record()
+            for _ in range(kf):
+                fn()
+            e1.record()
+            barrier()
+            tt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return tt.item() / kf
+
+        def two_pass():
+            step()
+            return _ops.grad_scale_sqnorm(path.weight.grad, scaler)
+
+        ms_two = timed(two_pass)
+        sq_two = float(two_pass().item())
+        path.set_fold(True)
+
+        def folded():
+            step()
+            return path.fold.sqnorm()
+
+        ms_fold = timed(folded)
+        sq_fold = float(folded().item())
+        path.set_fold(False)
+        fold_blk = {"ms_per_step_folded": ms_fold, "ms_per_step_plus_standalone_pass": ms_two,
+                    "saved_ms_per_step": ms_two - ms_fold, "grad_sqnorm_folded": sq_fold,
+                    "grad_sqnorm_standalone": sq_two, "sqnorm_rel_diff": abs(sq_fold - sq_two) / max(sq_two, 1e-30),
+                    "steps": kf, "what": "step + scale_grads(1/num_tokens) + sum(g^2) of the tied weight: folded "
+                    "into apply_dw / peer reduce + embedding backward vs one extra pass over the [V, D] gradient"}
+
     # ---- end to end through the public API with pinned host inputs
     e2e = None
     if not args.no_e2e:
@@ -495,7 +543,7 @@ def run_ours(args):
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
         "step_algorithmic_tflops_per_gpu": step_tflops,
         "step_frac_of_bf16_peak": {"burst": step_tflops / peaks["bf16_tflops"], "sustained": step_tflops / peak},
-        "kernels": kern, "fwd_only": fwd_only, "parity": parity, "k3_roofline": k3,
+        "kernels": kern, "fwd_only": fwd_only, "parity": parity, "k3_roofline": k3, "scale_grads_fold": fold_blk,
     }
     if per_rank_ms is not None:
         line["per_rank_kernel_ms_per_step"] = per_rank_ms

@@ -2,7 +2,7 @@
 set -x
 python -m pytest tests -m gpu -x -q > gpurun_out/r02_pytest_gpu.log 2>&1; tail -3 gpurun_out/r02_pytest_gpu.log
 python bench.py > gpurun_out/r02_bench_c5_n1.json 2> gpurun_out/r02_bench_c5_n1.err; tail -c 600 gpurun_out/r02_bench_c5_n1.json
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-fwd-only --no-gpu-reference --no-parity"
+CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-e2e --no-fwd-only --no-gpu-reference --no-parity --no-fold"
 $CMD > gpurun_out/plain_c5.log 2>&1 &&
 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/r02_launches_c5.csv $CMD > gpurun_out/ncu_launches_c5.log 2>&1
 ncu --set full --clock-control none --import-source on -k 'regex:gemm_kernel' -s 40 -c 6 -o gpurun_out/r02_prof_c5_gemm -f $CMD > gpurun_out/ncu_full_c5.log 2>&1

@@ -154,6 +154,28 @@ class FusedNormPassthrough(nn.Module):
         return x
 
 
+def attach_fold(loss_fn: FusedLinearCrossEntropyLoss, emb: nn.Module, enabled: bool = True):
+    """Give the loss and the tied embedding a shared :class:`ssi_b200.fold.TiedGradFold` (or take it away)."""
+    sync = getattr(loss_fn, "sync", None)
+    fold = None
+    if enabled:
+        if loss_fn.mode != "single_pass" or not isinstance(emb, TiedEmbeddingB200):
+            raise ValueError("ssi_b200.install(fold_scale_grads=True): needs mode='single_pass' and "
+                             "replace_embedding=True (the fold lives in apply_dw / the peer reduce and in the "
+                             "embedding backward)")
+        if sync is not None and sync.peer is None:
+            raise ValueError("ssi_b200.install(fold_scale_grads=True): exchange='nccl' all-reduces bf16 gradients "
+                             "after the step; there is no kernel of the library left to fold into")
+        from .fold import TiedGradFold
+
+        fold = TiedGradFold(emb.weight)
+    object.__setattr__(loss_fn, "fold", fold)
+    object.__setattr__(emb, "fold", fold)
+    if sync is not None:
+        sync.fold = fold
+    return fold
+
+
 def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -100,
             replace_embedding: bool = True, mode: str | None = None,
             replace_norm: bool = False, fuse_norm: bool = False, process_group=None,
@@ -215,19 +237,5 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
         object.__setattr__(loss_fn, "sync", sync)
         object.__setattr__(emb, "sync", sync)
     if fold_scale_grads:
-        if loss_fn.mode != "single_pass" or not isinstance(emb, TiedEmbeddingB200):
-            raise ValueError("ssi_b200.install(fold_scale_grads=True): needs mode='single_pass' and "
-                             "replace_embedding=True (the fold lives in apply_dw / the peer reduce and in the "
-                             "embedding backward)")
-        sync = getattr(loss_fn, "sync", None)
-        if sync is not None and sync.peer is None:
-            raise ValueError("ssi_b200.install(fold_scale_grads=True): exchange='nccl' all-reduces bf16 gradients "
-                             "after the step; there is no kernel of the library left to fold into")
-        from .fold import TiedGradFold
-
-        fold = TiedGradFold(emb.weight)
-        object.__setattr__(loss_fn, "fold", fold)
-        object.__setattr__(emb, "fold", fold)
-        if sync is not None:
-            sync.fold = fold
+        attach_fold(loss_fn, emb)
     return loss_fn

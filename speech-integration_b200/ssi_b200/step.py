@@ -66,6 +66,13 @@ class PathStep:
         self.ignore_index = ignore_index
         self.pg = process_group
 
+    def set_fold(self, enabled: bool) -> None:
+        """Switch the scale_grads / grad-norm fold on or off for the following steps."""
+        from .model_hooks import attach_fold
+
+        self.fold = attach_fold(self.loss_fn, self.emb, enabled)
+        self.fold_every_step = self.fold is not None
+
     @property
     def weight(self) -> nn.Parameter:
         return self.emb.weight

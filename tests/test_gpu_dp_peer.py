@@ -153,9 +153,18 @@ def _worker(rank, world, port, out):
             ev = step.forward_only(args[2], args[1])
             res[ex + "_eval"] = ev.item()
             step.close()
+        # scale_grads + grad norm folded into the peer reduce / gather and the sparse embedding exchange (8f-3)
+        step = PathStep(inp["W"].to(dev), process_group=pg, exchange="peer", fold_scale_grads=True)
+        for _ in range(2):
+            step.zero_grad()
+            step(*args)
+            fold_sq = step.fold.sqnorm()
+        torch.cuda.synchronize()
+        res["fold"] = (fold_sq.item(), None, step.weight.grad.cpu())
+        step.close()
         # every rank must hold the bit-identical summed gradient
         same = {}
-        for ex in ("peer", "nccl"):
+        for ex in ("peer", "nccl", "fold"):
             g = res[ex][2].cuda().view(torch.int16).to(torch.int32)
             lo, hi = g.clone(), g.clone()
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)
@@ -194,7 +203,7 @@ def _worker(rank, world, port, out):
             ref_loss, n_iter, ref_dH, ref_dW = oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"],
                                                                       inp["dH0"], inp["W"])
             want = ref_loss.item() * n_iter
-            out["same_on_all_ranks"] = same["peer"] and same["nccl"]
+            out["same_on_all_ranks"] = same["peer"] and same["nccl"] and same["fold"]
             out["loss_ok"] = (abs(res["peer"][0] - want) <= LOSS_RTOL * abs(want)
                               and abs(res["nccl"][0] - want) <= LOSS_RTOL * abs(want))
             lab_loc = inp["labels"][b0:b1]
@@ -208,6 +217,10 @@ def _worker(rank, world, port, out):
                 assert_grad_close(res["nccl_acc"], 2 * ref_dW, "dW nccl, two micro-batches accumulated",
                                   elem_roundings=DW_ELEM_ROUNDINGS)
                 assert_grad_close(res["peer"][1].reshape(ref_dH[b0:b1].shape), ref_dH[b0:b1], "dH")
+                assert_grad_close(res["fold"][2], ref_dW / n_iter, "dW peer, scale_grads folded",
+                                  elem_roundings=DW_ELEM_ROUNDINGS)
+                own_sq = res["fold"][2].double().pow(2).sum().item()
+                assert abs(res["fold"][0] - own_sq) <= 1e-5 * own_sq, ("folded sqnorm", res["fold"][0], own_sq)
                 t_loss, t_dW, t_mix = _oracle_tiny(tin, [slice(0, B), slice(B, 2 * B)])
                 for ex in ("peer", "nccl"):
                     assert abs(tiny[ex][0] - t_loss) <= 2e-3 * abs(t_loss), (ex, tiny[ex][0], t_loss)
