@@ -1,4 +1,5 @@
 set -x
+./tools/cluster_probe.bin | tee gpurun_out/r02_cluster_probe.json
 nvidia-smi -L
 python -m pytest tests -m gpu -x -q > gpurun_out/r02_pytest_gpu_2gpu.log 2>&1; tail -5 gpurun_out/r02_pytest_gpu_2gpu.log
 python -m pytest tests/test_gpu_dp_peer.py tests/test_gpu_fold.py -m gpu -q -rA 2>&1 | tail -25 > gpurun_out/r02_pytest_dp_peer_2gpu.log; cat gpurun_out/r02_pytest_dp_peer_2gpu.log
