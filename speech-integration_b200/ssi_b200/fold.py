@@ -46,14 +46,18 @@ class TiedGradFold:
     def disarm(self) -> None:
         self.armed = False
 
+    def ensure(self, n_rows: int) -> None:
+        """Size the scratch for micro-batches of ``n_rows`` token rows (call on the stream that owns allocations)."""
+        if self.armed and (self.ws is None or n_rows > self._rows):
+            self.ws = ops.grad_fold_workspace(n_rows, self.weight.size(1), self.device)
+            self._rows = n_rows
+
     def dense_args(self, hint: torch.Tensor, n_rows: int):
         """``(post_scale, fold_ws)`` for the dense site of an armed micro-batch, else ``(None, None)``.  Enqueues on
         the current stream (which must be ordered after ``hint``)."""
         if not self.armed:
             return None, None
-        if self.ws is None or n_rows > self._rows:
-            self.ws = ops.grad_fold_workspace(n_rows, self.weight.size(1), self.device)
-            self._rows = n_rows
+        self.ensure(n_rows)
         if self._from_hint:
             h = hint.reshape(1).to(torch.float32)
             self.post_scale.copy_(torch.where(h > 0, 1.0 / h, torch.zeros_like(h)))

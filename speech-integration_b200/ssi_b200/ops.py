@@ -205,7 +205,9 @@ def grad_fold_workspace(max_rows: int, D: int, device: torch.device) -> torch.Te
     b = ctypes.c_size_t(0)
     _lib.check(_lib.load().ssi_b200_grad_fold_workspace_bytes(int(max_rows), int(D), ctypes.byref(b)),
                "grad_fold_workspace_bytes")
-    return torch.zeros(b.value, dtype=torch.uint8, device=device)
+    # not initialised here: the dense site of every fold zeroes it on ITS stream (an init kernel on the allocating
+    # stream could land after a side stream's first partials)
+    return torch.empty(b.value, dtype=torch.uint8, device=device)
 
 
 def grad_fold_sqnorm(fold_ws: torch.Tensor) -> torch.Tensor:

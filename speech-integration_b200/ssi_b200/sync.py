@@ -106,6 +106,8 @@ class TiedGradSync:
     def _dense(self, grad_out: torch.Tensor, hint: torch.Tensor, after_event: torch.cuda.Event | None) -> None:
         main = torch.cuda.current_stream(self.device)
         accumulate = self._grad_buffer()
+        if self.fold is not None:
+            self.fold.ensure(self._rows)  # allocate on the main stream, use on the side stream
         if after_event is not None:
             self.side.wait_event(after_event)
         else:

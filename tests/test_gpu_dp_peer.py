@@ -220,7 +220,7 @@ def _worker(rank, world, port, out):
                 assert_grad_close(res["fold"][2], ref_dW / n_iter, "dW peer, scale_grads folded",
                                   elem_roundings=DW_ELEM_ROUNDINGS)
                 own_sq = res["fold"][2].double().pow(2).sum().item()
-                assert abs(res["fold"][0] - own_sq) <= 1e-5 * own_sq, ("folded sqnorm", res["fold"][0], own_sq)
+                assert abs(res["fold"][0] - own_sq) <= 5e-5 * own_sq, ("folded sqnorm", res["fold"][0], own_sq)
                 t_loss, t_dW, t_mix = _oracle_tiny(tin, [slice(0, B), slice(B, 2 * B)])
                 for ex in ("peer", "nccl"):
                     assert abs(tiny[ex][0] - t_loss) <= 2e-3 * abs(t_loss), (ex, tiny[ex][0], t_loss)
