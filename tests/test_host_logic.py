@@ -118,3 +118,54 @@ def test_install_fuse_norm_keeps_the_state_dict_and_hands_over_the_scale():
     assert m.norm(x) is x
     assert loss_fn._norm_args()[0] is scale and loss_fn._norm_args()[1] == 1e-6
     assert "scale" not in dict(loss_fn.named_parameters())  # the loss does not own it
+
+
+def test_grad_fold_protocol_on_the_host():
+    """State machine of ssi_b200.fold.TiedGradFold and the scale_grads mirror (no kernel runs: CPU tensors)."""
+    from ssi_b200 import fold as sfold
+
+    w = nn.Parameter(torch.zeros(40, 64, dtype=torch.bfloat16))
+    f = sfold.TiedGradFold(w)
+    assert f.dense_args(torch.tensor([4.0]), 128) == (None, None)  # not armed: nothing folds
+    f.arm()                                                         # scaler = 1 / the announced multiplier
+    with pytest.raises(RuntimeError):
+        f.sparse_args(128)                                          # the dense site starts a fold
+    ps, ws = f.dense_args(torch.tensor([4.0]), 128)
+    assert ps.item() == 0.25 and ws.dtype == torch.uint8 and ws.numel() >= 4 * 4 * 4096
+    with pytest.raises(RuntimeError):
+        f.sparse_args(256)                                          # more token rows than the loss saw
+    ps2, ws2 = f.sparse_args(128)
+    assert ps2 is ps and ws2 is ws and f.folded and not f.armed
+    f.arm(torch.tensor(0.125))
+    assert f.dense_args(torch.tensor([4.0]), 64)[0].item() == 0.125 and not f.folded
+    f.arm()
+    assert f.dense_args(torch.tensor([0.0]), 64)[0].item() == 0.0   # no valid token: scale 0, not inf
+
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.a = w
+            self.b = nn.Parameter(torch.ones(3))
+
+    m, holder = M(), type("L", (), {})()
+    w.grad, m.b.grad = torch.ones_like(w), torch.ones(3)
+    holder.fold = f
+    f.folded = True
+    sfold.scale_grads(m, torch.tensor(0.5), holder)
+    assert torch.equal(w.grad, torch.ones_like(w)) and torch.equal(m.b.grad, torch.full((3,), 0.5))
+    f.folded = False
+    sfold.scale_grads(m, torch.tensor(0.5), holder)                 # nothing folded: the plain reference behaviour
+    assert torch.equal(w.grad, torch.full_like(w, 0.5)) and torch.equal(m.b.grad, torch.full((3,), 0.25))
+
+
+def test_fold_workspace_size_is_device_independent():
+    import ctypes
+
+    from ssi_b200 import _lib
+
+    b = ctypes.c_size_t(0)
+    assert _lib.load().ssi_b200_grad_fold_workspace_bytes(131072, 2048, ctypes.byref(b)) == 0
+    assert b.value == 4 * (2 * 4096 + 2 * (131072 // 32) * 8)
+    assert _lib.load().ssi_b200_grad_fold_workspace_bytes(64, 64, ctypes.byref(b)) == 0
+    assert b.value == 4 * (4 * 4096)
+    assert _lib.load().ssi_b200_grad_fold_workspace_bytes(0, 64, ctypes.byref(b)) < 0

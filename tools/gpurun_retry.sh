@@ -4,7 +4,7 @@ log=$1; shift
 for i in $(seq 1 40); do
   /usr/local/graft/bin/gpurun "$@" > "$log" 2>&1
   rc=$?
-  if [ $rc -ne 3 ]; then exit $rc; fi
+  if [ $rc -ne 3 ] && [ $rc -ne 2 ]; then exit $rc; fi
   sleep 150
 done
 exit 3
