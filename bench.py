@@ -49,7 +49,7 @@ def parse_args():
     ap.add_argument("--config", default="c5", help="SURVEY.md §8d configuration (c1..c5)")
     ap.add_argument("--mode", default=None, choices=["single_pass", "recompute"],
                     help="gradient mode of the fused loss (default: the library default, single_pass)")
-    ap.add_argument("--exchange", default=None, choices=["peer", "nccl"],
+    ap.add_argument("--exchange", default=None, choices=["peer", "nvls", "nccl"],
                     help="N > 1: how the tied gradient is summed over ranks (default: peer-memory reduce behind "
                          "the last dX contraction; nccl = bf16 all_reduce after the step)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -478,6 +478,8 @@ def run_ours(args):
     if path.sync is not None:
         path.sync.check(confirm_multiplier=True)  # raises if the exchange ran with a multiplier that backward did not confirm / timed out
     exchange = path.exchange
+    if path.sync is not None and path.sync.peer is not None and path.sync.peer.multicast_ptr:
+        exchange = "peer+nvls (multimem.ld_reduce in the dense reduce)"
     path.close()
     if rank != 0:
         if world > 1:

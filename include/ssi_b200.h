@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 111
+#define SSI_B200_ABI_VERSION 112
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -327,6 +327,14 @@ int ssi_b200_dp_exchange_fold(void* const* peer_bufs, int rank, int world, int64
                               uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW,
                               int accumulate_dW, void* host_flag, const float* post_scale, void* fold_ws,
                               size_t fold_ws_bytes, void* stream);
+/* ssi_b200_dp_exchange_fold with the in-switch reduction (NVLS): multicast_buf = the MULTICAST address of the
+ * exchange buffers (all ranks' buffers bound to one multicast object, e.g. torch.distributed._symmetric_memory's
+ * multicast_ptr) or NULL (= plain P2P loads).  The reduce then issues one multimem.ld_reduce per 16 bytes instead of
+ * `world` peer loads: 1/world of the NVLink bytes into the GPU. */
+int ssi_b200_dp_exchange_nvls(void* const* peer_bufs, const void* multicast_buf, int rank, int world, int64_t V,
+                              int64_t D, int64_t max_rows, uint32_t epoch, const float* grad_out,
+                              const float* grad_hint, void* dW, int accumulate_dW, void* host_flag,
+                              const float* post_scale, void* fold_ws, size_t fold_ws_bytes, void* stream);
 int ssi_b200_dp_embedding_exchange_fold(const void* dH, int64_t N, int64_t V, int64_t D, void* sort_ws,
                                         size_t sort_ws_bytes, void* const* peer_bufs, int rank, int world,
                                         int64_t max_rows, uint32_t epoch, void* dW, void* host_flag,

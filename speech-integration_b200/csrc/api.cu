@@ -1365,6 +1365,14 @@ int ssi_b200_dp_exchange_fold(void* const* peer_bufs, int rank, int world, int64
                               uint32_t epoch, const float* grad_out, const float* grad_hint, void* dW,
                               int accumulate_dW, void* host_flag, const float* post_scale, void* fold_ws_ptr,
                               size_t fold_ws_bytes, void* stream) {
+  return ssi_b200_dp_exchange_nvls(peer_bufs, nullptr, rank, world, V, D, max_rows, epoch, grad_out, grad_hint, dW,
+                                   accumulate_dW, host_flag, post_scale, fold_ws_ptr, fold_ws_bytes, stream);
+}
+
+int ssi_b200_dp_exchange_nvls(void* const* peer_bufs, const void* multicast_buf, int rank, int world, int64_t V,
+                              int64_t D, int64_t max_rows, uint32_t epoch, const float* grad_out,
+                              const float* grad_hint, void* dW, int accumulate_dW, void* host_flag,
+                              const float* post_scale, void* fold_ws_ptr, size_t fold_ws_bytes, void* stream) {
   SSI_CHECK_ARG(grad_out && grad_hint && dW, "null pointer argument");
   ssi::DpPeers peers;
   if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
@@ -1383,13 +1391,23 @@ int ssi_b200_dp_exchange_fold(void* const* peer_bufs, int rank, int world, int64
   const long long total_f4 = static_cast<long long>(V) * D / 4;
   const long long slice_f4 = static_cast<long long>(ceil_div(V, world)) * D / 4;
   const int grid = di->sms * 2 < FOLD_SEG ? di->sms * 2 : FOLD_SEG;
+  SSI_CHECK_ARG((reinterpret_cast<uintptr_t>(multicast_buf) & 15) == 0, "multicast_buf must be 16-byte aligned");
+  const float4* mc_acc = multicast_buf ? reinterpret_cast<const float4*>(static_cast<const char*>(multicast_buf) +
+                                                                         lay.off_acc)
+                                       : nullptr;
   uint2* out = static_cast<uint2*>(dW);
   unsigned int* hf = static_cast<unsigned int*>(host_flag);
   ProfScope ps(CAT_EXCHANGE, st);
 #define SSI_DP_CASE(W_)                                                                                               \
   case W_:                                                                                                            \
-    ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, grad_out, \
-                                                                grad_hint, accumulate_dW ? 1 : 0, out, hf, f_own);    \
+    if (mc_acc && W_ > 1)                                                                                             \
+      ssi::dp_reduce_kernel<W_, true><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch,  \
+                                                                        grad_out, grad_hint, accumulate_dW ? 1 : 0,   \
+                                                                        out, hf, f_own, mc_acc);                      \
+    else                                                                                                              \
+      ssi::dp_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch,        \
+                                                                  grad_out, grad_hint, accumulate_dW ? 1 : 0, out,    \
+                                                                  hf, f_own);                                         \
     SSI_LAUNCH_OK("dp_reduce");                                                                                       \
     if (W_ > 1) {                                                                                                     \
       ssi::dp_gather_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, slice_f4, total_f4, epoch, out,   \

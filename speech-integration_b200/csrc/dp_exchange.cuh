@@ -105,6 +105,17 @@ __device__ __forceinline__ uint4 ld_peer_u4(const uint4* p) {
   return v;
 }
 
+// NVLS: one load from the MULTICAST mapping of the exchange buffers returns the sum over all ranks, formed inside
+// the NVSwitch (fp32 adds in the switch's fixed order: the same value whichever rank asks, run to run on one topology)
+__device__ __forceinline__ float4 multimem_ld_reduce_f4(const float4* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(mc)
+               : "memory");
+  return v;
+}
+
 __device__ __forceinline__ unsigned long long global_timer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -188,13 +199,15 @@ __global__ void __launch_bounds__(32) dp_counts_kernel(DpPeers peers, int rank, 
 // ---------------------------------------------------------------------------------------------------
 // Dense exchange of the fp32 LM-head sums
 // ---------------------------------------------------------------------------------------------------
-template <int WORLD>
+// NVLS = true: `mc_acc` is the multicast address of dW_acc (all ranks' buffers bound to one multicast object); the
+// `world` peer loads per element become ONE multimem.ld_reduce, i.e. 1/world of the NVLink bytes into this GPU.
+template <int WORLD, bool NVLS = false>
 __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, DpLayout lay, int rank,
                                                                long long slice_f4, long long total_f4,
                                                                unsigned int epoch, const float* __restrict__ grad_out,
                                                                const float* __restrict__ grad_hint, int accumulate,
                                                                uint2* __restrict__ dW, unsigned int* host_flag,
-                                                               GradFold fold) {
+                                                               GradFold fold, const float4* mc_acc = nullptr) {
   __shared__ float s_fold[DP_THREADS / 32];
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
   // ---- announce: everything this rank contributes (its dW_acc) was finished by earlier kernels of this stream
@@ -214,17 +227,22 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
 #pragma unroll
   for (int p = 0; p < WORLD; ++p) src[p] = reinterpret_cast<const float4*>(peers.buf[p] + lay.off_acc);
   uint2* stage = reinterpret_cast<uint2*>(peers.buf[rank] + lay.off_stage);
-  constexpr int UNROLL = (WORLD <= 2) ? 4 : 2;
+  constexpr int UNROLL = NVLS ? 8 : (WORLD <= 2) ? 4 : 2;
+  constexpr int TERMS = NVLS ? 1 : WORLD;
   const long long stride = static_cast<long long>(gridDim.x) * DP_THREADS;
   for (long long i0 = begin + blockIdx.x * static_cast<long long>(DP_THREADS) + threadIdx.x; i0 < end;
        i0 += stride * UNROLL) {
-    float4 v[UNROLL][WORLD];
+    float4 v[UNROLL][TERMS];
 #pragma unroll
     for (int u = 0; u < UNROLL; ++u) {
       const long long i = i0 + u * stride;
       if (i < end) {
+        if constexpr (NVLS) {
+          v[u][0] = multimem_ld_reduce_f4(mc_acc + i);
+        } else {
 #pragma unroll
-        for (int p = 0; p < WORLD; ++p) v[u][p] = (p == rank) ? src[p][i] : ld_peer_f4(src[p] + i);
+          for (int p = 0; p < WORLD; ++p) v[u][p] = (p == rank) ? src[p][i] : ld_peer_f4(src[p] + i);
+        }
       }
     }
 #pragma unroll
@@ -233,7 +251,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
       if (i >= end) continue;
       float4 a = v[u][0];
 #pragma unroll
-      for (int p = 1; p < WORLD; ++p) a.x += v[u][p].x, a.y += v[u][p].y, a.z += v[u][p].z, a.w += v[u][p].w;
+      for (int p = 1; p < TERMS; ++p) a.x += v[u][p].x, a.y += v[u][p].y, a.z += v[u][p].z, a.w += v[u][p].w;
       a.x *= ratio, a.y *= ratio, a.z *= ratio, a.w *= ratio;
       if (accumulate) {
         const uint2 old = dW[i];

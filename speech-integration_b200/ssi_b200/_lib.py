@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 111
+ABI_VERSION = 112
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -129,6 +129,11 @@ SYMBOLS = {
         c_int,
         [POINTER(c_void_p), c_int, c_int, c_int64, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p, c_void_p,
          c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_dp_exchange_nvls": (
+        c_int,
+        [POINTER(c_void_p), c_void_p, c_int, c_int, c_int64, c_int64, c_int64, ctypes.c_uint32, c_void_p, c_void_p,
+         c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
     ),
     "ssi_b200_dp_embedding_exchange_fold": (
         c_int,

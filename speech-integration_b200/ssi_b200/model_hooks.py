@@ -195,7 +195,9 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     ssi/data/__init__.py:82-83): the tied gradient — and nothing else — is summed over the group's ranks, in the order
     a training step produces its parts (:mod:`ssi_b200.sync`; semantics of tt/recipes/full_finetune_distributed.py:
     844-851: losses are this rank's share of the global mean, gradients those of the global mean).  ``exchange``:
-    ``"peer"`` (default: the library's own NVLink peer-memory kernels) or ``"nccl"`` (bf16 all-reduce baseline);
+    ``"peer"`` (default: the library's own NVLink peer-memory kernels), ``"nvls"`` (the same with the dense reduce done
+    inside the NVSwitch, ``multimem.ld_reduce``; buffers from torch's symmetric-memory allocator) or ``"nccl"`` (bf16
+    all-reduce baseline);
     ``max_tokens_per_rank`` sizes the compact-row area of the peer exchange (most token rows of one micro-batch).
 
     ``fold_scale_grads``: give the loss a :class:`ssi_b200.fold.TiedGradFold` (``loss_fn.fold``): the trainer's
@@ -230,8 +232,8 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
 
         if loss_fn.mode != "single_pass":
             # the peer exchange sums the fp32 dW_acc that only single-pass mode forms
-            if exchange == "peer":
-                raise ValueError("ssi_b200: exchange='peer' needs mode='single_pass'")
+            if exchange in ("peer", "nvls"):
+                raise ValueError(f"ssi_b200: exchange={exchange!r} needs mode='single_pass'")
             exchange = exchange or "nccl"
         sync = TiedGradSync(emb.weight, process_group, exchange=exchange, max_rows=max_tokens_per_rank)
         object.__setattr__(loss_fn, "sync", sync)

@@ -22,6 +22,7 @@ distributed recipe (tt/recipes/full_finetune_distributed.py:844-851,867): gradie
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 import torch.distributed as dist
@@ -47,7 +48,12 @@ class TiedGradExchange:
         max_rows: most token rows one ``embedding_exchange`` call may carry (sizes the compact-row area).
     """
 
-    def __init__(self, V: int, D: int, group=None, device: torch.device | None = None, max_rows: int = 0):
+    def __init__(self, V: int, D: int, group=None, device: torch.device | None = None, max_rows: int = 0,
+                 nvls: bool | None = None):
+        """``nvls``: allocate the exchange buffers through ``torch.distributed._symmetric_memory`` (plumbing only:
+        allocation, handle exchange, multicast binding) and let the dense reduce use the in-switch reduction
+        (``multimem.ld_reduce`` on the multicast mapping).  None = the environment variable ``SSI_B200_NVLS`` (default
+        off); True raises if the box has no multicast support; the CUDA-IPC path is the fallback otherwise."""
         if not dist.is_initialized():
             raise RuntimeError("ssi_b200.peer: torch.distributed is not initialised")
         self.group = group
@@ -69,6 +75,13 @@ class TiedGradExchange:
         self._own = None
         self._peer_ptrs: list[int] = []
         self._opened: list[int] = []
+        self._symm = self._symm_tensor = None
+        self.multicast_ptr = 0
+        want_nvls = (os.environ.get("SSI_B200_NVLS") == "1") if nvls is None else bool(nvls)
+        if want_nvls and self._setup_symmetric():
+            return
+        if nvls:
+            raise RuntimeError("ssi_b200.peer: nvls=True, but symmetric memory with multicast is not available here")
         # Set-up is collective: a failure on ANY rank (no IPC in this container, no P2P between two GPUs, out of
         # memory) is agreed on by all ranks before anyone raises, so that callers can fall back together.
         err = None
@@ -108,6 +121,9 @@ class TiedGradExchange:
             self._opened, self._own = [], None
             why = next(e for e in [g[1] for g in gathered] + errs if e is not None)
             raise RuntimeError(f"ssi_b200.peer: peer-memory set-up failed on at least one rank: {why}")
+        self._finish_setup()
+
+    def _finish_setup(self) -> None:
         self._ptr_array = (ctypes.c_void_p * self.world)(*self._peer_ptrs)
         self.dw_acc = torch.as_tensor(_DevicePtr(self._own + self._acc_off, (self.V, self.D), "<f4"),
                                       device=self.device)
@@ -115,7 +131,32 @@ class TiedGradExchange:
         self._host_flag = torch.zeros(1, dtype=torch.int32).pin_memory()
         # every rank must have mapped (and zero-initialised) its buffers before the first exchange touches them
         torch.cuda.synchronize(self.device)
-        dist.barrier(group=group)
+        dist.barrier(group=self.group)
+
+    def _setup_symmetric(self) -> bool:
+        """Exchange buffers from torch's symmetric-memory allocator (cuMem + multicast binding); False -- agreed on
+        by all ranks -- when any rank cannot (old driver, no NVSwitch multicast, world size 1)."""
+        err, t, hdl = None, None, None
+        try:
+            import torch.distributed._symmetric_memory as symm
+
+            t = symm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            t.zero_()
+            hdl = symm.rendezvous(t, self.group if self.group is not None else dist.group.WORLD)
+            if int(hdl.multicast_ptr) == 0:
+                err = "no multicast mapping (multicast_ptr == 0)"
+        except Exception as e:  # noqa: BLE001 - any failure means "use the IPC path"
+            err = f"{type(e).__name__}: {e}"
+        errs: list = [None] * self.world
+        dist.all_gather_object(errs, err, group=self.group)
+        if any(e is not None for e in errs):
+            return False
+        self._symm, self._symm_tensor = hdl, t
+        self._peer_ptrs = [int(p) for p in hdl.buffer_ptrs]
+        self._own = self._peer_ptrs[self.rank]
+        self.multicast_ptr = int(hdl.multicast_ptr)
+        self._finish_setup()
+        return True
 
     # ------------------------------------------------------------------------------------------------ exchanges
     def _stream(self) -> int:
@@ -153,11 +194,11 @@ class TiedGradExchange:
         self.epoch_dense += 1
         ps, fw, fwb = ops._fold_args(post_scale, fold_ws, self.device)
         with torch.cuda.device(self.device):
-            rc = _lib.load().ssi_b200_dp_exchange_fold(self._ptr_array, self.rank, self.world, self.V, self.D,
-                                                       self.max_rows, self.epoch_dense & 0xFFFFFFFF,
-                                                       grad_out.data_ptr(), grad_hint.data_ptr(), dW.data_ptr(),
-                                                       1 if accumulate else 0, self._host_flag.data_ptr(), ps, fw, fwb,
-                                                       self._stream())
+            rc = _lib.load().ssi_b200_dp_exchange_nvls(self._ptr_array, self.multicast_ptr or None, self.rank,
+                                                       self.world, self.V, self.D, self.max_rows,
+                                                       self.epoch_dense & 0xFFFFFFFF, grad_out.data_ptr(),
+                                                       grad_hint.data_ptr(), dW.data_ptr(), 1 if accumulate else 0,
+                                                       self._host_flag.data_ptr(), ps, fw, fwb, self._stream())
         _lib.check(rc, "dp_exchange")
         return dW
 
@@ -206,8 +247,12 @@ class TiedGradExchange:
             dist.barrier(group=self.group)  # nobody may unmap while a peer can still read
         lib = _lib.load()
         self.dw_acc = None
-        with torch.cuda.device(self.device):
-            for p in self._opened:
-                lib.ssi_b200_dp_close(p)
-            lib.ssi_b200_dp_free(self._own)
+        if self._symm is not None:  # torch owns the symmetric allocation: drop the references
+            self._symm = self._symm_tensor = None
+            self.multicast_ptr = 0
+        else:
+            with torch.cuda.device(self.device):
+                for p in self._opened:
+                    lib.ssi_b200_dp_close(p)
+                lib.ssi_b200_dp_free(self._own)
         self._opened, self._own = [], None

@@ -52,7 +52,7 @@ class PathStep:
             import torch.distributed as dist
 
             self.world = dist.get_world_size(process_group)
-        use_pg = process_group if (process_group is not None and (self.world > 1 or exchange == "peer")) else None
+        use_pg = process_group if (process_group is not None and (self.world > 1 or exchange in ("peer", "nvls"))) else None
         self.loss_fn = install(self.model, num_output_chunks, ignore_index, mode=mode, process_group=use_pg,
                                exchange=exchange, max_tokens_per_rank=max_tokens_per_rank,
                                fold_scale_grads=fold_scale_grads)

@@ -46,16 +46,21 @@ class TiedGradSync:
         self.device = weight.device
         asked = exchange or os.environ.get("SSI_B200_EXCHANGE")
         self.mode = asked or "peer"
-        if self.mode not in ("peer", "nccl"):
-            raise ValueError(f"ssi_b200: unknown exchange {self.mode!r} (expected 'peer' or 'nccl')")
+        if self.mode not in ("peer", "nccl", "nvls"):
+            raise ValueError(f"ssi_b200: unknown exchange {self.mode!r} (expected 'peer', 'nvls' or 'nccl')")
+        # "nvls" = the peer exchange with the in-switch reduction (multimem.ld_reduce) for the dense part
+        nvls = True if self.mode == "nvls" else None
+        if self.mode == "nvls":
+            self.mode = "peer"
         self.peer = None
         if self.mode == "peer":
             from .peer import TiedGradExchange
 
             try:
-                self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, self.device, max_rows)
+                self.peer = TiedGradExchange(weight.size(0), weight.size(1), process_group, self.device, max_rows,
+                                             nvls=nvls)
             except RuntimeError as e:
-                if asked == "peer":
+                if asked in ("peer", "nvls"):
                     raise  # asked for explicitly
                 # the failure was agreed on by all ranks (TiedGradExchange), so all of them land here together
                 warnings.warn(f"{e}; using the NCCL all-reduce of the tied gradient instead")
