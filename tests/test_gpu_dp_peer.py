@@ -162,9 +162,24 @@ def _worker(rank, world, port, out):
         torch.cuda.synchronize()
         res["fold"] = (fold_sq.item(), None, step.weight.grad.cpu())
         step.close()
+        # the in-switch reduction (NVLS, multimem.ld_reduce) for the dense part, where the box has multicast support
+        try:
+            step = PathStep(inp["W"].to(dev), process_group=pg, exchange="nvls")
+        except RuntimeError as e:
+            step, res["nvls_why"] = None, str(e)
+        if step is not None:
+            grads = []
+            for _ in range(2):
+                step.zero_grad()
+                step(*args)
+                torch.cuda.synchronize()
+                grads.append(step.weight.grad.clone())
+            res["nvls"] = (None, None, grads[1].cpu())
+            res["nvls_repeatable"] = bool(torch.equal(grads[0], grads[1]))
+            step.close()
         # every rank must hold the bit-identical summed gradient
         same = {}
-        for ex in ("peer", "nccl", "fold"):
+        for ex in ("peer", "nccl", "fold") + (("nvls",) if "nvls" in res else ()):
             g = res[ex][2].cuda().view(torch.int16).to(torch.int32)
             lo, hi = g.clone(), g.clone()
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)
@@ -219,6 +234,12 @@ def _worker(rank, world, port, out):
                 assert_grad_close(res["peer"][1].reshape(ref_dH[b0:b1].shape), ref_dH[b0:b1], "dH")
                 assert_grad_close(res["fold"][2], ref_dW / n_iter, "dW peer, scale_grads folded",
                                   elem_roundings=DW_ELEM_ROUNDINGS)
+                if "nvls" in res:
+                    assert same["nvls"] and res["nvls_repeatable"], "NVLS reduce: not identical on all ranks / runs"
+                    assert_grad_close(res["nvls"][2], ref_dW, "dW peer + NVLS reduce", elem_roundings=DW_ELEM_ROUNDINGS)
+                    out["nvls"] = "tested"
+                else:
+                    out["nvls"] = "unavailable: " + res.get("nvls_why", "?")[:200]
                 own_sq = res["fold"][2].double().pow(2).sum().item()
                 assert abs(res["fold"][0] - own_sq) <= 5e-5 * own_sq, ("folded sqnorm", res["fold"][0], own_sq)
                 t_loss, t_dW, t_mix = _oracle_tiny(tin, [slice(0, B), slice(B, 2 * B)])
@@ -245,3 +266,4 @@ def test_peer_exchange_world2_matches_single_process_oracle():
     assert out.get("loss_ok") is True
     assert out.get("eval_ok") is True
     assert out.get("grads_ok") is True, out.get("why")
+    print("NVLS dense reduce:", out.get("nvls"))

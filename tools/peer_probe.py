@@ -54,10 +54,26 @@ def main():
     t_peer = timed(lambda: ex.exchange(dW, one, one))
     want = float(sum(range(1, world + 1)))
     ok = bool((dW.float() == want).all().item())
+    # the same exchange with the in-switch reduction (multimem.ld_reduce on the multicast mapping)
+    t_nvls, ok_nvls = None, None
+    try:
+        exn = TiedGradExchange(V, D, dist.group.WORLD, dev, nvls=True)
+    except RuntimeError as e:
+        exn, why = None, str(e)
+    if exn is not None:
+        exn.dw_acc.fill_(float(rank + 1))
+        dW.zero_()
+        t_nvls = timed(lambda: exn.exchange(dW, one, one))
+        ok_nvls = bool((dW.float() == want).all().item())
+        exn.close()
     g = torch.ones(V, D, dtype=torch.bfloat16, device=dev)
     t_nccl = timed(lambda: dist.all_reduce(g))
     if rank == 0:
         gb = V * D * 2 / 1e9
+        if t_nvls is not None:
+            print(f"world {world}: NVLS reduce + bf16 gather {t_nvls:.3f} ms (result ok={ok_nvls})", flush=True)
+        else:
+            print(f"world {world}: NVLS unavailable: {why[:200]}", flush=True)
         print(f"world {world}: peer exchange {t_peer:.3f} ms (fp32 reduce + bf16 gather, result ok={ok}), "
               f"nccl bf16 all_reduce {t_nccl:.3f} ms, buffer {gb:.3f} GB bf16", flush=True)
     ex.close()
