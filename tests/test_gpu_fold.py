@@ -63,9 +63,14 @@ def test_fold_single_gpu_matches_oracle_and_two_pass_form(shape):
     torch.cuda.synchronize()
     a, b = runs[0][0].float(), two_pass.float()
     assert_grad_close(a.cpu(), b.cpu(), "folded vs two-pass gradient")
-    ulp = torch.maximum(b.abs(), torch.tensor(1e-30, device=dev)) * 2.0 ** -7
-    within = ((a - b).abs() <= ulp).float().mean().item()  # rows the embedding touched round at different points
-    assert within >= 0.999, f"only {within:.5f} of the elements are within one bf16 ulp of the two-pass form"
+    # rows the embedding did not touch: one rounding against two, never more than one bf16 ulp apart; the touched rows
+    # round their two parts at different points (covered by the tolerance above and by the oracle comparison)
+    untouched = torch.ones(a.size(0), dtype=torch.bool, device=dev)
+    ids = args[0].reshape(-1)
+    untouched[ids[(ids >= 0) & (ids < a.size(0))]] = False
+    au, bu = a[untouched], b[untouched]
+    ulp = torch.maximum(bu.abs(), torch.tensor(1e-30, device=dev)) * 2.0 ** -7
+    assert ((au - bu).abs() <= ulp).all(), "untouched rows: folded and two-pass form differ by more than one bf16 ulp"
     # helpers: scale_grads skips the folded weight, grad_norm takes the folded sum of squares
     before = folded.weight.grad.clone()
     sfold.scale_grads(folded.model, torch.tensor(123.0), folded.loss_fn)
