@@ -76,6 +76,9 @@ class TiedGradSync:
         self._target = None           # nccl mode: where this micro-batch's LM-head gradient went
         self._dense_done = False      # peer mode: this micro-batch's dense exchange is enqueued
         self.grad_hint_mismatch: torch.Tensor | None = None
+        # SSI_B200_TIMELINE=1 (diagnostics): CUDA events at the seams of every micro-batch, summarised by close()
+        self._tl = [] if (os.environ.get("SSI_B200_TIMELINE") == "1" and self.peer is not None) else None
+        self._tl_cur = None
         self.fold = None              # ssi_b200.fold.TiedGradFold (install(fold_scale_grads=True)), peer mode only
         self._rows = 0                # token rows of the running micro-batch (sizes the fold scratch)
 
@@ -90,6 +93,8 @@ class TiedGradSync:
         returned event says when (``ops.lmhead_ce_fwd_grad(pre_grad_event=...)`` waits for it on the device)."""
         if self.peer is not None:
             main = torch.cuda.current_stream(self.device)
+            if self._tl is not None:
+                self._tl_cur = {"start": self._mark(main)}
             self.local_ready.record(main)
             self.side.wait_event(self.local_ready)
             with torch.cuda.stream(self.side):
@@ -120,7 +125,11 @@ class TiedGradSync:
         with torch.cuda.stream(self.side):
             # the scale_grads / grad-norm fold rides in the reduce (the side stream is ordered after `hint`)
             ps, fws = self.fold.dense_args(hint, self._rows) if self.fold is not None else (None, None)
+            if self._tl_cur is not None:
+                self._tl_cur["dw_done"] = self._mark(self.side)
             self.peer.exchange(self.weight.grad, grad_out, hint, accumulate=accumulate, post_scale=ps, fold_ws=fws)
+            if self._tl_cur is not None:
+                self._tl_cur["dense_done"] = self._mark(self.side)
         self._dense_done = True
 
     def after_forward(self, hint: torch.Tensor, announced: bool, n_rows: int = 0) -> None:
@@ -168,6 +177,8 @@ class TiedGradSync:
         """The last contribution of a micro-batch to the tied gradient (backward of ``tok_embeddings``)."""
         main = torch.cuda.current_stream(self.device)
         if self.peer is not None:
+            if self._tl_cur is not None:
+                self._tl_cur["bwd_done"] = self._mark(main)
             if not self.serial:
                 main.wait_stream(self.side)  # the dense exchange wrote .grad; peers are done with last step's rows
             if self.weight.grad is None:
@@ -175,6 +186,11 @@ class TiedGradSync:
             ps, fws = self.fold.sparse_args(dH.size(0)) if self.fold is not None else (None, None)
             self.peer.embedding_exchange(dH, sort_ws, self.weight.grad, post_scale=ps, fold_ws=fws)
             self._dense_done = False
+            if self._tl_cur is not None:
+                self._tl_cur["end"] = self._mark(main)
+                if len(self._tl_cur) == 5:
+                    self._tl.append(self._tl_cur)
+                self._tl_cur = None
             return
         target = self._target
         if target is None:  # no LM-head backward in this micro-batch
@@ -204,8 +220,29 @@ class TiedGradSync:
                                "backward received a different upstream gradient; announce the right one "
                                "(loss_fn.grad_hint) or none at all")
 
+    @staticmethod
+    def _mark(stream) -> torch.cuda.Event:
+        e = torch.cuda.Event(enable_timing=True)
+        e.record(stream)
+        return e
+
+    def timeline(self, last: int = 10) -> dict | None:
+        """Mean milliseconds, over the last micro-batches, from the start of the loss forward to: the last dW
+        contraction done (side stream released), the dense exchange done, dX returned (loss backward done), the end of
+        the embedding exchange.  Diagnostics (``SSI_B200_TIMELINE=1``); synchronises."""
+        if not self._tl:
+            return None
+        torch.cuda.synchronize(self.device)
+        rows = self._tl[-last:]
+        keys = ("dw_done", "dense_done", "bwd_done", "end")
+        return {k: sum(r["start"].elapsed_time(r[k]) for r in rows) / len(rows) for k in keys}
+
     def close(self) -> None:
         """Release the peer exchange buffers (collective: every rank must call it)."""
+        if self._tl:
+            import sys
+
+            print(f"ssi_b200 timeline rank {self.rank}: {self.timeline()}", file=sys.stderr, flush=True)
         if self.peer is not None:
             self.peer.close()
             self.peer = None
