@@ -319,8 +319,10 @@ def run_ours(args):
     _lib.profile_begin()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
+    t_host0 = time.perf_counter()
     for _ in range(args.steps):
         out = step()
+    host_ms_step = (time.perf_counter() - t_host0) * 1e3 / args.steps  # time to ENQUEUE a step (no sync inside)
     e1.record()
     barrier()
     ms_total = e0.elapsed_time(e1)
@@ -554,7 +556,8 @@ def run_ours(args):
                            "(ssi/trainer.py:393-394), through install()",
                    "l2": "inputs (X, W, dlogits blocks) are several times larger than "
                    "the 126 MB L2, no explicit flush", "loss_batch_rank0": float(loss_batch.item())},
-        "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline,
+        "clocks": clocks, "gpu_launches": launches, "host_enqueue_ms_per_step": host_ms_step, "e2e": e2e,
+        "roofline": roofline,
         "step_algorithmic_tflops_per_gpu": step_tflops,
         "step_frac_of_bf16_peak": {"burst": step_tflops / peaks["bf16_tflops"], "sustained": step_tflops / peak},
         "kernels": kern, "fwd_only": fwd_only, "parity": parity, "k3_roofline": k3, "scale_grads_fold": fold_blk,

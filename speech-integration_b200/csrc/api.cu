@@ -325,6 +325,7 @@ struct Tune {
   // single-pass: 1 = K1 stashes E = exp(logit - ref[row]) and the softmax normalisation is a per-row factor folded into
   // the dX epilogue and the X rows of dW (no pass over the block); 0 = stash logits + separate softmax-grad HBM pass
   int exp_stash = 1;
+  int sparse_two_phase = -1;  // sparse (embedding) exchange: 1 = owner-reduce + apply, 0 = one phase, -1 = auto (world > 4)
   int k1_group_m = 0;  // K1: m-tiles (128 rows) per raster group, 0 = the whole row chunk (GemmParams::lse_group_m)
 };
 // The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
@@ -351,6 +352,7 @@ Tune& global_tune() {
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_EXP_STASH")) x.exp_stash = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_K1_GROUP_M")) x.k1_group_m = atoi(e);
+    if (const char* e = getenv("SSI_B200_SPARSE_TWO_PHASE")) x.sparse_two_phase = atoi(e);
     return x;
   }();
   return t;
@@ -583,6 +585,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "exp_stash")) t.exp_stash = value ? 1 : 0;
   else if (!strcmp(name, "k1_group_m")) t.k1_group_m = value > 0 ? static_cast<int>(value) : 0;
+  else if (!strcmp(name, "sparse_two_phase")) t.sparse_two_phase = value < 0 ? -1 : (value ? 1 : 0);
   else return fail(-1, "unknown option '%s'", name);
   return 0;
 }
@@ -1443,6 +1446,7 @@ int ssi_b200_dp_embedding_exchange_fold(const void* dH, int64_t N, int64_t V, in
                                         int64_t max_rows, uint32_t epoch, void* dW, void* host_flag,
                                         const float* post_scale, void* fold_ws_ptr, size_t fold_ws_bytes,
                                         void* stream) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(dH && sort_ws && dW, "null pointer argument");
   ssi::DpPeers peers;
   if (int r = dp_peers(peer_bufs, rank, world, &peers)) return r;
@@ -1478,10 +1482,19 @@ int ssi_b200_dp_embedding_exchange_fold(const void* dH, int64_t N, int64_t V, in
   ssi::GradFold gf;
   gf.post_scale = post_scale, gf.sq = fw.seg(2);
   ProfScope ps(CAT_EXCHANGE, st);
-#define SSI_DP_CASE(W_)                                                                                        \
-  case W_:                                                                                                     \
-    ssi::dp_sparse_add_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),     \
-                                                                    static_cast<int>(D), epoch, g, hf, gf);    \
+  const int tp_opt = tune().sparse_two_phase;
+  const bool two_phase = tp_opt < 0 ? world > 4 : tp_opt != 0;
+#define SSI_DP_CASE(W_)                                                                                            \
+  case W_:                                                                                                         \
+    if (two_phase) {                                                                                               \
+      ssi::dp_sparse_reduce_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),    \
+                                                                         static_cast<int>(D), epoch, hf);          \
+      ssi::dp_sparse_apply_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),     \
+                                                                        static_cast<int>(D), epoch, g, hf, gf);    \
+    } else {                                                                                                       \
+      ssi::dp_sparse_add_kernel<W_><<<grid, ssi::DP_THREADS, 0, st>>>(peers, lay, rank, static_cast<int>(V),       \
+                                                                      static_cast<int>(D), epoch, g, hf, gf);      \
+    }                                                                                                              \
     break;
   switch (world) {
     SSI_DP_CASE(1)

@@ -49,6 +49,7 @@ struct DpCtrl {
   unsigned int arrive_b[DP_MAX_WORLD];  // written by peers: epoch of their last "slice reduced"
   unsigned int arrive_c[DP_MAX_WORLD];  // written by peers: epoch of their last "compact embedding rows published"
   unsigned int arrive_n[DP_MAX_WORLD];  // written by peers: epoch of their last "token counts posted"
+  unsigned int arrive_d[DP_MAX_WORLD];  // written by peers: epoch of their last "owned embedding rows reduced"
   unsigned long long counts[2][DP_MAX_WORLD][2];  // [epoch & 1][rank] = {unshifted, shifted} valid-token counts
   unsigned int blocks_done;             // local: blocks of dp_reduce_kernel that finished (reset by the last one)
   unsigned int timed_out;               // local: set when a wait gave up (a peer never arrived): results are invalid
@@ -63,8 +64,9 @@ struct DpPeers {
 
 // byte offsets inside an exchange buffer (identical on every rank)
 struct DpLayout {
-  size_t off_acc, off_stage, off_slot, off_ids, off_rows, bytes;
+  size_t off_acc, off_stage, off_slot, off_ids, off_rows, off_own_flag, off_own_rows, bytes;
   long long cap;  // rows of the compact embedding list
+  long long vs;   // ceil(V / world): ids a rank owns in the two-phase sparse exchange (id % world == rank)
 };
 __host__ __device__ inline DpLayout dp_layout(long long V, long long D, int world, long long cap) {
   DpLayout l;
@@ -76,7 +78,11 @@ __host__ __device__ inline DpLayout dp_layout(long long V, long long D, int worl
   l.off_slot = o, o += up(static_cast<size_t>(V) * 8);
   l.off_ids = o, o += up(static_cast<size_t>(cap) * 4);
   l.off_rows = o, o += up(static_cast<size_t>(cap) * D * 2);
-  l.bytes = o, l.cap = cap;
+  // two-phase sparse exchange: the reduced row of owned id v = k * world + rank lives at own_rows[k], valid for the
+  // exchange whose epoch is in own_flag[k]
+  l.off_own_flag = o, o += up(static_cast<size_t>(vs) * 4);
+  l.off_own_rows = o, o += up(static_cast<size_t>(cap > 0 ? vs : 0) * D * 2);
+  l.bytes = o, l.cap = cap, l.vs = vs;
   return l;
 }
 
@@ -430,6 +436,179 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers
     }
   }
   if (fold.sq) {  // one partial per warp: sum(new^2 - old^2) over the rows it rewrote
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
+    if (lane == 0) fold.sq[gw] = dsq;
+  }
+}
+
+
+// ---------------------------------------------------------------------------------------------------
+// Two-phase form of the sparse exchange (default for world > 4).  The one-phase kernel above makes every rank pull
+// every other rank's rows: sum_p U_p rows per rank (c5 at 8 ranks: 56 k rows = 229 MB, of which two thirds are the
+// ~5000 DSU ids that EVERY rank holds).  Here id v is owned by rank v % world:
+//   dp_sparse_reduce_kernel  the owner sums the ranks' rows of its ids in rank order in fp32, rounds once to bf16 and
+//                            leaves the row in its own_rows[v / world] (own_flag = epoch);
+//   dp_sparse_apply_kernel   every rank reads each present id's reduced row from its owner (one row per id instead
+//                            of one per holder) and adds it to its bf16 gradient row.
+// c5 at 8 ranks: 7 k + 26 k rows = 135 MB per rank.  The same bf16 row is added by every rank, so the gradients stay
+// bit-identical across ranks; one more rounding of the embedding sum than the one-phase form.
+// ---------------------------------------------------------------------------------------------------
+template <int WORLD>
+__global__ void __launch_bounds__(DP_THREADS) dp_sparse_reduce_kernel(DpPeers peers, DpLayout lay, int rank, int V,
+                                                                      int D, unsigned int epoch,
+                                                                      unsigned int* host_flag) {
+  constexpr int WP2 = WORLD <= 1 ? 1 : WORLD <= 2 ? 2 : WORLD <= 4 ? 4 : 8;
+  constexpr int PER = 32 / WP2;  // owned ids per warp iteration
+  DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
+  if (blockIdx.x == 0 && threadIdx.x < WORLD && static_cast<int>(threadIdx.x) != rank) {
+    __threadfence_system();
+    st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_c[rank], epoch);
+  }
+  dp_wait_all(ctrl->arrive_c, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  if (dp_is_bad(ctrl)) return;  // the apply kernel poisons the gradient
+  const uint32_t lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * DP_THREADS + threadIdx.x) >> 5;
+  const int nw = (gridDim.x * DP_THREADS) >> 5;
+  const int sub = lane / WP2, pl = lane % WP2;
+  const unsigned long long* slot_p =
+      (pl < WORLD) ? reinterpret_cast<const unsigned long long*>(peers.buf[pl] + lay.off_slot) : nullptr;
+  unsigned int* own_flag = reinterpret_cast<unsigned int*>(peers.buf[rank] + lay.off_own_flag);
+  __nv_bfloat16* own_rows = reinterpret_cast<__nv_bfloat16*>(peers.buf[rank] + lay.off_own_rows);
+  for (long long k0 = static_cast<long long>(gw) * PER; k0 < lay.vs; k0 += static_cast<long long>(nw) * PER) {
+    const long long v = (k0 + sub) * WORLD + rank;
+    unsigned long long s = 0;
+    if (slot_p != nullptr && v < V) {
+      asm volatile("ld.global.L1::no_allocate.u64 %0, [%1];" : "=l"(s) : "l"(slot_p + v));
+    }
+    const bool present = (static_cast<unsigned int>(s >> 32) == epoch) && slot_p != nullptr && v < V &&
+                         static_cast<long long>(s & 0xFFFFFFFFull) < lay.cap;
+    const unsigned pm = __ballot_sync(0xffffffffu, present);
+    if (pm == 0) continue;
+    const unsigned int my_idx = static_cast<unsigned int>(s & 0xFFFFFFFFull);
+    for (int q = 0; q < PER; ++q) {
+      const unsigned m = (pm >> (q * WP2)) & ((1u << WP2) - 1u);
+      if (m == 0) continue;
+      __nv_bfloat16* orow = own_rows + static_cast<size_t>(k0 + q) * D;
+      for (int d0 = 0; d0 < D; d0 += SPARSE_COLS) {
+        const int dcols = min(SPARSE_COLS, D - d0);
+        float acc[SPARSE_G][8];
+#pragma unroll
+        for (int g = 0; g < SPARSE_G; ++g)
+#pragma unroll
+          for (int e = 0; e < 8; ++e) acc[g][e] = 0.f;
+#pragma unroll
+        for (int pb = 0; pb < WORLD; pb += 4) {  // 4 peers' loads in flight, summed in rank order
+          uint4 u[4][SPARSE_G];
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            const int p = pb + kk;
+            if (p >= WORLD) break;
+            const unsigned int idx = __shfl_sync(0xffffffffu, my_idx, q * WP2 + p);
+            const bool has = (m >> p) & 1u;
+            const __nv_bfloat16* src =
+                reinterpret_cast<const __nv_bfloat16*>(peers.buf[p] + lay.off_rows) + static_cast<size_t>(idx) * D + d0;
+#pragma unroll
+            for (int g = 0; g < SPARSE_G; ++g) {
+              const int col = g * 256 + static_cast<int>(lane) * 8;
+              u[kk][g] = (has && col < dcols) ? ld_peer_u4(reinterpret_cast<const uint4*>(src + col))
+                                              : make_uint4(0, 0, 0, 0);
+            }
+          }
+#pragma unroll
+          for (int kk = 0; kk < 4; ++kk) {
+            if (pb + kk >= WORLD) break;
+#pragma unroll
+            for (int g = 0; g < SPARSE_G; ++g) {
+              acc[g][0] += bf16lo(u[kk][g].x), acc[g][1] += bf16hi(u[kk][g].x);
+              acc[g][2] += bf16lo(u[kk][g].y), acc[g][3] += bf16hi(u[kk][g].y);
+              acc[g][4] += bf16lo(u[kk][g].z), acc[g][5] += bf16hi(u[kk][g].z);
+              acc[g][6] += bf16lo(u[kk][g].w), acc[g][7] += bf16hi(u[kk][g].w);
+            }
+          }
+        }
+#pragma unroll
+        for (int g = 0; g < SPARSE_G; ++g) {
+          const int col = g * 256 + static_cast<int>(lane) * 8;
+          if (col < dcols) *reinterpret_cast<uint4*>(orow + d0 + col) = f32x8_to_bf16(acc[g]);
+        }
+      }
+      if (lane == 0) own_flag[k0 + q] = epoch;
+    }
+  }
+}
+
+constexpr int APPLY_IDS = 8;  // ids per warp iteration of the apply kernel (balances the dense DSU id range)
+
+template <int WORLD>
+__global__ void __launch_bounds__(DP_THREADS) dp_sparse_apply_kernel(DpPeers peers, DpLayout lay, int rank, int V, int D,
+                                                                     unsigned int epoch, __nv_bfloat16* __restrict__ dW,
+                                                                     unsigned int* host_flag, GradFold fold) {
+  DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
+  // everything this rank owns was reduced by the previous kernel of this stream
+  if (blockIdx.x == 0 && threadIdx.x < WORLD && static_cast<int>(threadIdx.x) != rank) {
+    __threadfence_system();
+    st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_d[rank], epoch);
+  }
+  dp_wait_all(ctrl->arrive_d, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  if (dp_is_bad(ctrl)) {  // poison the first gradient row: grad-norm and loss checks trip at once
+    if (blockIdx.x == 0)
+      for (int j = threadIdx.x; j < D / 2; j += DP_THREADS) reinterpret_cast<uint32_t*>(dW)[j] = BF16X2_NAN;
+    return;
+  }
+  const uint32_t lane = threadIdx.x & 31;
+  const int gw = (blockIdx.x * DP_THREADS + threadIdx.x) >> 5;
+  const int nw = (gridDim.x * DP_THREADS) >> 5;
+  const float ps = fold_scale(fold);
+  float dsq = 0.f;
+  const int row_u4 = D / 8;
+  for (long long v0 = static_cast<long long>(gw) * APPLY_IDS; v0 < V; v0 += static_cast<long long>(nw) * APPLY_IDS) {
+    const long long v = v0 + lane;
+    unsigned int fl = epoch + 1u;
+    if (lane < APPLY_IDS && v < V) {
+      const unsigned int* fp =
+          reinterpret_cast<const unsigned int*>(peers.buf[v % WORLD] + lay.off_own_flag) + v / WORLD;
+      asm volatile("ld.global.L1::no_allocate.u32 %0, [%1];" : "=r"(fl) : "l"(fp));
+    }
+    unsigned pm = __ballot_sync(0xffffffffu, fl == epoch);
+    while (pm) {
+      const int q = __ffs(pm) - 1;
+      pm &= pm - 1;
+      const long long vq = v0 + q;
+      const uint4* src = reinterpret_cast<const uint4*>(
+          reinterpret_cast<const __nv_bfloat16*>(peers.buf[vq % WORLD] + lay.off_own_rows) +
+          static_cast<size_t>(vq / WORLD) * D);
+      uint4* dst = reinterpret_cast<uint4*>(dW + static_cast<size_t>(vq) * D);
+      for (int c0 = 0; c0 < row_u4; c0 += 32 * 8) {  // 8 x 16 bytes in flight per lane (D = 2048: one trip)
+        uint4 r[8], o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = c0 + j * 32 + static_cast<int>(lane);
+          if (c < row_u4) r[j] = ld_peer_u4(src + c);
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = c0 + j * 32 + static_cast<int>(lane);
+          if (c < row_u4) o[j] = dst[c];
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const int c = c0 + j * 32 + static_cast<int>(lane);
+          if (c >= row_u4) continue;
+          uint4 w;
+          w.x = pack_bf16x2(fmaf(ps, bf16lo(r[j].x), bf16lo(o[j].x)), fmaf(ps, bf16hi(r[j].x), bf16hi(o[j].x)));
+          w.y = pack_bf16x2(fmaf(ps, bf16lo(r[j].y), bf16lo(o[j].y)), fmaf(ps, bf16hi(r[j].y), bf16hi(o[j].y)));
+          w.z = pack_bf16x2(fmaf(ps, bf16lo(r[j].z), bf16lo(o[j].z)), fmaf(ps, bf16hi(r[j].z), bf16hi(o[j].z)));
+          w.w = pack_bf16x2(fmaf(ps, bf16lo(r[j].w), bf16lo(o[j].w)), fmaf(ps, bf16hi(r[j].w), bf16hi(o[j].w)));
+          dst[c] = w;
+          if (fold.sq)
+            dsq += (sq_of_bf16x2(w.x) - sq_of_bf16x2(o[j].x)) + (sq_of_bf16x2(w.y) - sq_of_bf16x2(o[j].y)) +
+                   (sq_of_bf16x2(w.z) - sq_of_bf16x2(o[j].z)) + (sq_of_bf16x2(w.w) - sq_of_bf16x2(o[j].w));
+        }
+      }
+    }
+  }
+  if (fold.sq) {
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) dsq += __shfl_xor_sync(0xffffffffu, dsq, o);
     if (lane == 0) fold.sq[gw] = dsq;

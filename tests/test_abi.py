@@ -63,8 +63,10 @@ def test_data_parallel_and_next_row_entry_points_validate_on_the_host():
     slice_rows = -(-V // 8)
     up = lambda x: -(-x // 256) * 256  # noqa: E731
     # [ctrl][dW_acc fp32][stage bf16 slice][slot u64 V][ids i32 R][rows bf16 R x D]
+    # [own_flag u32 ceil(V/8)][own_rows bf16 ceil(V/8) x D]  (two-phase sparse exchange)
     assert off.value == 4096 and nbytes.value == (4096 + up(V * D * 4) + up(slice_rows * D * 2) + up(V * 8)
-                                                  + up(R * 4) + up(R * D * 2))
+                                                  + up(R * 4) + up(R * D * 2) + up(slice_rows * 4)
+                                                  + up(slice_rows * D * 2))
     assert lib.ssi_b200_dp_buffer_bytes(V, D, 9, R, byref(nbytes), byref(off)) < 0  # one NVSwitch node: <= 8 ranks
     assert b"world size" in lib.ssi_b200_last_error()
     assert lib.ssi_b200_dp_exchange(None, 0, 2, V, D, R, 1, None, None, None, 0, None, None) < 0

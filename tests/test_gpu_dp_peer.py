@@ -79,6 +79,21 @@ def test_peer_exchange_world1_matches_oracle_and_plain_path():
         plain(*args)
         torch.cuda.synchronize()
         assert_grad_close(plain.weight.grad, outs[0][2].float(), "peer vs plain path")
+        # two-phase form of the sparse exchange (owner-reduce + apply; default only for world > 4), forced here
+        from ssi_b200 import _lib
+
+        _lib.set_option("sparse_two_phase", 1)
+        try:
+            two = []
+            for _ in range(2):
+                step.zero_grad()
+                step(*args)
+                torch.cuda.synchronize()
+                two.append(step.weight.grad.clone())
+        finally:
+            _lib.set_option("sparse_two_phase", -1)
+        assert torch.equal(two[0], two[1])
+        assert_grad_close(two[0], ref_dW, "dW, two-phase sparse exchange", elem_roundings=DW_ELEM_ROUNDINGS)
         step.close()
     finally:
         dist.destroy_process_group()
@@ -162,6 +177,21 @@ def _worker(rank, world, port, out):
         torch.cuda.synchronize()
         res["fold"] = (fold_sq.item(), None, step.weight.grad.cpu())
         step.close()
+        # two-phase sparse exchange (owner-reduce + apply), forced at world 2, with the fold riding along
+        from ssi_b200 import _lib as _l
+
+        _l.set_option("sparse_two_phase", 1)
+        try:
+            step = PathStep(inp["W"].to(dev), process_group=pg, exchange="peer", fold_scale_grads=True)
+            for _ in range(2):
+                step.zero_grad()
+                step(*args)
+                tp_sq = step.fold.sqnorm()
+            torch.cuda.synchronize()
+            res["twophase"] = (tp_sq.item(), None, step.weight.grad.cpu())
+            step.close()
+        finally:
+            _l.set_option("sparse_two_phase", -1)
         # the in-switch reduction (NVLS, multimem.ld_reduce) for the dense part, where the box has multicast support
         try:
             step = PathStep(inp["W"].to(dev), process_group=pg, exchange="nvls")
@@ -179,7 +209,7 @@ def _worker(rank, world, port, out):
             step.close()
         # every rank must hold the bit-identical summed gradient
         same = {}
-        for ex in ("peer", "nccl", "fold") + (("nvls",) if "nvls" in res else ()):
+        for ex in ("peer", "nccl", "fold", "twophase") + (("nvls",) if "nvls" in res else ()):
             g = res[ex][2].cuda().view(torch.int16).to(torch.int32)
             lo, hi = g.clone(), g.clone()
             dist.all_reduce(lo, op=dist.ReduceOp.MIN)
@@ -218,7 +248,7 @@ def _worker(rank, world, port, out):
             ref_loss, n_iter, ref_dH, ref_dW = oracle.train_step_path(inp["tokens"], inp["labels"], inp["X"],
                                                                       inp["dH0"], inp["W"])
             want = ref_loss.item() * n_iter
-            out["same_on_all_ranks"] = same["peer"] and same["nccl"] and same["fold"]
+            out["same_on_all_ranks"] = same["peer"] and same["nccl"] and same["fold"] and same["twophase"]
             out["loss_ok"] = (abs(res["peer"][0] - want) <= LOSS_RTOL * abs(want)
                               and abs(res["nccl"][0] - want) <= LOSS_RTOL * abs(want))
             lab_loc = inp["labels"][b0:b1]
@@ -234,6 +264,10 @@ def _worker(rank, world, port, out):
                 assert_grad_close(res["peer"][1].reshape(ref_dH[b0:b1].shape), ref_dH[b0:b1], "dH")
                 assert_grad_close(res["fold"][2], ref_dW / n_iter, "dW peer, scale_grads folded",
                                   elem_roundings=DW_ELEM_ROUNDINGS)
+                assert_grad_close(res["twophase"][2], ref_dW / n_iter, "dW peer, two-phase sparse exchange, folded",
+                                  elem_roundings=DW_ELEM_ROUNDINGS)
+                tp_own = res["twophase"][2].double().pow(2).sum().item()
+                assert abs(res["twophase"][0] - tp_own) <= 5e-5 * tp_own, ("two-phase sqnorm", res["twophase"][0])
                 if "nvls" in res:
                     assert same["nvls"] and res["nvls_repeatable"], "NVLS reduce: not identical on all ranks / runs"
                     assert_grad_close(res["nvls"][2], ref_dW, "dW peer + NVLS reduce", elem_roundings=DW_ELEM_ROUNDINGS)
