@@ -53,8 +53,11 @@ int64_t ssi_b200_launch_count(void);
  * it), "cta_group" (2 = CTA pairs, default), "wide_dw" / "wide_dx" (2 = 256x512 tiles for the long-K contractions,
  * default), "tail_split" (1 = a last wave that is at most half full runs as 256x256 halves, default), "shape_gate" (1 = the 256x256 kernel is enqueued as well and the device-side plan picks, default), "lockstep"
  * (k-blocks between sync points of dW / dX, default 64, 0 = off), "lockstep_k1" (1 = K1 sweeps its vocabulary tiles
- * in lockstep, default), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints",
- * "dw_hints", "dx_hints" (experiments; see profiles/r01_tuning_notes.md). */
+ * in lockstep, default), "exp_stash" (1 = single-pass K1 stashes exp(logit - ref) and the softmax normalisation is a
+ * per-row factor, default; 0 = stash logits + a separate softmax-grad pass), "sparse_two_phase" (data-parallel
+ * embedding exchange: -1 = two phases when world > 4, default; 0 / 1 force), "k1_group_m" (m-tiles per raster group
+ * of K1, 0 = all), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints", "dw_hints",
+ * "dx_hints" (experiments; see profiles/r01_tuning_notes.md). */
 int ssi_b200_set_option(const char* name, int64_t value);
 
 /* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. Workspaces must be 256-byte
@@ -231,6 +234,9 @@ int ssi_b200_embedding_grad_scatter_sorted(const void* dH, int64_t N, int64_t V,
  *                       list (emb_rows bf16, slot[id] = epoch | index); then every rank adds, for every id present on
  *                       any rank, the ranks' rows in rank order in fp32 to its bf16 dW row (one rounding, identical on
  *                       all ranks).  Must follow this step's dp_exchange in stream order.  N <= max_rows.
+ *                       world > 4 (option "sparse_two_phase": -1 auto, 0, 1): two phases -- the owner of an id
+ *                       (id % world) sums the ranks' rows once (fp32, rank order, one rounding to bf16), every rank
+ *                       then adds the reduced row: one row pulled per id instead of one per holder.
  */
 int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, int64_t max_rows, size_t* bytes,
                              size_t* dw_acc_offset);

@@ -2,7 +2,7 @@
 // one NVSwitch node).  Every rank exposes one exchange buffer to its peers (CUDA IPC):
 //
 //   [ctrl 4 KiB: flags, token counts]  [dW_acc fp32 V x D]  [stage bf16 Vs x D]
-//   [slot u64 V]  [emb_ids int32 cap]  [emb_rows bf16 cap x D]
+//   [slot u64 V]  [emb_ids int32 cap]  [emb_rows bf16 cap x D]  [own_flag u32 Vs]  [own_rows bf16 Vs x D]
 //
 // dW_acc is where the rank's own dW contractions accumulate in fp32; Vs = ceil(V / world) is the height of the
 // vocabulary slice a rank owns.  The step has THREE exchanges, in the order a training step produces their inputs:
@@ -14,8 +14,10 @@
 //   sparse exchange    (embedding part; it only exists after the decoder backward has produced dH0): every rank
 //                      segment-reduces its dH0 rows by id into a compact list (scatter.cuh, SCAT_COMPACT: emb_rows,
 //                      emb_ids, slot[id] = epoch | index) and dp_sparse_add_kernel then adds, for every id present
-//                      on any rank, the ranks' rows in rank order (fp32) to the bf16 gradient row -- U x D x 2 bytes
-//                      per rank instead of a second dense V x D pass.
+//                      on any rank, the ranks' rows in rank order (fp32) to the bf16 gradient row -- the other ranks'
+//                      distinct rows per rank instead of a second dense V x D pass.  For world > 4 in two phases
+//                      (dp_sparse_reduce_kernel + dp_sparse_apply_kernel at the end of this file): the owner of an id
+//                      (id % world) sums its rows once, every rank then adds the reduced row.
 //
 // The dense exchange is two small-footprint kernels (no shared memory, 256 threads per block) that co-reside with the
 // persistent tensor-core CTAs of the dX contraction still running on the main stream, so the transfer hides behind
