@@ -169,3 +169,50 @@ def test_fold_workspace_size_is_device_independent():
     assert _lib.load().ssi_b200_grad_fold_workspace_bytes(64, 64, ctypes.byref(b)) == 0
     assert b.value == 4 * (4 * 4096)
     assert _lib.load().ssi_b200_grad_fold_workspace_bytes(0, 64, ctypes.byref(b)) < 0
+
+
+def test_install_returns_a_ce_with_chunked_output_loss_when_torchtune_is_importable(monkeypatch):
+    """ssi/trainer.py:303 checks ``isinstance(self.loss_fn, CEWithChunkedOutputLoss)``: with torchtune importable the
+    object install() returns must pass it.  torchtune itself cannot be imported here (torchao is missing), so the
+    module path is stubbed with the REFERENCE's own class loaded by file path when the checkout is present, else with
+    a stand-in of the same constructor (tt/torchtune/modules/loss/ce_chunked_output_loss.py:30-33)."""
+    import importlib.util
+    import os
+    import sys
+    import types
+
+    ref = "/root/reference/third_party/torchtune/torchtune/modules/loss/ce_chunked_output_loss.py"
+    if os.path.exists(ref):
+        spec = importlib.util.spec_from_file_location("_ref_ce_chunked", ref)
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        ref_cls = mod.CEWithChunkedOutputLoss
+    else:
+        class ref_cls(nn.Module):  # noqa: N801
+            def __init__(self, num_output_chunks: int = 8, ignore_index: int = -100):
+                super().__init__()
+                self.num_output_chunks = num_output_chunks
+                self.ignore_index = ignore_index
+
+    tt, ttm, ttl = types.ModuleType("torchtune"), types.ModuleType("torchtune.modules"), types.ModuleType(
+        "torchtune.modules.loss")
+    ttl.CEWithChunkedOutputLoss = ref_cls
+    tt.modules, ttm.loss = ttm, ttl
+    for name, m in (("torchtune", tt), ("torchtune.modules", ttm), ("torchtune.modules.loss", ttl)):
+        monkeypatch.setitem(sys.modules, name, m)
+
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.tok_embeddings = nn.Embedding(50, 64, dtype=torch.bfloat16)
+            self.output = None
+            self.chunks = None
+
+        def set_num_output_chunks(self, n):
+            self.chunks = n
+
+    m = M()
+    loss_fn = ssi_b200.install(m, num_output_chunks=4, ignore_index=-7)
+    assert isinstance(loss_fn, ref_cls) and isinstance(loss_fn, ssi_b200.FusedLinearCrossEntropyLoss)
+    assert loss_fn.num_output_chunks == 4 and loss_fn.ignore_index == -7 and m.chunks == 4
+    assert list(loss_fn.state_dict().keys()) == [] and loss_fn.tied_module is m.tok_embeddings
