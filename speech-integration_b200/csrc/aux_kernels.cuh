@@ -67,33 +67,59 @@ __global__ void __launch_bounds__(1024) compact_scan_kernel(const int64_t* __res
                                                             int chunk_t_max = 0, int chunks_max = 0,
                                                             int d_tiles = 0, int64_t* n_valid_out = nullptr,
                                                             int cg = 1, int half_tail = 0) {
-  __shared__ int s_sum[1024];
+  // Every warp owns one contiguous segment of the rows (a multiple of 32) and walks it 32 rows at a time with
+  // coalesced loads, four of them in flight: positions come from ballots, so the compaction stays stable.
+  __shared__ int s_wsum[32];
   __shared__ int s_chunk_t;
-  const int per = (n + 1023) / 1024;
-  const int b = threadIdx.x * per;
-  const int e = min(b + per, n);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  const int wseg = ((n + 31) / 32 + 31) / 32 * 32;
+  const int b = min(warp * wseg, n);
+  const int e = min(b + wseg, n);
   int a = 0;
-  for (int i = b; i < e; ++i) a += (labels[i] != ignore_index);
-  s_sum[threadIdx.x] = a;
-  __syncthreads();
-  for (int off = 1; off < 1024; off <<= 1) {
-    int v = 0;
-    if (threadIdx.x >= off) v = s_sum[threadIdx.x - off];
-    __syncthreads();
-    s_sum[threadIdx.x] += v;
-    __syncthreads();
+  for (int i0 = b; i0 < e; i0 += 128) {
+    long long l[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 32 + lane;
+      l[u] = (i < e) ? labels[i] : ignore_index;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) a += (l[u] != ignore_index);
   }
-  int run = (threadIdx.x == 0) ? 0 : s_sum[threadIdx.x - 1];
-  const int n_valid = s_sum[1023];
-  for (int i = b; i < e; ++i) {
-    const long long l = labels[i];
-    if (l != ignore_index) {
-      pos[i] = run;
-      idx[run] = i;
-      labels_c[run] = l;
-      ++run;
-    } else {
-      pos[i] = -1;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) s_wsum[warp] = a;
+  __syncthreads();
+  int run = 0, n_valid = 0;
+  for (int w = 0; w < 32; ++w) {
+    const int c = s_wsum[w];
+    if (w < warp) run += c;
+    n_valid += c;
+  }
+  for (int i0 = b; i0 < e; i0 += 128) {
+    long long l[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 32 + lane;
+      l[u] = (i < e) ? labels[i] : ignore_index;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 32 + lane;
+      const bool ok = l[u] != ignore_index;
+      const unsigned m = __ballot_sync(0xffffffffu, ok);
+      if (i < e) {
+        if (ok) {
+          const int r = run + __popc(m & lt_mask);
+          pos[i] = r;
+          idx[r] = i;
+          labels_c[r] = l[u];
+        } else {
+          pos[i] = -1;
+        }
+      }
+      run += __popc(m);
     }
   }
   for (int i = n_valid + threadIdx.x; i < n_pad; i += 1024) labels_c[i] = ignore_index;
