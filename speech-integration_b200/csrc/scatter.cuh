@@ -91,7 +91,10 @@ __device__ __forceinline__ void sort_grid_barrier(unsigned int* ctr, unsigned in
 // [digit][block] -> grid barrier -> every block scans ghist (digit-major, block-minor) for its bases -> scatter ->
 // grid barrier.  Buffers and ghist are read with ld.global.cg: they are rewritten inside the kernel.
 constexpr int SORT_MAX_BLOCKS = 64;
-constexpr int SORT_KEYS_PER_BLOCK = 2048;
+#ifndef SSI_SORT_KEYS_PER_BLOCK
+#define SSI_SORT_KEYS_PER_BLOCK 2048
+#endif
+constexpr int SORT_KEYS_PER_BLOCK = SSI_SORT_KEYS_PER_BLOCK;
 
 __global__ void __launch_bounds__(SORT_THREADS, 1) sort_grid_kernel(const int64_t* __restrict__ ids, int n,
                                                                     long long V, int passes, uint32_t* kbuf0,
@@ -277,7 +280,10 @@ __global__ void __launch_bounds__(SORT_THREADS, 1) sort_grid_kernel(const int64_
 
 // ---------------------------------------------------------------------------------------------------
 constexpr int SCAT_COLS = 32 * 8;  // columns per slab (blockIdx.y): one 16-byte group per lane and row
-constexpr int SCAT_AHEAD = 4;      // rows in flight per warp ahead of the one being accumulated
+#ifndef SSI_SCAT_AHEAD
+#define SSI_SCAT_AHEAD 3
+#endif
+constexpr int SCAT_AHEAD = SSI_SCAT_AHEAD;  // rows in flight per warp ahead of the one being accumulated
 constexpr int SCAT_THREADS = 128;
 enum ScatMode { SCAT_DENSE_BF16 = 0, SCAT_DENSE_F32 = 1, SCAT_COMPACT = 2 };
 
@@ -369,8 +375,13 @@ __device__ __forceinline__ void emit_run(const ScatOut& o, uint32_t key, int ur,
   }
 }
 
+// 8 resident blocks of 128 threads per SM (64 registers) and 3 rows in flight per warp measured best on B200
+// (profiles/r02_k3_variants.txt): more rows in flight cost occupancy and lose
+#ifndef SSI_SCAT_MINBLOCKS
+#define SSI_SCAT_MINBLOCKS 8
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(SCAT_THREADS) scatter_reduce_kernel(const __nv_bfloat16* __restrict__ dH,
+__global__ void __launch_bounds__(SCAT_THREADS, SSI_SCAT_MINBLOCKS) scatter_reduce_kernel(const __nv_bfloat16* __restrict__ dH,
                                                              const uint32_t* __restrict__ skeys,
                                                              const uint32_t* __restrict__ srows,
                                                              const int* __restrict__ urank, int n, uint32_t V, int D,
