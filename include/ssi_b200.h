@@ -56,7 +56,8 @@ int64_t ssi_b200_launch_count(void);
  * in lockstep, default), "exp_stash" (1 = single-pass K1 stashes exp(logit - ref) and the softmax normalisation is a
  * per-row factor, default; 0 = stash logits + a separate softmax-grad pass), "sparse_two_phase" (data-parallel
  * embedding exchange: -1 = two phases when world > 4, default; 0 / 1 force), "k1_group_m" (m-tiles per raster group
- * of K1, 0 = all), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints", "dw_hints",
+ * of the single-pass K1, default 64, 0 = all) and "k1_store_first" (1 = evict-first L2 policy on its E-tile stores,
+ * default), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints", "dw_hints",
  * "dx_hints" (experiments; see profiles/r01_tuning_notes.md). */
 int ssi_b200_set_option(const char* name, int64_t value);
 

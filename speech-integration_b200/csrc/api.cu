@@ -326,7 +326,11 @@ struct Tune {
   // the dX epilogue and the X rows of dW (no pass over the block); 0 = stash logits + separate softmax-grad HBM pass
   int exp_stash = 1;
   int sparse_two_phase = -1;  // sparse (embedding) exchange: 1 = owner-reduce + apply, 0 = one phase, -1 = auto (world > 4)
-  int k1_group_m = 0;  // K1: m-tiles (128 rows) per raster group, 0 = the whole row chunk (GemmParams::lse_group_m)
+  // single-pass K1: m-tiles (128 rows) per raster group, 0 = the whole row chunk (GemmParams::lse_group_m), and
+  // evict-first L2 policy on its E-tile stores.  Together they keep the X rows of a group L2-resident next to the
+  // 4.35 GB write stream: DRAM reads per 16k-row chunk 4.3 -> 2.0 GB, step -0.75 % (profiles/r02_ab_k1_l2hints*.txt)
+  int k1_group_m = 64;
+  int k1_store_first = 1;
 };
 // The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
 // thread-local SNAPSHOT under the mutex (TuneScope), so one call never sees half of an update.
@@ -352,6 +356,7 @@ Tune& global_tune() {
     if (const char* e = getenv("SSI_B200_WIDE_DX")) x.wide_dx = atoi(e) == 1 ? 1 : 2;
     if (const char* e = getenv("SSI_B200_EXP_STASH")) x.exp_stash = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_K1_GROUP_M")) x.k1_group_m = atoi(e);
+    if (const char* e = getenv("SSI_B200_K1_STORE_FIRST")) x.k1_store_first = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_SPARSE_TWO_PHASE")) x.sparse_two_phase = atoi(e);
     return x;
   }();
@@ -585,6 +590,7 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "wide_dx")) t.wide_dx = (value == 1) ? 1 : 2;
   else if (!strcmp(name, "exp_stash")) t.exp_stash = value ? 1 : 0;
   else if (!strcmp(name, "k1_group_m")) t.k1_group_m = value > 0 ? static_cast<int>(value) : 0;
+  else if (!strcmp(name, "k1_store_first")) t.k1_store_first = value ? 1 : 0;
   else if (!strcmp(name, "sparse_two_phase")) t.sparse_two_phase = value < 0 ? -1 : (value ? 1 : 0);
   else return fail(-1, "unknown option '%s'", name);
   return 0;
@@ -647,7 +653,6 @@ int ssi_b200_lmhead_ce_fwd(const void* X, const void* W, const int64_t* labels, 
   p.tiles_n = 1;
   p.k_blocks = static_cast<int>(D / ssi::BK);
   p.group_m = f.tiles_m;  // all m-tiles of one split run together: they stream the same W tiles through L2
-  p.lse_group_m = tune().k1_group_m;
   p.labels = labels_c;
   p.ignore_index = ignore_index;
   p.n_rows = static_cast<int>(f.n_pad);
@@ -941,7 +946,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       p.tiles_m = f.t_max, p.tiles_n = 1, p.k_blocks = static_cast<int>(D / ssi::BK);
       p.group_m = f.t_max;
       p.lse_group_m = tune().k1_group_m;
-      p.store_policy = tune().store_hint ? ssi::kEvictFirst : 0ull;
+      p.store_policy = (tune().store_hint || tune().k1_store_first) ? ssi::kEvictFirst : 0ull;
       p.labels = labels_c, p.ignore_index = ignore_index;
       p.n_rows = static_cast<int>(f.n_pad), p.vocab = static_cast<int>(V), p.col0 = 0;
       p.vtiles_per_split = f.vtiles_total, p.vtiles_total = f.vtiles_total;

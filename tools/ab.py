@@ -19,7 +19,7 @@ from ssi_b200 import _lib, synth  # noqa: E402
 from ssi_b200.step import PathStep  # noqa: E402
 
 DEFAULTS = {"g_cap_mib": 4608, "g_tiles": 0, "group_m_grad": 16, "group_m_dw": 1, "group_m_dx": 1, "store_hint": 0, "k1_hints": 0, "dw_hints": 0, "dx_hints": 0, "lockstep": 64,
-            "cta_group": 2, "wide_dw": 2, "wide_dx": 2, "tail_split": 1, "lockstep_k1": 1, "shape_gate": 1, "exp_stash": 1, "k1_group_m": 0, "sparse_two_phase": -1}
+            "cta_group": 2, "wide_dw": 2, "wide_dx": 2, "tail_split": 1, "lockstep_k1": 1, "shape_gate": 1, "exp_stash": 1, "k1_group_m": 64, "k1_store_first": 1, "sparse_two_phase": -1}
 
 
 def main():
