@@ -216,3 +216,33 @@ def test_install_returns_a_ce_with_chunked_output_loss_when_torchtune_is_importa
     assert isinstance(loss_fn, ref_cls) and isinstance(loss_fn, ssi_b200.FusedLinearCrossEntropyLoss)
     assert loss_fn.num_output_chunks == 4 and loss_fn.ignore_index == -7 and m.chunks == 4
     assert list(loss_fn.state_dict().keys()) == [] and loss_fn.tied_module is m.tok_embeddings
+
+
+def test_global_batch_is_the_same_for_every_world_size():
+    """bench.py slices ONE global batch by rank: the slices of any world size concatenate to the
+    batch a single process sees, tokens and labels from the global generator, X / dH0 seeded per sequence."""
+    cfg = synth.CONFIGS["c1"]
+    dev = torch.device("cpu")
+    tok, lab, X, dH = synth.global_batch_rows(cfg, 0, cfg.batch, dev, hidden=64)
+    for world in (2, 4, 8):
+        parts = []
+        for r in range(world):
+            b0, b1 = ddist.shard_rows(cfg.batch, r, world)
+            parts.append(synth.global_batch_rows(cfg, b0, b1, dev, hidden=64))
+        assert torch.equal(torch.cat([p[0] for p in parts]), tok) and torch.equal(torch.cat([p[1] for p in parts]), lab)
+        assert torch.equal(torch.cat([p[2] for p in parts]), X) and torch.equal(torch.cat([p[3] for p in parts]), dH)
+
+
+def test_install_rejects_option_combinations_that_have_no_kernel():
+    class M(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.tok_embeddings = nn.Embedding(50, 64, dtype=torch.bfloat16)
+            self.output = None
+
+    with pytest.raises(ValueError):
+        ssi_b200.install(M(), mode="recompute", fold_scale_grads=True)      # the fold lives in single-pass kernels
+    with pytest.raises(ValueError):
+        ssi_b200.install(M(), replace_embedding=False, fold_scale_grads=True)
+    with pytest.raises(ValueError):
+        ssi_b200.install(M(), mode="bogus")
