@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 112
+#define SSI_B200_ABI_VERSION 113
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -287,6 +287,33 @@ int ssi_b200_rmsnorm_fwd(const void* x, const void* scale, float eps, int64_t N,
 int ssi_b200_rmsnorm_bwd_workspace_bytes(int64_t N, int64_t D, size_t* bytes);
 int ssi_b200_rmsnorm_bwd(const void* dy, const void* x, const void* scale, const float* rstd, int64_t N, int64_t D,
                          void* dx, float* dscale, void* ws, size_t ws_bytes, void* stream);
+
+/*
+ * ssi_b200_rmsnorm_bwd without the `ws` argument.  This one has no counterpart in the reference (which leaves all
+ * memory management to PyTorch); it exists for hosts of this C ABI that cannot obtain device scratch at the point
+ * where the backward runs:
+ *   - a trainer or server that handed the whole GPU to its own arena at start-up, so that cudaMalloc has nothing
+ *     left to give (and no torch caching allocator sits behind the binding to ask instead);
+ *   - a step that keeps several streams busy (the tied-gradient exchange beside the decoder backward): cudaMalloc
+ *     and cudaFree stall every stream of the device while they run, so allocating mid-step costs the overlap.
+ * The per-warp partial rows of dscale therefore live in a fixed array inside the library image itself:
+ * 148 x 2 x 8 x SSI_B200_RMSNORM_BWD_STATIC_MAX_D floats = 18.5 MiB, which every GPU that loads the library holds
+ * until the process exits whether this entry point is used or not.  Consequences a caller must know:
+ *   - D > SSI_B200_RMSNORM_BWD_STATIC_MAX_D is refused (negative return, text in ssi_b200_last_error()); use
+ *     ssi_b200_rmsnorm_bwd with your own workspace for wider rows.  N is not limited by the array.
+ *   - The FIRST call on each device (with that device current) also looks up where the array sits on that device.
+ *     That is set-up work: make this first call before you begin any stream capture on that device.
+ *   - All calls on one GPU share the one array, and it keeps whatever the previous call left in it.  The kernels
+ *     overwrite every partial row they later read, so nothing needs clearing between calls -- but two calls whose
+ *     kernels can be on the GPU at the same time (different streams without an ordering between them, or two host
+ *     threads) would overwrite each other's partial sums.  Order them on one stream or with events.
+ *   - The call itself allocates nothing and frees nothing: no cudaMalloc / cudaFree, no library routine that
+ *     allocates.  dy, x, scale, rstd, dx and dscale are the caller's, exactly as for ssi_b200_rmsnorm_bwd, and the
+ *     results are bit-identical to that entry point's.
+ */
+#define SSI_B200_RMSNORM_BWD_STATIC_MAX_D 2048
+int ssi_b200_rmsnorm_bwd_static(const void* dy, const void* x, const void* scale, const float* rstd, int64_t N,
+                                int64_t D, void* dx, float* dscale, void* stream);
 
 /*
  * ssi_b200_label_shift_count plus the token-type histogram of ssi/train_utils.py:150-165 in the same pass, all

@@ -1617,6 +1617,84 @@ int ssi_b200_rmsnorm_bwd(const void* dy, const void* x, const void* scale, const
   return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// RMSNorm backward for callers that have no device memory to give us and may not ask the driver for any.
+//
+// ssi_b200_rmsnorm_bwd needs one fp32 partial row of dscale per warp of its grid, and expects the caller to bring
+// that as `ws`.  A host that binds this C ABI without torch's caching allocator behind it does not always have
+// such a buffer: a trainer or server that carved the whole GPU into its own arena at start-up has nothing left
+// for cudaMalloc to hand out, and one that runs several streams (here: the tied-gradient exchange beside the
+// decoder backward) cannot afford cudaMalloc / cudaFree in the middle of a step, because both stall every stream
+// of the device while they run.  For those callers the partial rows live in the array below, which is part of
+// the loaded library image: the driver materialises it once per GPU when the module is loaded there and keeps
+// it until the process exits (18.5 MiB per GPU, used or not).
+//
+// `g_rms_bwd_static_scratch` as written in HOST code is only the host-side handle of that symbol, not a device
+// address, so the launch below never passes it directly: rms_bwd_static_scratch() asks the runtime for the
+// address the array has on the CURRENT device (cudaGetSymbolAddress) and remembers it per device ordinal.
+// ---------------------------------------------------------------------------------------------------
+namespace {
+constexpr int RMS_BWD_STATIC_MAX_D = 2048;  // == SSI_B200_RMSNORM_BWD_STATIC_MAX_D in the header
+constexpr size_t RMS_BWD_STATIC_FLOATS = static_cast<size_t>(148) * RMS_BWD_BLOCKS_PER_SM * 8 * RMS_BWD_STATIC_MAX_D;
+}  // namespace
+
+static __device__ __align__(256) float g_rms_bwd_static_scratch[RMS_BWD_STATIC_FLOATS];
+
+namespace {
+// Device address of the array above on the current device; looked up on the first call per device (set-up work:
+// the runtime may load the module on that device at this point), cached afterwards.
+int rms_bwd_static_scratch(int dev, float** out) {
+  static float* ptrs[64];
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lk(mu);
+  if (!ptrs[dev]) {
+    void* p = nullptr;
+    SSI_CUDA(cudaGetSymbolAddress(&p, g_rms_bwd_static_scratch));
+    SSI_CHECK_ARG(p && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "static scratch of device %d is not usable", dev);
+    ptrs[dev] = static_cast<float*>(p);
+  }
+  *out = ptrs[dev];
+  return 0;
+}
+}  // namespace
+
+int ssi_b200_rmsnorm_bwd_static(const void* dy, const void* x, const void* scale, const float* rstd, int64_t N,
+                                int64_t D, void* dx, float* dscale, void* stream) {
+  SSI_CHECK_ARG(dy && x && scale && rstd && dx && dscale, "null pointer argument");
+  SSI_CHECK_ARG(N >= 1 && D >= 8 && D % 8 == 0 && N < (int64_t(1) << 31), "bad shape N=%lld D=%lld", (long long)N,
+                (long long)D);
+  SSI_CHECK_ARG(D <= RMS_BWD_STATIC_MAX_D,
+                "D=%lld exceeds the %d columns the built-in scratch of ssi_b200_rmsnorm_bwd_static holds; use "
+                "ssi_b200_rmsnorm_bwd with a caller-provided workspace",
+                (long long)D, RMS_BWD_STATIC_MAX_D);
+  DeviceInfo* di = nullptr;
+  if (int r = device_info(&di)) return r;
+  float* partial = nullptr;
+  if (int r = rms_bwd_static_scratch(di->dev, &partial)) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int sms = di->sms < 148 ? di->sms : 148;
+  const int grid = sms * RMS_BWD_BLOCKS_PER_SM;
+  const int nparts = grid * 8;  // nparts * D <= RMS_BWD_STATIC_FLOATS by the checks above
+  const int row_u4 = static_cast<int>(D / 8);
+  const int maxj = (row_u4 + 31) / 32;
+  ProfScope ps(CAT_AUX, st);
+  // Every warp of the grid overwrites its whole partial row, rows of an earlier call included, so nothing in the
+  // shared array has to be cleared between calls.
+#define SSI_RMS_BWD_STATIC(J)                                                                                        \
+  ssi::rmsnorm_bwd_kernel<J><<<grid, 256, 0, st>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(x),     \
+                                                   static_cast<const uint4*>(scale), rstd, static_cast<int>(N),    \
+                                                   row_u4, static_cast<uint4*>(dx), partial)
+  if (maxj <= 2) SSI_RMS_BWD_STATIC(2);
+  else if (maxj <= 4) SSI_RMS_BWD_STATIC(4);
+  else SSI_RMS_BWD_STATIC(8);
+#undef SSI_RMS_BWD_STATIC
+  SSI_LAUNCH_OK("rmsnorm_bwd_static");
+  ssi::rmsnorm_dscale_reduce_kernel<<<static_cast<int>(ceil_div(D, 32)), 256, 0, st>>>(partial, nparts,
+                                                                                      static_cast<int>(D), dscale);
+  SSI_LAUNCH_OK("rmsnorm_dscale_reduce_static");
+  return 0;
+}
+
 int ssi_b200_label_shift_count_types(const int64_t* labels, const int64_t* tokens, int64_t B, int64_t S,
                                      int64_t ignore_index, const int64_t* range_lo, const int64_t* range_hi,
                                      int n_ranges, int64_t pad_idx, int64_t* labels_out, int64_t* counts,

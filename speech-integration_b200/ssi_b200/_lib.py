@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 112
+ABI_VERSION = 113
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -106,6 +106,10 @@ SYMBOLS = {
     "ssi_b200_rmsnorm_bwd": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p],
+    ),
+    "ssi_b200_rmsnorm_bwd_static": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_void_p, c_void_p, c_void_p],
     ),
     "ssi_b200_label_shift_count_types": (
         c_int,
