@@ -166,8 +166,11 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
                                    float* dW_acc, void* ws, size_t ws_bytes, void* stream,
                                    const ssi_b200_fwd_grad_opts* opts);
 
-/* Synchronising debug query: *gave_up != 0 if a lockstep wait inside the last single-pass call on `ws` timed out
- * (part of the persistent grid was not resident; the kernels then ran un-throttled -- slower, still correct). */
+/* Synchronising debug query on the last single-pass call that used `ws`: bit 0 of *gave_up is set if a lockstep wait
+ * timed out (part of the persistent grid was not resident; the kernels then ran un-throttled -- slower, still
+ * correct); bit 1 if the exp-stash form overflowed on some row -- a logit more than ~88 nats above the largest of the
+ * row's first 256 vocabulary columns: that row's loss is inf and the gradients of the call are NaN (never silently
+ * wrong); rerun with option "exp_stash" = 0, which has no such range limit. */
 int ssi_b200_single_pass_lockstep_status(const void* ws, int64_t N, int64_t V, int64_t D, int* gave_up);
 
 /*

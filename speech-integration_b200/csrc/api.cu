@@ -475,7 +475,7 @@ struct SpPlan {
   CompactWs cw;
   size_t off_m, off_l, off_z, off_lse_c, off_loss_c, off_bl, off_bc, off_sync, off_rstd, off_dsp, off_dxc, off_s, bytes;
   // exp-stash form: pilot reference, per-row factor, scaled X rows, workspace of the label-keyed onehot scatter
-  size_t off_ref2, off_rowscale, off_xs, off_lscat, lscat_bytes;
+  size_t off_ref2, off_rowscale, off_labw, off_xs, off_lscat, lscat_bytes;
 };
 constexpr size_t SYNC_AREA_BYTES = 4096;
 constexpr int NORM_BWD_BLOCKS = 148 * 2;            // grid of the fused norm-backward scatter
@@ -514,6 +514,7 @@ int plan_single_pass(int64_t N, int64_t V, int64_t D, SpPlan* out) {
   f.off_dxc = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
   f.off_ref2 = o, o += align_up(items * ssi::BM * sizeof(float), 256);
   f.off_rowscale = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);
+  f.off_labw = o, o += align_up(static_cast<size_t>(f.n_pad) * sizeof(float), 256);  // 1 - p_label per compact row
   f.off_xs = o, o += align_up(static_cast<size_t>(f.n_pad) * D * 2, 1024);
   f.lscat_bytes = plan_scatter(f.n_pad, V, D).bytes;
   f.off_lscat = o, o += align_up(f.lscat_bytes, 1024);
@@ -889,6 +890,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
   void* S = wsb + f.off_s;
   float* ref2 = reinterpret_cast<float*>(wsb + f.off_ref2);
   float* rowscale_c = reinterpret_cast<float*>(wsb + f.off_rowscale);
+  float* labw_c = reinterpret_cast<float*>(wsb + f.off_labw);
   void* Xs = wsb + f.off_xs;
   const bool estash = tune().exp_stash != 0;
   const int d_tiles = static_cast<int>(ceil_div(D, ssi::BN));
@@ -896,7 +898,8 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
   const int64_t* nvt = n_valid_total ? n_valid_total : n_valid;
   unsigned int* sync_area = reinterpret_cast<unsigned int*>(wsb + f.off_sync);
   const int lockstep = tune().lockstep;
-  if (lockstep > 0 || tune().lockstep_k1) SSI_CUDA(cudaMemsetAsync(sync_area, 0, SYNC_AREA_BYTES, st));
+  // word 1022 = exp-stash overflow flag, word 1023 = lockstep gave up, the rest = lockstep counters
+  if (lockstep > 0 || tune().lockstep_k1 || estash) SSI_CUDA(cudaMemsetAsync(sync_area, 0, SYNC_AREA_BYTES, st));
 
   {
     ProfScope ps(CAT_AUX, st);
@@ -974,7 +977,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       if (ch == 0 && pre_grad_event) SSI_CUDA(cudaStreamWaitEvent(st, static_cast<cudaEvent_t>(pre_grad_event), 0));
       ProfScope ps(CAT_AUX, st);
       ssi::exp_combine_kernel<<<64, 256, 0, st>>>(ref2, part_l, part_z, cplan, grad_hint, nvt, lse_c, loss_c,
-                                                  rowscale_c);
+                                                  rowscale_c, labw_c, sync_area + 1022);
       SSI_LAUNCH_OK("exp_combine");
       ssi::scale_rows_kernel<<<di->sms * 4, 256, 0, st>>>(static_cast<const uint4*>(Xc), rowscale_c, cplan,
                                                           static_cast<int>(D / 8), static_cast<uint4*>(Xs));
@@ -1020,9 +1023,11 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
         return r;
       if (ch == f.chunks_max - 1) {
         if (estash) {
-          // the onehot term of dW, exact in fp32: dW_acc[v, :] -= g * sum of the X_c rows whose label is v
+          // the label column's term of dW in fp32: dW_acc[v, :] -= g * sum over the X_c rows whose label is v of
+          // (1 - p_label[row]) * X_c[row, :]
           ssi::ScatOut o = dense_out(dW_acc);
           o.scale_num = grad_hint, o.scale_den = reinterpret_cast<const long long*>(nvt), o.scale_sign = -1.f;
+          o.row_w = labw_c;
           if (int r = embedding_grad_scatter_impl<ssi::SCAT_DENSE_F32>(Xc, labels_c, f.n_pad, V, D, o,
                                                                        wsb + f.off_lscat, f.lscat_bytes, stream, 3,
                                                                        CAT_SOFTMAX))
@@ -1063,7 +1068,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
       ssi::dx_label_term_kernel<<<di->sms * 8, 256, 0, st>>>(static_cast<uint4*>(dXc), labels_c,
                                                              static_cast<int>(f.n_pad), row_u4,
                                                              static_cast<const uint4*>(W), static_cast<int>(V),
-                                                             grad_hint, nvt);
+                                                             grad_hint, nvt, labw_c);
       SSI_LAUNCH_OK("dx_label_term");
     }
     const int maxj = (row_u4 + 31) / 32;
@@ -1087,7 +1092,7 @@ int ssi_b200_lmhead_ce_fwd_grad_ex(const void* X, const void* W, const int64_t* 
   }
   ssi::dx_scatter_bf16_kernel<<<di->sms * 8, 256, 0, st>>>(
       static_cast<const uint4*>(dXc), pos, static_cast<int>(N), static_cast<int>(D / 8), static_cast<uint4*>(dX),
-      estash ? static_cast<const uint4*>(W) : nullptr, labels_c, static_cast<int>(V), grad_hint, nvt);
+      estash ? static_cast<const uint4*>(W) : nullptr, labels_c, static_cast<int>(V), grad_hint, nvt, labw_c);
   SSI_LAUNCH_OK("dx_scatter");
   return 0;
 }
@@ -1775,10 +1780,10 @@ int ssi_b200_single_pass_lockstep_status(const void* ws, int64_t N, int64_t V, i
   SSI_CHECK_ARG(ws && gave_up, "null pointer argument");
   SpPlan f;
   if (int r = plan_single_pass(N, V, D, &f)) return r;
-  unsigned int v = 0;
-  SSI_CUDA(cudaMemcpy(&v, static_cast<const char*>(ws) + f.off_sync + 1023 * sizeof(unsigned int), sizeof(v),
+  unsigned int v[2] = {0, 0};  // {exp-stash overflow, lockstep gave up}
+  SSI_CUDA(cudaMemcpy(v, static_cast<const char*>(ws) + f.off_sync + 1022 * sizeof(unsigned int), sizeof(v),
                       cudaMemcpyDeviceToHost));
-  *gave_up = static_cast<int>(v);
+  *gave_up = (v[1] ? 1 : 0) | (v[0] ? 2 : 0);
   return 0;
 }
 

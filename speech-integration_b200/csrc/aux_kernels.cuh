@@ -429,13 +429,18 @@ __device__ __forceinline__ uint4 f32x8_to_bf16(const float (&f)[8]) {
 //   exp_combine_kernel   lse = (ref2 + log2 L) ln2, loss = lse - z_label, rowscale[r] = g / L[r]
 //   scale_rows_kernel    Xs[r, :] = bf16(rowscale[r] * X_c[r, :]): the rows dW = E^T Xs contracts with
 //   dX contraction       rowscale[r] * (E W)[r, :] in its epilogue.
-// The onehot term -- the dominant part of every row of the gradient -- is exact arithmetic on the operands instead
-// of a bf16-rounded matrix element:
-//   dX[r, :] -= g * W[label_r, :]          while the compact rows go back to their positions (dx_scatter_bf16_kernel,
-//                                          or dx_label_term_kernel in place before the fused norm backward)
-//   dW_acc[v, :] -= g * sum_{label_r = v} X_c[r, :]   by the sorted fp32 segmented reduction of scatter.cuh, keyed by
-//                                          the labels (no atomics: bit-identical run to run).
-// No pass over the [rows, V] block.
+// The LABEL column of every row -- softmax and onehot together, g (p_label - 1), the dominant and for a confident
+// row nearly cancelling part of the gradient -- never goes through a bf16 matrix element: K1 stashes 0 there (the
+// label's exponential still counts in L), exp_combine_kernel forms labw[r] = 1 - p_label = (L - e_label) / L in fp32,
+// and the term is exact arithmetic on the operands:
+//   dX[r, :] -= g * labw[r] * W[label_r, :]   while the compact rows go back to their positions
+//                                          (dx_scatter_bf16_kernel, or dx_label_term_kernel in place before the fused
+//                                          norm backward)
+//   dW_acc[v, :] -= g * sum_{label_r = v} labw[r] * X_c[r, :]   by the sorted fp32 segmented reduction of scatter.cuh,
+//                                          keyed by the labels (no atomics: bit-identical run to run).
+// No pass over the [rows, V] block.  A row whose L is not finite (a logit more than ~88 nats above the pilot's
+// reference: E overflowed) raises bit 1 of the status word that ssi_b200_single_pass_lockstep_status reads; its loss
+// is inf and its gradients are NaN, never silently wrong.
 // ---------------------------------------------------------------------------------------------------
 __device__ __forceinline__ float grad_scale(const float* grad_hint, const int64_t* n_valid_total) {
   const long long nvt = *n_valid_total;
@@ -449,12 +454,14 @@ __global__ void __launch_bounds__(256) exp_combine_kernel(const float* __restric
                                                           const float* __restrict__ grad_hint,
                                                           const int64_t* __restrict__ n_valid_total,
                                                           float* __restrict__ lse_c, float* __restrict__ loss_c,
-                                                          float* __restrict__ rowscale_c) {
+                                                          float* __restrict__ rowscale_c,
+                                                          float* __restrict__ labw_c,
+                                                          unsigned int* __restrict__ overflow_word) {
   const int rows = plan->tiles_m * 128, nv = plan->n_valid, row0 = plan->row0;
   const int splits = plan->splits, part_stride = plan->part_stride;
   const float gscale = grad_scale(grad_hint, n_valid_total);
   for (int r = blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += gridDim.x * blockDim.x) {
-    float l = 0.f, loss = 0.f, rs = 0.f;
+    float l = 0.f, loss = 0.f, rs = 0.f, lw = 0.f;
     if (r < nv) {
       float L = 0.f, z = -INFINITY;
       for (int s = 0; s < splits; ++s) {  // fixed order: deterministic
@@ -465,10 +472,19 @@ __global__ void __launch_bounds__(256) exp_combine_kernel(const float* __restric
       l = (ref2[r] + log2f(L)) * 0.6931471805599453f;
       loss = l - z;
       rs = gscale / L;
+      // the label's exponential exactly as K1 formed it (same instruction, same operands), so L - e_lab is the sum
+      // of the OTHER columns up to the rounding of the additions: 1 - p_label without cancellation against 1
+      const float e_lab = (z > -INFINITY) ? fast_exp2(fmaf(z, 1.4426950408889634f, -ref2[r])) : 0.f;
+      lw = fminf(fmaxf((L - e_lab) / L, 0.f), 1.f);
+      if (!(L > 0.f && L < INFINITY)) {
+        lw = NAN;  // E overflowed (or every exponential underflowed): poison instead of a plausible-looking gradient
+        atomicOr(overflow_word, 1u);
+      }
     }
     lse_c[row0 + r] = l;
     loss_c[row0 + r] = loss;
     rowscale_c[row0 + r] = rs;
+    labw_c[row0 + r] = lw;
   }
 }
 
@@ -545,14 +561,15 @@ __device__ __forceinline__ uint4 bf16x8_sub_scaled(const uint4& a, const uint4& 
 }
 
 // dX[r, :] = dXc[pos[r], :] for valid rows, zeros for ignored rows (bf16 rows, 16-byte accesses).  With W (exp-stash
-// form): dX[r, :] = dXc[pos[r], :] - g * W[label, :], the onehot term of the row.
+// form): dX[r, :] = dXc[pos[r], :] - g * labw[pos[r]] * W[label, :], the label column's term of the row.
 __global__ void __launch_bounds__(256) dx_scatter_bf16_kernel(const uint4* __restrict__ dXc,
                                                               const int* __restrict__ pos, int n, int row_u4,
                                                               uint4* __restrict__ dX,
                                                               const uint4* __restrict__ W,
                                                               const int64_t* __restrict__ labels_c, int V,
                                                               const float* __restrict__ grad_hint,
-                                                              const int64_t* __restrict__ n_valid_total) {
+                                                              const int64_t* __restrict__ n_valid_total,
+                                                              const float* __restrict__ labw_c) {
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const float g = W ? grad_scale(grad_hint, n_valid_total) : 0.f;
@@ -564,7 +581,8 @@ __global__ void __launch_bounds__(256) dx_scatter_bf16_kernel(const uint4* __res
       const long long lab = W ? labels_c[c] : -1;
       if (lab >= 0 && lab < V) {
         const uint4* wrow = W + static_cast<size_t>(lab) * row_u4;
-        for (int j = lane; j < row_u4; j += 32) dst[j] = bf16x8_sub_scaled(src[j], __ldg(wrow + j), g);
+        const float gl = g * labw_c[c];
+        for (int j = lane; j < row_u4; j += 32) dst[j] = bf16x8_sub_scaled(src[j], __ldg(wrow + j), gl);
       } else {
         for (int j = lane; j < row_u4; j += 32) dst[j] = src[j];
       }
@@ -574,12 +592,14 @@ __global__ void __launch_bounds__(256) dx_scatter_bf16_kernel(const uint4* __res
   }
 }
 
-// In place on the compact rows: dXc[c, :] -= g * W[labels_c[c], :] (exp-stash form ahead of the fused norm backward).
+// In place on the compact rows: dXc[c, :] -= g * labw[c] * W[labels_c[c], :] (exp-stash form ahead of the fused norm
+// backward).
 __global__ void __launch_bounds__(256) dx_label_term_kernel(uint4* __restrict__ dXc,
                                                             const int64_t* __restrict__ labels_c, int n_pad,
                                                             int row_u4, const uint4* __restrict__ W, int V,
                                                             const float* __restrict__ grad_hint,
-                                                            const int64_t* __restrict__ n_valid_total) {
+                                                            const int64_t* __restrict__ n_valid_total,
+                                                            const float* __restrict__ labw_c) {
   const int lane = threadIdx.x & 31;
   const int warps = (gridDim.x * blockDim.x) >> 5;
   const float g = grad_scale(grad_hint, n_valid_total);
@@ -588,7 +608,8 @@ __global__ void __launch_bounds__(256) dx_label_term_kernel(uint4* __restrict__ 
     if (lab < 0 || lab >= V) continue;
     uint4* row = dXc + static_cast<size_t>(c) * row_u4;
     const uint4* wrow = W + static_cast<size_t>(lab) * row_u4;
-    for (int j = lane; j < row_u4; j += 32) row[j] = bf16x8_sub_scaled(row[j], __ldg(wrow + j), g);
+    const float gl = g * labw_c[c];
+    for (int j = lane; j < row_u4; j += 32) row[j] = bf16x8_sub_scaled(row[j], __ldg(wrow + j), gl);
   }
 }
 

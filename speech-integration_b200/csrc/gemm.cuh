@@ -666,6 +666,15 @@ __global__ void __launch_bounds__(GEMM_THREADS, 1) gemm_kernel(const __grid_cons
 #pragma unroll
               for (int j = 0; j < 32; j += 4) s0 += v[j], s1 += v[j + 1], s2 += v[j + 2], s3 += v[j + 3];
               l_run += (s0 + s1) + (s2 + s3);
+              // The label's own exponential stays in the row sum but is NOT stashed: its share of the gradient,
+              // g (p_label - 1), nearly cancels for a confident row and would lose its leading bits to the bf16
+              // rounding of E.  exp_combine_kernel forms 1 - p_label in fp32 and the label-keyed passes apply it.
+              if (valid && label >= ch0 && label < ch0 + 32) {
+                const int jl = static_cast<int>(label - ch0);
+#pragma unroll
+                for (int j = 0; j < 32; ++j)
+                  if (j == jl) v[j] = 0.f;
+              }
 #pragma unroll
               for (int j = 0; j < 16; ++j) w[h * 16 + j] = pack_bf16x2(v[2 * j], v[2 * j + 1]);
             }

@@ -299,6 +299,9 @@ struct ScatOut {
   const float* scale_num;
   const long long* scale_den;
   float scale_sign;
+  // fp32 dense mode: optional per-SOURCE-row weight (indexed like dH's rows; null = 1): row r joins its id's sum as
+  // row_w[r] * dH[r, :].  The label-keyed term of the LM-head gradient weights row r with 1 - p_label[r].
+  const float* row_w;
   // bf16 dense mode: scale_grads / grad-norm fold (aux_kernels.cuh GradFold): rows are multiplied by *post_scale
   // before they are added; fold.sq[warp] (scatter_reduce) and fold.sq[warps + warp] (scatter_fixup) receive
   // sum(new^2 - old^2) over the elements the warp rewrote
@@ -402,6 +405,10 @@ __global__ void __launch_bounds__(SCAT_THREADS, SSI_SCAT_MINBLOCKS) scatter_redu
   const uint32_t my_key = in ? skeys[p0 + lane] : KEY_NONE;
   const uint32_t my_row = in ? srows[p0 + lane] : 0u;
   const int my_ur = in ? urank[p0 + lane] : -1;
+  float my_w = 1.f;
+  if constexpr (MODE == SCAT_DENSE_F32) {
+    if (in && out.row_w) my_w = out.row_w[my_row];
+  }
   const uint32_t prev_key = (p0 > 0) ? skeys[p0 - 1] : KEY_NONE;
   const uint32_t next_key = (p0 + cnt < n) ? skeys[p0 + cnt] : KEY_NONE;
   const float sc = (MODE == SCAT_DENSE_F32) ? scat_scale(out) : (MODE == SCAT_DENSE_BF16) ? fold_scale(out.fold) : 1.f;
@@ -437,8 +444,14 @@ __global__ void __launch_bounds__(SCAT_THREADS, SSI_SCAT_MINBLOCKS) scatter_redu
     {
       float f[8];
       bf16x8_to_f32(u[0], f);
+      if constexpr (MODE == SCAT_DENSE_F32) {
+        const float w = __shfl_sync(0xffffffffu, my_w, i);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) acc[e] += f[e];
+        for (int e = 0; e < 8; ++e) acc[e] = fmaf(w, f[e], acc[e]);  // w == 1: the plain sum, bit for bit
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) acc[e] += f[e];
+      }
     }
 #pragma unroll
     for (int a = 0; a < SCAT_AHEAD; ++a) u[a] = u[a + 1];

@@ -27,6 +27,24 @@ def free_workspaces() -> None:
     _WS.clear()
 
 
+def single_pass_status(N: int, V: int, D: int, device: torch.device | None = None) -> int:
+    """Status bits of the last :func:`lmhead_ce_fwd_grad` call of this shape on the current stream (synchronises;
+    a debug query): bit 0 = a lockstep wait gave up (slower, still correct), bit 1 = the exp-stash form overflowed
+    on some row (a logit > ~88 nats above the row's first 256 vocabulary columns): loss inf, gradients NaN -- rerun
+    with ``_lib.set_option("exp_stash", 0)``."""
+    import ctypes
+
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else device
+    ws = _WS.get(("single_pass", device.index, torch.cuda.current_stream(device).cuda_stream))
+    if ws is None:
+        raise RuntimeError("ssi_b200: no single-pass call has run on this device and stream yet")
+    out = ctypes.c_int(0)
+    with torch.cuda.device(device):
+        rc = _lib.load().ssi_b200_single_pass_lockstep_status(ws.data_ptr(), N, V, D, ctypes.byref(out))
+    _lib.check(rc, "single_pass_lockstep_status")
+    return out.value
+
+
 def _stream(device: torch.device) -> int:
     return torch.cuda.current_stream(device).cuda_stream
 

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import reference_path as oracle
-from test_gpu_parity import CASES, DW_ELEM_ROUNDINGS, LOSS_RTOL, _case, assert_grad_close
+from test_gpu_parity import CASES, DW_ELEM_ROUNDINGS, FRO_TOL, LOSS_RTOL, _case, assert_grad_close
 
 pytestmark = pytest.mark.gpu
 
@@ -179,3 +179,100 @@ def test_large_logits_and_a_spike_far_above_the_first_vocabulary_tile(exp_stash)
     assert torch.isfinite(dX.float()).all() and torch.isfinite(dW.float()).all()
     assert_grad_close(dX, G @ W.float(), "dX")
     assert_grad_close(dW, G.t() @ X.float(), "dW", elem_roundings=DW_ELEM_ROUNDINGS)
+
+
+def _confident_case(target_p, seed, B=2, S=300, V=5002, D=256):
+    """Rows whose hidden state points along their label's embedding, scaled so that softmax[label] ~ target_p."""
+    import math
+
+    g = torch.Generator().manual_seed(seed)
+    W = (torch.randn(V, D, generator=g) * 0.06).to(torch.bfloat16)
+    labels = torch.randint(0, V, (B * S,), generator=g)
+    t = math.log(V) + math.log(target_p / (1 - target_p))
+    wl = W[labels].float()
+    X = (wl * (t / wl.pow(2).sum(-1, keepdim=True))).to(torch.bfloat16)
+    ignored = torch.rand(B * S, generator=g) < 0.2
+    labels[ignored] = -100
+    return {"X": X.reshape(B, S, D), "W": W, "shifted": labels.reshape(B, S)}
+
+
+@pytest.mark.parametrize("target_p", [0.9, 0.99, 0.998])
+def test_confident_rows_keep_the_reference_accuracy(target_p):
+    """with a peaked softmax the label column's gradient g (p_label - 1) nearly cancels; the
+    exp-stash form used to round p_label to bf16 inside E BEFORE subtracting the onehot, leaving an absolute error of
+    2^-9 g |W| on a signal of g (1 - p_label) |W| (31 % at p_label = 0.998).  The label column is now handled in fp32
+    (1 - p_label = (L - e_label) / L).  Logits of ~10-15 nats move by several per cent of a nat when rounded to bf16
+    (tied_linear.py:25), so -- as in the spike test above -- the oracle is fp32 arithmetic ON the bf16-rounded logits,
+    what the reference's fp32 cross-entropy sees.  Bounds: the usual ones overall, and per row at most 4e-3 or the error
+    of the reference's own arithmetic (dlogits rounded to bf16 before the contractions, bf16 results)."""
+    inp = _confident_case(target_p, seed=int(target_p * 1000))
+    V, D = inp["W"].shape
+    X, W = inp["X"].reshape(-1, D).float(), inp["W"].float()
+    labels = inp["shifted"].reshape(-1)
+    valid = labels != -100
+    nv = int(valid.sum())
+    upstream = float(nv)
+    logits = (X @ W.t()).to(torch.bfloat16).float()
+    P = torch.softmax(logits, -1)
+    p_lab = P[valid][torch.arange(nv), labels[valid]]
+    assert abs(p_lab.median().item() - target_p) < 0.5 * (1 - target_p) + 0.05, p_lab.median().item()
+    G = torch.zeros_like(P)
+    G[valid] = (P[valid] - torch.nn.functional.one_hot(labels[valid], V).float()) * (upstream / nv)
+    rdX, rdW = G @ W, G.t() @ X
+    Gb = G.to(torch.bfloat16).float()  # the reference's autograd hands bf16 dlogits to the two contractions
+    bdX, bdW = (Gb @ W).to(torch.bfloat16).float(), (Gb.t() @ X).to(torch.bfloat16).float()
+    loss_out, lse, n_valid, dX, dW, _ = _run(inp, D, upstream)
+    assert torch.isfinite(dX.float()).all() and torch.isfinite(dW.float()).all()
+
+    def row_err(got, ref):
+        got, ref = got.float().cpu(), ref.float().cpu()
+        return (got - ref).norm(dim=-1) / ref.norm(dim=-1).clamp_min(1e-30)
+
+    ours, theirs = row_err(dX.cpu()[valid], rdX[valid]), row_err(bdX[valid], rdX[valid])
+    touched = torch.unique(labels[valid])  # the label rows of dW carry the cancelling term
+    ours_w, theirs_w = row_err(dW.cpu()[touched], rdW[touched]), row_err(bdW[touched], rdW[touched])
+    print(f"p_label~{target_p}: dX rows ours {ours.median().item():.2e}/{ours.max().item():.2e} ref-bf16 "
+          f"{theirs.median().item():.2e}/{theirs.max().item():.2e}; dW label rows ours "
+          f"{ours_w.median().item():.2e}/{ours_w.max().item():.2e} ref-bf16 "
+          f"{theirs_w.median().item():.2e}/{theirs_w.max().item():.2e}")
+    assert_grad_close(dX, rdX, "dX")
+    assert_grad_close(dW, rdW, "dW", elem_roundings=DW_ELEM_ROUNDINGS)
+    assert ours.max().item() <= max(FRO_TOL, theirs.max().item()), (
+        f"dX rows: worst relative error {ours.max().item():.3e} (median {ours.median().item():.3e}); the reference's "
+        f"bf16 arithmetic: worst {theirs.max().item():.3e} (median {theirs.median().item():.3e})")
+    assert ours_w.max().item() <= max(FRO_TOL, theirs_w.max().item()), (
+        f"dW label rows: worst relative error {ours_w.max().item():.3e} (median {ours_w.median().item():.3e}); the "
+        f"reference's bf16 arithmetic: worst {theirs_w.max().item():.3e} (median {theirs_w.median().item():.3e})")
+
+
+def test_exp_stash_overflow_is_flagged_not_silent():
+    """A logit more than ~88 nats above everything in the row's first 256 vocabulary columns overflows the stashed
+    exponentials.  The call must say so (bit 1 of the status word, non-finite loss and gradients) instead of handing
+    back plausible numbers; the logits-stash form (exp_stash = 0) has no such limit and stays exact."""
+    from ssi_b200 import _lib, ops
+
+    g = torch.Generator().manual_seed(5)
+    N, V, D = 256, 1500, 128
+    X = torch.randn(N, D, generator=g).to(torch.bfloat16)
+    W = (torch.randn(V, D, generator=g) * D ** -0.5).to(torch.bfloat16)  # logits ~ N(0, 1)
+    W[900] = (X[5].float() * (120.0 / X[5].float().pow(2).sum())).to(torch.bfloat16)  # logit[5, 900] ~ 120
+    labels = torch.randint(0, V, (N,), generator=g)
+    inp = {"X": X.reshape(1, N, D), "W": W, "shifted": labels.reshape(1, N)}
+    logits = (X.float() @ W.float().t()).to(torch.bfloat16).float()
+    assert logits[5, 900] - logits[5, :256].max() > 100.0
+    loss_out, lse, n_valid, dX, dW, _ = _run(inp, D, 1.0)
+    assert ops.single_pass_status(N, V, D) & 2, "overflow not flagged"
+    assert not torch.isfinite(loss_out[1]).item() and not torch.isfinite(dX[5].float()).all()
+    # an ordinary call on the same workspace clears the flag
+    inp2 = dict(inp, W=(torch.randn(V, D, generator=g) * D ** -0.5).to(torch.bfloat16))
+    _run(inp2, D, 1.0)
+    assert ops.single_pass_status(N, V, D) & 2 == 0
+    _lib.set_option("exp_stash", 0)
+    try:
+        loss_out, lse, n_valid, dX, dW, _ = _run(inp, D, 1.0)
+    finally:
+        _lib.set_option("exp_stash", 1)
+    ref_lse = torch.logsumexp(logits, dim=-1)
+    ref_loss = (ref_lse - logits[torch.arange(N), labels]).mean()
+    assert abs(loss_out[1].item() - ref_loss.item()) <= LOSS_RTOL * abs(ref_loss.item())
+    assert torch.isfinite(dX.float()).all() and torch.isfinite(dW.float()).all()
