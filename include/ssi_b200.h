@@ -36,7 +36,7 @@
 extern "C" {
 #endif
 
-#define SSI_B200_ABI_VERSION 113
+#define SSI_B200_ABI_VERSION 114
 
 /* ABI version of the loaded library (== SSI_B200_ABI_VERSION it was built with). */
 int ssi_b200_version(void);
@@ -57,9 +57,12 @@ int64_t ssi_b200_launch_count(void);
  * per-row factor, default; 0 = stash logits + a separate softmax-grad pass), "sparse_two_phase" (data-parallel
  * embedding exchange: -1 = two phases when world > 4, default; 0 / 1 force), "k1_group_m" (m-tiles per raster group
  * of the single-pass K1, default 64, 0 = all) and "k1_store_first" (1 = evict-first L2 policy on its E-tile stores,
- * default), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints", "dw_hints",
+ * default), "dp_timeout_s" (see ssi_b200_dp_status), "g_tiles", "group_m_grad", "group_m_dw", "group_m_dx", "store_hint", "k1_hints", "dw_hints",
  * "dx_hints" (experiments; see profiles/r01_tuning_notes.md). */
 int ssi_b200_set_option(const char* name, int64_t value);
+/* The value an option has now (the names of ssi_b200_set_option).  The data-parallel set-up compares the options
+ * that every rank must agree on ("sparse_two_phase": ranks that disagree wait on different flags) across ranks. */
+int ssi_b200_get_option(const char* name, int64_t* value);
 
 /* Workspace sizes (bytes) for the given problem. Any out pointer may be NULL. Workspaces must be 256-byte
  * aligned. */
@@ -219,7 +222,7 @@ int ssi_b200_embedding_grad_scatter_sorted(const void* dH, int64_t N, int64_t V,
  * The three exchanges of a step, in the order a training step produces their inputs (all enqueue-only; `epoch` is a
  * counter the caller increments by one per step, starting at 1, identical on all ranks; `host_flag` is NULL or a
  * pinned, device-mapped host word that a timed-out wait sets to 1 so the host can notice without synchronising --
- * after a time-out every exchange writes NaN instead of sums):
+ * after a time-out every exchange on every rank writes NaN instead of sums until ssi_b200_dp_reset):
  *
  * dp_counts             global_counts[0..1] = sum over ranks of local_counts[0..1] ({unshifted, shifted} valid-token
  *                       counts, ssi/trainer.py:391 and ce_chunked_output_loss.py:66) and, if hint_out != NULL,
@@ -248,9 +251,15 @@ int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle);
 int ssi_b200_dp_open(const void* ipc_handle, void** ptr);
 int ssi_b200_dp_close(void* ptr);
 int ssi_b200_dp_free(void* ptr);
-/* Synchronising check (set-up / tear-down class): *timed_out != 0 if a wait inside an exchange gave up after 20 s
- * because a peer never arrived (its process died); the gradients of that step are NaN. */
+/* Synchronising check (set-up / tear-down class): *timed_out != 0 if a wait inside an exchange -- on this rank or on
+ * any peer, which then marks every rank -- gave up because a rank did not arrive within the time limit; every exchange
+ * since writes NaN.  The limit is option "dp_timeout_s" / SSI_B200_DP_TIMEOUT_S (seconds, default 600 = the default
+ * time-out of a torch.distributed process group), read by dp_alloc and dp_reset. */
 int ssi_b200_dp_status(const void* own_buf, int* timed_out);
+/* Collective recovery after a time-out (set-up class: synchronises the device): clears this rank's mark and
+ * re-reads the time limit.  Every rank must call it between two host-side barriers (no exchange in flight anywhere),
+ * and all ranks must continue with the same `epoch`. */
+int ssi_b200_dp_reset(void* own_buf);
 int ssi_b200_dp_counts(void* const* peer_bufs, int rank, int world, uint32_t epoch, const int64_t* local_counts,
                        int64_t* global_counts, float* hint_out, void* host_flag, void* stream);
 int ssi_b200_dp_exchange(void* const* peer_bufs, int rank, int world, int64_t V, int64_t D, int64_t max_rows,

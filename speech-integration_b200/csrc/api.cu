@@ -331,6 +331,9 @@ struct Tune {
   // 4.35 GB write stream: DRAM reads per 16k-row chunk 4.3 -> 2.0 GB, step -0.75 % (profiles/r02_ab_k1_l2hints*.txt)
   int k1_group_m = 64;
   int k1_store_first = 1;
+  // data-parallel exchange: seconds a device-side wait for a peer may last before the step is declared lost (all
+  // ranks poisoned); read when an exchange buffer is allocated or reset.  Default = torch.distributed's 10 minutes.
+  int64_t dp_timeout_s = 600;
 };
 // The knobs are process-global and may be changed at run time (ssi_b200_set_option): every API entry takes a
 // thread-local SNAPSHOT under the mutex (TuneScope), so one call never sees half of an update.
@@ -358,6 +361,7 @@ Tune& global_tune() {
     if (const char* e = getenv("SSI_B200_K1_GROUP_M")) x.k1_group_m = atoi(e);
     if (const char* e = getenv("SSI_B200_K1_STORE_FIRST")) x.k1_store_first = atoi(e) ? 1 : 0;
     if (const char* e = getenv("SSI_B200_SPARSE_TWO_PHASE")) x.sparse_two_phase = atoi(e);
+    if (const char* e = getenv("SSI_B200_DP_TIMEOUT_S")) x.dp_timeout_s = atoll(e) > 0 ? atoll(e) : 600;
     return x;
   }();
   return t;
@@ -593,8 +597,29 @@ int ssi_b200_set_option(const char* name, int64_t value) {
   else if (!strcmp(name, "k1_group_m")) t.k1_group_m = value > 0 ? static_cast<int>(value) : 0;
   else if (!strcmp(name, "k1_store_first")) t.k1_store_first = value ? 1 : 0;
   else if (!strcmp(name, "sparse_two_phase")) t.sparse_two_phase = value < 0 ? -1 : (value ? 1 : 0);
+  else if (!strcmp(name, "dp_timeout_s")) t.dp_timeout_s = value > 0 ? value : 600;
   else return fail(-1, "unknown option '%s'", name);
   return 0;
+}
+
+int ssi_b200_get_option(const char* name, int64_t* value) {
+  SSI_CHECK_ARG(name && value, "null pointer argument");
+  std::lock_guard<std::mutex> lk(g_tune_mu);
+  const Tune& t = global_tune();
+  const struct { const char* n; int64_t v; } all[] = {
+      {"g_cap_mib", t.g_cap_elems >> 19}, {"g_tiles", t.g_tiles}, {"group_m_grad", t.group_m_grad},
+      {"group_m_dw", t.group_m_dw}, {"group_m_dx", t.group_m_dx}, {"store_hint", t.store_hint},
+      {"cta_group", t.cta_group}, {"k1_hints", t.k1_hints}, {"lockstep", t.lockstep}, {"dw_hints", t.dw_hints},
+      {"dx_hints", t.dx_hints}, {"lockstep_k1", t.lockstep_k1}, {"shape_gate", t.shape_gate},
+      {"tail_split", t.tail_split}, {"wide_dw", t.wide_dw}, {"wide_dx", t.wide_dx}, {"exp_stash", t.exp_stash},
+      {"k1_group_m", t.k1_group_m}, {"k1_store_first", t.k1_store_first}, {"sparse_two_phase", t.sparse_two_phase},
+      {"dp_timeout_s", t.dp_timeout_s}};
+  for (const auto& o : all)
+    if (!strcmp(name, o.n)) {
+      *value = o.v;
+      return 0;
+    }
+  return fail(-1, "unknown option '%s'", name);
 }
 
 int64_t ssi_b200_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
@@ -1290,13 +1315,27 @@ int ssi_b200_dp_buffer_bytes(int64_t V, int64_t D, int world, int64_t max_rows, 
   return 0;
 }
 
+namespace {
+int dp_store_timeout(void* own_buf) {
+  const unsigned long long ns = static_cast<unsigned long long>(tune().dp_timeout_s) * 1000000000ull;
+  SSI_CUDA(cudaMemcpy(static_cast<char*>(own_buf) + offsetof(ssi::DpCtrl, timeout_ns), &ns, sizeof(ns),
+                      cudaMemcpyHostToDevice));
+  return 0;
+}
+}  // namespace
+
 int ssi_b200_dp_alloc(size_t bytes, void** ptr, void* ipc_handle) {
+  TuneScope tune_scope_;
   SSI_CHECK_ARG(ptr && ipc_handle && bytes >= ssi::DP_CTRL_BYTES, "bad argument");
   DeviceInfo* di = nullptr;
   if (int r = device_info(&di)) return r;
   void* p = nullptr;
   SSI_CUDA(cudaMalloc(&p, bytes));
   SSI_CUDA(cudaMemset(p, 0, bytes));  // flags, and slot entries whose stale epoch tags could match
+  if (int r = dp_store_timeout(p)) {
+    cudaFree(p);
+    return r;
+  }
   cudaIpcMemHandle_t h;
   cudaError_t e = cudaIpcGetMemHandle(&h, p);
   if (e != cudaSuccess) {
@@ -1336,6 +1375,16 @@ int ssi_b200_dp_status(const void* own_buf, int* timed_out) {
                       cudaMemcpyDeviceToHost));
   *timed_out = static_cast<int>(v);
   return 0;
+}
+
+int ssi_b200_dp_reset(void* own_buf) {
+  TuneScope tune_scope_;
+  SSI_CHECK_ARG(own_buf, "null pointer argument");
+  SSI_CUDA(cudaDeviceSynchronize());  // no exchange kernel of this rank may still be spinning or poisoning
+  const unsigned int zero = 0;
+  SSI_CUDA(cudaMemcpy(static_cast<char*>(own_buf) + offsetof(ssi::DpCtrl, timed_out), &zero, sizeof(zero),
+                      cudaMemcpyHostToDevice));
+  return dp_store_timeout(own_buf);
 }
 
 namespace {

@@ -54,10 +54,15 @@ struct DpCtrl {
   unsigned int arrive_d[DP_MAX_WORLD];  // written by peers: epoch of their last "owned embedding rows reduced"
   unsigned long long counts[2][DP_MAX_WORLD][2];  // [epoch & 1][rank] = {unshifted, shifted} valid-token counts
   unsigned int blocks_done;             // local: blocks of dp_reduce_kernel that finished (reset by the last one)
-  unsigned int timed_out;               // local: set when a wait gave up (a peer never arrived): results are invalid
+  unsigned int timed_out;               // set when a wait gave up, here OR on a peer (which then stores 1 into every
+                                        // rank's word): this step's results are invalid, see dp_wait_all
+  unsigned long long timeout_ns;        // local: how long a wait may last (set by dp_alloc / dp_reset; 0 = the default)
 };
 static_assert(sizeof(DpCtrl) <= DP_CTRL_BYTES, "ctrl block too large");
-constexpr unsigned long long DP_WAIT_TIMEOUT_NS = 20ull * 1000 * 1000 * 1000;  // a dead peer must not hang the GPU
+// A dead peer must not hang the GPU, but ordinary rank skew (a checkpoint written by rank 0, an uneven eval shard,
+// a dataloader stall, first-step compilation) must not trip the wait either: the default matches the 10 minutes a
+// torch.distributed process group waits by default.  Option "dp_timeout_s" / SSI_B200_DP_TIMEOUT_S, read at dp_alloc.
+constexpr unsigned long long DP_WAIT_TIMEOUT_DEFAULT_NS = 600ull * 1000 * 1000 * 1000;
 constexpr uint32_t BF16X2_NAN = 0x7FC07FC0u;
 
 struct DpPeers {
@@ -130,32 +135,55 @@ __device__ __forceinline__ unsigned long long global_timer_ns() {
   return t;
 }
 
-// wait until every peer's slot in `flags` (this rank's own ctrl block) has reached `epoch`; gives up after
-// DP_WAIT_TIMEOUT_NS and records it in *timed_out and in the pinned host word `host_flag` (the host polls that
-// word without synchronising; the kernels then write NaN instead of sums so that no optimizer step can use them)
-__device__ __forceinline__ void dp_wait_all(const unsigned int* flags, int world, int rank, unsigned int epoch,
-                                            unsigned int* timed_out, unsigned int* host_flag) {
+// timed_out stays set -- every exchange writes NaN -- until all ranks clear it together (ssi_b200_dp_reset between two
+// host barriers, TiedGradExchange.reset())
+__device__ __forceinline__ bool dp_is_bad(const DpCtrl* ctrl) {
+  return *reinterpret_cast<const volatile unsigned int*>(&ctrl->timed_out) != 0u;
+}
+
+__device__ __forceinline__ unsigned long long dp_timeout_ns(const DpCtrl* ctrl) {
+  const unsigned long long t = *reinterpret_cast<const volatile unsigned long long*>(&ctrl->timeout_ns);
+  return t ? t : DP_WAIT_TIMEOUT_DEFAULT_NS;
+}
+
+// A wait gave up: mark EVERY rank's ctrl block (own block included), not only this one.  The peer that was late
+// finds all flags of the step already posted, so its own waits succeed at once -- without the poison it would read
+// buffers this rank may already be rewriting for its next step and carry on with wrong, finite gradients.
+__device__ __forceinline__ void dp_poison_all(const DpPeers& peers, int world, unsigned int* host_flag) {
+  for (int p = 0; p < world; ++p)
+    *reinterpret_cast<volatile unsigned int*>(&reinterpret_cast<DpCtrl*>(peers.buf[p])->timed_out) = 1u;
+  if (host_flag) *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;  // pinned host word: no sync to read
+  __threadfence_system();
+}
+
+// wait until every peer's slot in `flags` (this rank's own ctrl block) has reached `epoch`; gives up after the ctrl
+// block's timeout and then poisons all ranks (dp_poison_all) and raises the pinned host word `host_flag` (the host
+// polls that word without synchronising; the kernels write NaN instead of sums so that no optimizer step can use them)
+__device__ __forceinline__ void dp_wait_all(const DpPeers& peers, const unsigned int* flags, int world, int rank,
+                                            unsigned int epoch, unsigned int* host_flag) {
   if (threadIdx.x < static_cast<unsigned>(world) && static_cast<int>(threadIdx.x) != rank) {
     // epochs only grow; the signed difference keeps the comparison valid across 32-bit wrap-around
     const unsigned long long t0 = global_timer_ns();
+    const unsigned long long limit = dp_timeout_ns(reinterpret_cast<const DpCtrl*>(peers.buf[rank]));
     unsigned int spins = 0;
     while (static_cast<int>(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
       __nanosleep(64);
-      if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > DP_WAIT_TIMEOUT_NS) {
-        *timed_out = 1u;
-        if (host_flag) *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;  // pinned host word: no sync to read
-        __threadfence_system();
-        break;
+      if ((++spins & 1023u) == 0) {
+        if (dp_is_bad(reinterpret_cast<const DpCtrl*>(peers.buf[rank]))) break;  // the step is already lost: do not wait again
+        if (global_timer_ns() - t0 > limit) {
+          dp_poison_all(peers, world, host_flag);
+          break;
+        }
       }
     }
   }
   __syncthreads();
+  // a PEER's wait gave up (it marked this rank's block): tell this rank's host too
+  if (threadIdx.x == 0 && host_flag &&
+      *reinterpret_cast<const volatile unsigned int*>(&reinterpret_cast<const DpCtrl*>(peers.buf[rank])->timed_out))
+    *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;
 }
 
-// timed_out is sticky: once a wait gave up nothing this rank exchanges can be trusted until the set-up is redone
-__device__ __forceinline__ bool dp_is_bad(const DpCtrl* ctrl) {
-  return *reinterpret_cast<const volatile unsigned int*>(&ctrl->timed_out) != 0u;
-}
 
 // ---------------------------------------------------------------------------------------------------
 // Token counts: one warp.  Lane p stores this rank's pair into rank p's ctrl block (own block included) and
@@ -179,14 +207,16 @@ __global__ void __launch_bounds__(32) dp_counts_kernel(DpPeers peers, int rank, 
   unsigned long long c0 = 0, c1 = 0;
   if (p < world) {
     const unsigned long long t0 = global_timer_ns();
+    const unsigned long long limit = dp_timeout_ns(ctrl);
     unsigned int spins = 0;
     while (static_cast<int>(ld_acquire_sys(&ctrl->arrive_n[p]) - epoch) < 0) {
       __nanosleep(64);
-      if ((++spins & 1023u) == 0 && global_timer_ns() - t0 > DP_WAIT_TIMEOUT_NS) {
-        ctrl->timed_out = 1u;
-        if (host_flag) *reinterpret_cast<volatile unsigned int*>(host_flag) = 1u;
-        __threadfence_system();
-        break;
+      if ((++spins & 1023u) == 0) {
+        if (dp_is_bad(reinterpret_cast<const DpCtrl*>(peers.buf[rank]))) break;  // the step is already lost: do not wait again
+        if (global_timer_ns() - t0 > limit) {
+          dp_poison_all(peers, world, host_flag);
+          break;
+        }
       }
     }
     const volatile unsigned long long* src = ctrl->counts[par][p];
@@ -223,7 +253,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_reduce_kernel(DpPeers peers, Dp
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_a[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_a, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  dp_wait_all(peers, ctrl->arrive_a, WORLD, rank, epoch, host_flag);
   const bool bad = dp_is_bad(ctrl);  // a peer never arrived: NaN out, so that no optimizer step can use the result
 
   const float ratio = grad_ratio(grad_out, grad_hint);
@@ -298,7 +328,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_gather_kernel(DpPeers peers, Dp
                                                                unsigned int* host_flag, GradFold fold) {
   __shared__ float s_fold[DP_THREADS / 32];
   DpCtrl* ctrl = reinterpret_cast<DpCtrl*>(peers.buf[rank]);
-  dp_wait_all(ctrl->arrive_b, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  dp_wait_all(peers, ctrl->arrive_b, WORLD, rank, epoch, host_flag);
   const bool bad = dp_is_bad(ctrl);
   float sq = 0.f;
   // bf16 slices move as 16-byte words: 2 of the fp32-quad units per word (slice_f4 is even, see the host side)
@@ -350,7 +380,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_add_kernel(DpPeers peers
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_c[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_c, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  dp_wait_all(peers, ctrl->arrive_c, WORLD, rank, epoch, host_flag);
   if (dp_is_bad(ctrl)) {  // poison the first gradient row: grad-norm and loss checks trip at once
     if (blockIdx.x == 0)
       for (int j = threadIdx.x; j < D / 2; j += DP_THREADS) reinterpret_cast<uint32_t*>(dW)[j] = BF16X2_NAN;
@@ -467,7 +497,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_reduce_kernel(DpPeers pe
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_c[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_c, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  dp_wait_all(peers, ctrl->arrive_c, WORLD, rank, epoch, host_flag);
   if (dp_is_bad(ctrl)) return;  // the apply kernel poisons the gradient
   const uint32_t lane = threadIdx.x & 31;
   const int gw = (blockIdx.x * DP_THREADS + threadIdx.x) >> 5;
@@ -552,7 +582,7 @@ __global__ void __launch_bounds__(DP_THREADS) dp_sparse_apply_kernel(DpPeers pee
     __threadfence_system();
     st_release_sys(&reinterpret_cast<DpCtrl*>(peers.buf[threadIdx.x])->arrive_d[rank], epoch);
   }
-  dp_wait_all(ctrl->arrive_d, WORLD, rank, epoch, &ctrl->timed_out, host_flag);
+  dp_wait_all(peers, ctrl->arrive_d, WORLD, rank, epoch, host_flag);
   if (dp_is_bad(ctrl)) {  // poison the first gradient row: grad-norm and loss checks trip at once
     if (blockIdx.x == 0)
       for (int j = threadIdx.x; j < D / 2; j += DP_THREADS) reinterpret_cast<uint32_t*>(dW)[j] = BF16X2_NAN;

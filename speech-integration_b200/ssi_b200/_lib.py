@@ -11,7 +11,7 @@ from ctypes import c_char_p, c_int, c_int64, c_size_t, c_void_p, POINTER
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libssi_b200.so")
-ABI_VERSION = 113
+ABI_VERSION = 114
 
 # name -> (restype, argtypes); must list every symbol include/ssi_b200.h declares
 SYMBOLS = {
@@ -19,6 +19,7 @@ SYMBOLS = {
     "ssi_b200_last_error": (c_char_p, []),
     "ssi_b200_launch_count": (c_int64, []),
     "ssi_b200_set_option": (c_int, [c_char_p, c_int64]),
+    "ssi_b200_get_option": (c_int, [ctypes.c_char_p, POINTER(c_int64)]),
     "ssi_b200_workspace_bytes": (
         c_int,
         [c_int64, c_int64, c_int64, POINTER(c_size_t), POINTER(c_size_t), POINTER(c_size_t)],
@@ -84,6 +85,7 @@ SYMBOLS = {
     "ssi_b200_dp_close": (c_int, [c_void_p]),
     "ssi_b200_dp_free": (c_int, [c_void_p]),
     "ssi_b200_dp_status": (c_int, [c_void_p, POINTER(c_int)]),
+    "ssi_b200_dp_reset": (c_int, [c_void_p]),
     "ssi_b200_dp_counts": (
         c_int,
         [POINTER(c_void_p), c_int, c_int, ctypes.c_uint32, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p],
@@ -224,6 +226,12 @@ def single_pass_workspace_bytes(N: int, V: int, D: int) -> int:
 
 def set_option(name: str, value: int) -> None:
     check(load().ssi_b200_set_option(name.encode(), int(value)), f"set_option({name})")
+
+
+def get_option(name: str) -> int:
+    v = c_int64(0)
+    check(load().ssi_b200_get_option(name.encode(), ctypes.byref(v)), f"get_option({name})")
+    return int(v.value)
 
 
 def launch_count() -> int:

@@ -125,6 +125,7 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
                     hint, announced = ghint, True
                 kw["pre_grad_event"] = ev
                 if sync.peer is not None:
+                    sync.before_dw_acc_write()  # a dense exchange still reading the buffer (2nd loss of a micro-batch)
                     kw["dW_acc"], kw["dw_ready_event"] = sync.dw_acc, sync.dw_ready
                 ctx.sync = sync
             nvt = _ones_i64(X.device) if reduction == "sum" else n_valid_override
@@ -170,11 +171,13 @@ class _FusedLinearCESinglePass(torch.autograd.Function):
         if sync is not None:
             # data parallel: dX is rescaled here; the LM-head gradient is summed over ranks by the exchange -- already
             # running behind the last dX contraction when the multiplier was announced, started now otherwise
-            if ctx.sync is None and sync.peer is not None:
+            outside = ctx.sync is None and sync.peer is not None
+            if outside:
                 # formed outside the exchange buffer (compute_cross_entropy): move it there before it is exchanged
+                sync.before_dw_acc_write()  # the previous chunk's exchange may still read the buffer, here or remotely
                 sync.dw_acc.copy_(dW_acc)
                 dW_acc = sync.dw_acc
-            sync.in_backward(dX, dW_acc, g, hint)
+            sync.in_backward(dX, dW_acc, g, hint, formed_outside=outside)
             return (dX, None) + nones + (dscale, None, None)
         if tied:
             acc = wparam.grad is not None

@@ -66,6 +66,14 @@ class TiedGradExchange:
         self.max_rows = int(max_rows)
         self.epoch_dense = self.epoch_sparse = self.epoch_counts = 0
         lib = _lib.load()
+        # options that change which flags a rank waits on must be the same everywhere: found here, by all ranks
+        # together, instead of as a device-side time-out in the first exchange
+        mine = {k: _lib.get_option(k) for k in ("sparse_two_phase",)}
+        every: list = [None] * self.world
+        dist.all_gather_object(every, mine, group=group)
+        if any(e != every[0] for e in every):
+            raise RuntimeError(f"ssi_b200.peer: the ranks disagree on an exchange option (set_option / SSI_B200_*): "
+                               f"{every}")
         nbytes, off = ctypes.c_size_t(0), ctypes.c_size_t(0)
         _lib.check(lib.ssi_b200_dp_buffer_bytes(self.V, self.D, self.world, self.max_rows, ctypes.byref(nbytes),
                                                 ctypes.byref(off)), "dp_buffer_bytes")
@@ -129,6 +137,10 @@ class TiedGradExchange:
                                       device=self.device)
         # pinned host word a timed-out wait sets to 1: polled by check() without any device synchronisation
         self._host_flag = torch.zeros(1, dtype=torch.int32).pin_memory()
+        # the wait limit (option dp_timeout_s / SSI_B200_DP_TIMEOUT_S) goes into the ctrl block: dp_alloc stored it
+        # for the IPC buffers, torch's symmetric allocation gets it here
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().ssi_b200_dp_reset(self._own), "dp_reset")
         # every rank must have mapped (and zero-initialised) its buffers before the first exchange touches them
         torch.cuda.synchronize(self.device)
         dist.barrier(group=self.group)
@@ -165,8 +177,24 @@ class TiedGradExchange:
     def check(self) -> None:
         """Raise if an earlier exchange timed out waiting for a peer (reads a pinned host word: no device sync)."""
         if self._host_flag is not None and int(self._host_flag[0]) != 0:
-            raise RuntimeError("ssi_b200.peer: an exchange timed out waiting for a peer; the gradients of that step "
-                               "were replaced by NaN")
+            raise RuntimeError("ssi_b200.peer: an exchange timed out waiting for a peer (on this rank or another); "
+                               "the gradients since were replaced by NaN on every rank -- reset() on all ranks "
+                               "recovers; option dp_timeout_s sets the limit")
+
+    def reset(self) -> None:
+        """Collective recovery after a time-out (every rank of the group must call it, e.g. from the ``except`` of a
+        failed :meth:`check`): waits until no rank has an exchange in flight, clears every rank's time-out mark,
+        re-reads the ``dp_timeout_s`` option and realigns the step counters, so that the next step exchanges
+        normally.  The gradients of the step that timed out are lost (NaN) -- redo or skip that step."""
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)  # nobody is spinning on, or still poisoning, anybody's ctrl block
+        with torch.cuda.device(self.device):
+            _lib.check(_lib.load().ssi_b200_dp_reset(self._own), "dp_reset")
+        self._host_flag.zero_()
+        mine = (self.epoch_counts, self.epoch_dense, self.epoch_sparse)
+        every: list = [None] * self.world
+        dist.all_gather_object(every, mine, group=self.group)  # doubles as the barrier after the clear
+        self.epoch_counts, self.epoch_dense, self.epoch_sparse = (max(e[i] for e in every) for i in range(3))
 
     def counts(self, local_counts: torch.Tensor):
         """Enqueue on the current stream: returns ``(global_counts int64 [2], hint fp32 [1])`` = the int64 ``[2]``

@@ -69,8 +69,8 @@ class TiedGradSync:
             # SSI_B200_PEER_SERIAL=1 (diagnostics): run the exchanges on the main stream instead of beside it
             self.serial = os.environ.get("SSI_B200_PEER_SERIAL") == "1"
             self.side = torch.cuda.current_stream(self.device) if self.serial else torch.cuda.Stream(self.device)
-            self.dw_ready, self.counts_ready, self.local_ready = (torch.cuda.Event() for _ in range(3))
-            for e in (self.dw_ready, self.counts_ready, self.local_ready):
+            self.dw_ready, self.counts_ready, self.local_ready, self.dense_done = (torch.cuda.Event() for _ in range(4))
+            for e in (self.dw_ready, self.counts_ready, self.local_ready, self.dense_done):
                 e.record(torch.cuda.current_stream(self.device))  # creates the CUDA handle
         self._scratch = None          # nccl mode: this micro-batch's contribution when .grad already holds earlier ones
         self._target = None           # nccl mode: where this micro-batch's LM-head gradient went
@@ -100,6 +100,10 @@ class TiedGradSync:
             with torch.cuda.stream(self.side):
                 gcounts, hint = self.peer.counts(local_counts)
                 self.counts_ready.record(self.side)
+            if not self.serial:  # each tensor is allocated under one stream and used on the other
+                local_counts.record_stream(self.side)
+                gcounts.record_stream(main)
+                hint.record_stream(main)
             return gcounts, hint, self.counts_ready
         gcounts = local_counts.clone()
         dist.all_reduce(gcounts, op=dist.ReduceOp.SUM, group=self.pg)
@@ -130,7 +134,17 @@ class TiedGradSync:
             self.peer.exchange(self.weight.grad, grad_out, hint, accumulate=accumulate, post_scale=ps, fold_ws=fws)
             if self._tl_cur is not None:
                 self._tl_cur["dense_done"] = self._mark(self.side)
+            self.dense_done.record(self.side)
         self._dense_done = True
+
+    def before_dw_acc_write(self) -> None:
+        """Call on the main stream before anything overwrites the peer-visible ``dw_acc``: the previous dense exchange
+        (side stream) reads it here AND on every peer; its gather step ends only after all peers reduced their slice,
+        i.e. finished reading, so waiting for the event behind it is enough for both.  A micro-batch with ONE loss
+        backward never waits (the embedding backward already joined the streams); two ``compute_cross_entropy``
+        backwards per micro-batch do."""
+        if self.peer is not None and not self.serial:
+            torch.cuda.current_stream(self.device).wait_event(self.dense_done)
 
     def after_forward(self, hint: torch.Tensor, announced: bool, n_rows: int = 0) -> None:
         """Called right after the single-pass forward was enqueued (it recorded ``dw_ready`` behind its last dW
@@ -140,14 +154,20 @@ class TiedGradSync:
         if self.peer is not None and announced:
             self._dense(hint, hint, self.dw_ready)
 
-    def in_backward(self, dX: torch.Tensor, dW_acc: torch.Tensor, g: torch.Tensor, hint: torch.Tensor) -> None:
-        """Backward of the loss: dX is rescaled in place; the LM-head gradient goes to the exchange."""
+    def in_backward(self, dX: torch.Tensor, dW_acc: torch.Tensor, g: torch.Tensor, hint: torch.Tensor,
+                    formed_outside: bool = False) -> None:
+        """Backward of the loss: dX is rescaled in place; the LM-head gradient goes to the exchange.
+        ``formed_outside``: this loss's forward did not go through :meth:`after_forward` (a ``compute_cross_entropy``
+        chunk): its gradient was just copied into the exchange buffer and needs an exchange of its own, however many
+        such backwards a micro-batch has."""
         if self.peer is not None:
             self._rows = max(self._rows, dX.size(0))
             ops.lmhead_ce_apply_grad(dX, dW_acc, g, hint, skip_dW=True)
-            if self._dense_done:
+            if self._dense_done and not formed_outside:
                 # the exchange already ran with the announced multiplier: leave a wrong announcement visible
-                self.grad_hint_mismatch = (g != hint)
+                # (OR-ed over the micro-batches of an accumulation window until check() reads it)
+                m = (g != hint)
+                self.grad_hint_mismatch = m if self.grad_hint_mismatch is None else (self.grad_hint_mismatch | m)
             else:
                 self._dense(g, hint, None)
             return
@@ -215,6 +235,8 @@ class TiedGradSync:
         if self.peer is not None:
             self.peer.check()
         m = self.grad_hint_mismatch if confirm_multiplier else None
+        if m is not None:
+            self.grad_hint_mismatch = None
         if m is not None and bool(m.any().item()):
             raise RuntimeError("ssi_b200.sync: the dense exchange ran with the announced loss multiplier, but "
                                "backward received a different upstream gradient; announce the right one "

@@ -301,3 +301,134 @@ def test_peer_exchange_world2_matches_single_process_oracle():
     assert out.get("eval_ok") is True
     assert out.get("grads_ok") is True, out.get("why")
     print("NVLS dense reduce:", out.get("nvls"))
+
+
+def _timeout_worker(rank, world, port, out):
+    """Rank 1 arrives 3 s late at an exchange whose wait limit is 1 s."""
+    import time
+
+    from ssi_b200 import _lib
+    from ssi_b200.peer import TiedGradExchange
+
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            device_id=dev)
+    try:
+        V, D = 1024, 128
+        _lib.set_option("dp_timeout_s", 1)
+        px = TiedGradExchange(V, D, max_rows=256, group=dist.group.WORLD, device=dev, nvls=False)
+        one = torch.ones(1, dtype=torch.float32, device=dev)
+
+        def step():
+            px.dw_acc.fill_(float(rank + 1))
+            dW = torch.zeros(V, D, dtype=torch.bfloat16, device=dev)
+            px.exchange(dW, one, one)
+            torch.cuda.synchronize()
+            return dW
+
+        ok_first = bool((step() == 3).all().item())  # 1 + 2: an ordinary exchange
+        dist.barrier()
+        if rank == 1:
+            time.sleep(3.0)
+        late = step()
+        # the rank that waited gave up and marked BOTH ranks; the late rank must not come away with finite numbers
+        nan_everywhere = bool(torch.isnan(late.float()).all().item())
+        flagged = px.timed_out()
+        raised = False
+        try:
+            px.check()
+        except RuntimeError:
+            raised = True
+        _lib.set_option("dp_timeout_s", 600)
+        px.reset()
+        ok_after = bool((step() == 3).all().item()) and not px.timed_out()
+        out[rank] = (ok_first, nan_everywhere, flagged, raised, ok_after)
+        px.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_a_wait_that_times_out_poisons_every_rank_and_reset_recovers():
+    """the device-side wait used to give up after a hard-coded 20 s, marked only the rank that
+    waited (the late rank then read buffers being rewritten and kept finite, wrong gradients), and never recovered.
+    Now the limit is an option (default 10 min), a time-out marks every rank, and reset() is the collective way back."""
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_timeout_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    for rank in (0, 1):
+        assert out.get(rank) == (True, True, True, True, True), (rank, out.get(rank))
+
+
+def _two_chunk_worker(rank, world, port, out):
+    """Two ``compute_cross_entropy`` chunks per micro-batch and rank (what ``compile_loss`` drives), peer exchange."""
+    import ssi_b200
+    from ssi_b200 import ops
+
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    if world == 1:  # in-process on a one-GPU box: the exchange kernels' own-rank path
+        dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=0, world_size=1)
+    else:
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                                device_id=dev)
+    try:
+        V, D, B, S = 3001, 256, 4, 96
+        tin = _inputs(B=B, S=S, V=V, D=D, cfg="c2", seed=17)
+        n_iter = oracle.count_valid(tin["labels"])
+        n_shift = oracle.count_valid(oracle.shift_labels(tin["labels"]))
+        model = TinyDecoder(V, D).to(dev)
+        with torch.no_grad():
+            model.tok_embeddings.weight.copy_(tin["W"])
+        loss_fn = ssi_b200.install(model, process_group=dist.group.WORLD, exchange="peer", max_tokens_per_rank=B * S)
+        model.set_num_output_chunks(2)
+        b = B // world
+        sl = slice(rank * b, (rank + 1) * b)
+        grads = []
+        for _ in range(2):  # twice: the second pass runs on top of the first one's buffers and must repeat it
+            model.zero_grad(set_to_none=True)
+            tok, lab, X = (tin[k][sl].to(dev) for k in ("tokens", "labels", "X"))
+            shifted, _ = ops.label_shift_count(lab.contiguous())
+            chunks = model(tok, X)
+            total = sum(loss_fn.compute_cross_entropy(hc, lc.contiguous())
+                        for hc, lc in zip(chunks, shifted.chunk(2, dim=1)))
+            (total * (n_iter / n_shift)).backward()
+            torch.cuda.synchronize()
+            grads.append(model.tok_embeddings.weight.grad.clone())
+        loss_fn.sync.check()
+        loss_fn.sync.close()
+        tot = (total.detach() * (n_iter / n_shift)).reshape(1).clone()
+        if world > 1:
+            dist.all_reduce(tot)
+        if rank == 0:
+            t_loss, t_dW, _ = _oracle_tiny(tin, [slice(0, B)])
+            ok, why = True, ""
+            try:
+                assert abs(tot.item() - t_loss) <= 2e-3 * abs(t_loss), (tot.item(), t_loss)
+                assert torch.equal(grads[0], grads[1]), "not repeatable"
+                assert_grad_close(grads[1], t_dW, "tied dW, two compute_cross_entropy chunks per rank",
+                                  elem_roundings=DW_ELEM_ROUNDINGS)
+            except AssertionError as e:  # pragma: no cover
+                ok, why = False, str(e)
+            out["ok"], out["why"] = ok, why
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_compute_cross_entropy_backwards_per_micro_batch_world1():
+    """The same on one GPU (world 1): both chunks' gradients must reach the tied weight's .grad."""
+    out = {}
+    _two_chunk_worker(0, 1, _free_port(), out)
+    assert out.get("ok") is True, out.get("why")
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_compute_cross_entropy_backwards_per_micro_batch_are_both_exchanged():
+    """every chunk's LM-head gradient is copied into the one peer-visible fp32 buffer and exchanged
+    from there; the copy of chunk k+1 must wait for the exchange of chunk k (local and remote readers), and every
+    chunk needs its own exchange (the second one used to be taken for "already exchanged in forward")."""
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_two_chunk_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    assert out.get("ok") is True, out.get("why")

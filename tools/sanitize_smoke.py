@@ -1,7 +1,6 @@
-"""Small shapes of every kernel family for compute-sanitizer:
-
-    compute-sanitizer --tool memcheck  python tools/sanitize_smoke.py
-    compute-sanitizer --tool racecheck python tools/sanitize_smoke.py
+"""Small shapes of every kernel family in one process, each checked by its own bounds asserts -- a quick smoke
+run (python tools/sanitize_smoke.py).  It was written as the target of a memory / race checker; this GPU pool refuses
+such tools for good (profiles/r02_sanitizer_refused.log), so it stays as a plain smoke test.  Covered:
 
 the three operand-major forms of the tcgen05 contraction, one single-pass and one recompute micro-batch through
 PathStep (mbarrier / TMEM / cross-CTA protocols, lockstep counters), the K3 sort + segmented reduce, and the
