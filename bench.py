@@ -251,6 +251,96 @@ def grad_checksums(g):
     return torch.stack([v.sum(), (v * w).sum()])
 
 
+def oracle_parity(path, out, tokens, labels, X, dH0, W, world, dev, ignore):
+    """Parity of the TIMED shape against the oracle at any world size: the closed-form fp32 check of
+    tests/test_gpu_full_size.py, evaluated on the GPU tensors with the oracle's own functions where they exist
+    (oracle.tied_linear: bf16 logits like tied_linear.py:25; oracle.shift_labels) --
+      loss    global sum of the per-row CE on bf16 logits / global valid count * num_tokens_iter vs the summed
+              loss_batch of the ranks (ssi/trainer.py:391-395; tt/recipes/full_finetune_distributed.py:844-851,867);
+      dX      256 sampled token rows of THIS rank: (softmax - onehot) * scale rounded to bf16, times W, in fp32;
+      dW      256 vocabulary rows (half of them label ids): every rank forms its fp32 partial G^T X over its rows plus
+              its embedding rows (sum of dH0 rows per token id) with plain torch; the [256, D] partials are
+              all-reduced and compared with weight.grad -- the tied gradient the exchange produced.
+    Errors are reported as the worst |err| / (2^-7 |ref| + 2^-8 max|ref|) (<= 1 passes assert_grad_close) and the
+    relative Frobenius error.  Every rank runs it (collectives inside); rank 0 reports."""
+    import torch
+    import torch.distributed as dist
+
+    from oracle import reference_path as oracle
+
+    V, D = W.shape
+    Xf = X.reshape(-1, D)
+    n_local = Xf.size(0)
+    shifted = oracle.shift_labels(labels).reshape(-1)
+    valid = shifted != ignore
+    cnt = torch.stack([(labels != ignore).sum(), valid.sum()]).to(torch.float64)
+    if world > 1:
+        dist.all_reduce(cnt)
+    n_iter, n_shift = cnt[0].item(), cnt[1].item()
+    scale = n_iter / max(n_shift, 1.0)
+    # ---- one chunked pass of the oracle's forward: per-row logsumexp and the CE sum on bf16 logits
+    lse = torch.zeros(n_local, dtype=torch.float32, device=dev)
+    ce_sum = torch.zeros(1, dtype=torch.float64, device=dev)
+    with torch.no_grad():
+        for r0 in range(0, n_local, 4096):
+            sl = slice(r0, min(r0 + 4096, n_local))
+            logits = oracle.tied_linear(Xf[sl], W).float()  # ce_chunked_output_loss.py:41 upcasts the bf16 logits
+            l = torch.logsumexp(logits, dim=-1)
+            lse[sl] = l
+            v = valid[sl]
+            z = logits.gather(1, shifted[sl].clamp_min(0)[:, None])[:, 0]
+            ce_sum += ((l - z) * v).sum().to(torch.float64)
+            del logits
+        lb = out[0].detach().reshape(1).to(torch.float64).clone()
+        if world > 1:
+            dist.all_reduce(ce_sum)
+            dist.all_reduce(lb)
+        want_loss = ce_sum.item() / max(n_shift, 1.0) * n_iter
+        g = torch.Generator().manual_seed(7)
+
+        def worst(got, ref):
+            got, ref = got.float(), ref.float()
+            bound = ref.abs() * 2.0 ** -7 + ref.abs().max() * 2.0 ** -8
+            return float(((got - ref).abs() / bound).max().item()), rel_fro(got, ref)
+
+        # ---- dX: sampled token rows of this rank
+        rows = torch.randperm(n_local, generator=g)[:256].to(dev)
+        lg = oracle.tied_linear(Xf[rows], W).float()
+        G = torch.softmax(lg, dim=-1)
+        rv = valid[rows]
+        G[torch.arange(rows.numel(), device=dev)[rv], shifted[rows][rv]] -= 1.0
+        G = (G * scale * rv[:, None]).to(torch.bfloat16).float()  # autograd hands bf16 dlogits to the matmuls
+        dx_over, dx_fro = worst(out[1].reshape(-1, D)[rows], G @ W.float())
+        dxs = torch.tensor([dx_over, dx_fro], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dxs, op=dist.ReduceOp.MAX)
+        # ---- dW: the same vocabulary rows on every rank (label ids of rank 0 + random ids)
+        labs = shifted[valid][:128]
+        labs = torch.cat([labs, torch.zeros(128 - labs.numel(), dtype=labs.dtype, device=dev)])
+        if world > 1:
+            dist.broadcast(labs, src=0)
+        vs = torch.unique(torch.cat([labs, torch.randint(0, V, (128,), generator=g).to(dev)]))
+        Xv = Xf[valid].float()
+        Gv = torch.exp((Xv @ W[vs].float().t()).to(torch.bfloat16).float() - lse[valid][:, None])
+        Gv -= (shifted[valid][:, None] == vs[None, :]).float()
+        part = (Gv * scale).to(torch.bfloat16).float().t() @ Xv
+        del Xv, Gv
+        hit = (tokens.reshape(-1)[:, None] == vs[None, :]).float()
+        part += hit.t() @ dH0.reshape(-1, D).float()  # backward of nn.Embedding: the rows of dH0 summed per id
+        del hit
+        if world > 1:
+            dist.all_reduce(part)
+        dw_over, dw_fro = worst(path.weight.grad[vs], part)
+    return {"loss_times_n": float(lb.item()), "loss_times_n_oracle": want_loss,
+            "loss_rel_err": abs(float(lb.item()) - want_loss) / abs(want_loss),
+            "dX_worst_over_bound": float(dxs[0].item()), "dX_rel_frobenius": float(dxs[1].item()),
+            "dW_worst_over_bound": dw_over, "dW_rel_frobenius": dw_fro, "rows": 256 * world,
+            "vocab_rows": int(vs.numel()), "rows_checked_shape": f"{n_local} token rows per rank x {world} ranks",
+            "how": "closed-form fp32 oracle on the timed shape: loss over ALL rows, 256 sampled dX rows per rank (max "
+                   "over ranks), tied dW (LM head + embedding) on sampled vocabulary rows from all-reduced fp32 "
+                   "partials; bound = 2^-7 |ref| + 2^-8 max|ref| (tests/test_gpu_parity.py), <= 1 passes"}
+
+
 def rel_fro(a, b):
     return float(((a.float() - b.float()).norm() / (b.float().norm() + 1e-30)).item())
 
@@ -395,6 +485,16 @@ def run_ours(args):
 
             _ops.free_workspaces()
             torch.cuda.empty_cache()
+        barrier()
+
+    # ---- oracle parity on the timed shape, at every world size (all ranks take part)
+    oracle_blk = None
+    if not args.no_parity:
+        try:
+            oracle_blk = oracle_parity(path, out, tokens, labels, X, dH0, W, world, dev, synth.IGNORE)
+        except Exception as e:  # noqa: BLE001 - report, do not lose the bench line
+            oracle_blk = {"error": f"{type(e).__name__}: {str(e)[:200]}"}
+        torch.cuda.empty_cache()
         barrier()
 
     # ---- forward only (the eval path, ssi/eval.py:27-33): K1 alone
@@ -636,6 +736,8 @@ def run_ours(args):
                           "dX_rel_frobenius": rel_fro(dXs.reshape(ref_dH.shape).cpu(), ref_dH),
                           "dW_rel_frobenius": rel_fro(solo.weight.grad.cpu(), ref_dW),
                           "tolerance": "loss rel <= 1e-3, gradients rel-Frobenius <= 4e-3 (tests/test_gpu_parity.py)"}
+    if oracle_blk is not None:
+        line["parity"] = dict(line.get("parity") or {}, oracle=oracle_blk)
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

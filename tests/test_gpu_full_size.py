@@ -1,4 +1,5 @@
-"""Parity at BASELINE.json's FULL sizes (configs c1-c4, and c5's per-rank share at 8 GPUs) through the C ABI.
+"""Parity at BASELINE.json's FULL sizes (configs c1-c4, and c5's per-rank shares at 8, 4, 2 and 1 GPUs) through the
+C ABI.
 
 The oracle's arithmetic (oracle/reference_path.py: the reference's own torch ops) is too slow on the CPU at these
 sizes, so it is evaluated here on the GPU tensors: the whole-batch loss by the oracle's chunked CE (forward only,
@@ -15,7 +16,9 @@ from test_gpu_parity import DW_ELEM_ROUNDINGS, LOSS_RTOL, assert_grad_close
 
 pytestmark = pytest.mark.gpu
 
-FULL = [("c1", None), ("c2", None), ("c3", None), ("c4", None), ("c5", 8)]  # (config, batch override)
+# (config, batch override): c5 at 8 / 16 / 32 / 64 sequences = the per-rank shapes bench.py times at 8 / 4 / 2 / 1 GPUs
+# (1 / 2 / 4 / 8 row chunks at V = 133,258)
+FULL = [("c1", None), ("c2", None), ("c3", None), ("c4", None), ("c5", 8), ("c5", 16), ("c5", 32), ("c5", 64)]
 
 
 def _run(X, W, shifted, upstream):
@@ -28,7 +31,7 @@ def _run(X, W, shifted, upstream):
     return loss_out, lse, n_valid, dX, dW
 
 
-@pytest.mark.parametrize("name,batch", FULL, ids=[f"{n}" for n, _ in FULL])
+@pytest.mark.parametrize("name,batch", FULL, ids=[n if b is None else f"{n}-{b}seq" for n, b in FULL])
 def test_full_size_parity(name, batch):
     from ssi_b200 import synth
 
