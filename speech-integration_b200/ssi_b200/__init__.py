@@ -14,7 +14,7 @@ Everything computes in ``libssi_b200.so`` (hand-written CUDA, tcgen05/TMEM/TMA);
 """
 from . import _lib, build, ops  # noqa: F401
 from .loss import FusedLinearCrossEntropyLoss, fused_linear_cross_entropy  # noqa: F401
-from .model_hooks import HiddenPassthroughOutput, RMSNormB200, TiedEmbeddingB200, install  # noqa: F401
+from .model_hooks import HiddenPassthroughOutput, RMSNormB200, TiedEmbeddingB200, install, uninstall  # noqa: F401
 
 __all__ = [
     "FusedLinearCrossEntropyLoss",
@@ -23,6 +23,7 @@ __all__ = [
     "TiedEmbeddingB200",
     "RMSNormB200",
     "install",
+    "uninstall",
     "ops",
     "build",
 ]

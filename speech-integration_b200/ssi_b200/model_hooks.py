@@ -204,6 +204,11 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
     ``scale_grads`` and the tied weight's share of ``clip_grad_norm_`` (ssi/trainer.py:404-408) ride along in the kernels
     that write the tied gradient anyway (single-pass mode; with a process group: the peer exchange)."""
     norm = getattr(model, "norm", None)
+    # what uninstall() puts back (kept outside nn.Module's registries: no state-dict keys, no extra parameters);
+    # a second install() on the same model keeps the ORIGINAL parts of the first
+    saved = getattr(model, "_ssi_b200_saved", None) or {
+        "output": getattr(model, "output", None), "tok_embeddings": model.tok_embeddings, "norm": norm,
+        "has_norm": hasattr(model, "norm"), "num_output_chunks": getattr(model, "num_output_chunks", None)}
     fused_norm = None
     if fuse_norm:
         if norm is None or not (hasattr(norm, "scale") and hasattr(norm, "eps")):
@@ -240,4 +245,29 @@ def install(model: nn.Module, num_output_chunks: int = 8, ignore_index: int = -1
         object.__setattr__(emb, "sync", sync)
     if fold_scale_grads:
         attach_fold(loss_fn, emb)
+    saved["loss_fn"] = loss_fn
+    object.__setattr__(model, "_ssi_b200_saved", saved)
     return loss_fn
+
+
+def uninstall(model: nn.Module) -> None:
+    """Undo :func:`install`: ``model.output`` (the ``TiedLinear`` of tt/torchtune/models/llama3_2/
+    _component_builders.py:123), ``model.tok_embeddings``, ``model.norm`` and the chunk count are the objects the model
+    had before, so ``TransformerDecoder.forward`` returns LOGITS again (tt/torchtune/modules/transformer.py:651-661)
+    -- for generation, for a caller that wants ``model.unembed``, or to hand the model back to the reference's own
+    loss.  Parameters were shared all along (same ``tok_embeddings.weight`` / ``norm.scale`` objects), so weights,
+    gradients and optimizer state carry over unchanged.  With a process group this also releases the exchange buffers
+    (collective: every rank must call it).  No-op on a model :func:`install` never touched."""
+    saved = getattr(model, "_ssi_b200_saved", None)
+    if saved is None:
+        return
+    sync = getattr(saved.get("loss_fn"), "sync", None)
+    if sync is not None:
+        sync.close()
+    model.tok_embeddings = saved["tok_embeddings"]
+    model.output = saved["output"]
+    if saved["has_norm"]:
+        model.norm = saved["norm"]
+    if saved["num_output_chunks"] is not None and hasattr(model, "set_num_output_chunks"):
+        model.set_num_output_chunks(saved["num_output_chunks"])
+    object.__delattr__(model, "_ssi_b200_saved")

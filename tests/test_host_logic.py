@@ -246,3 +246,45 @@ def test_install_rejects_option_combinations_that_have_no_kernel():
         ssi_b200.install(M(), replace_embedding=False, fold_scale_grads=True)
     with pytest.raises(ValueError):
         ssi_b200.install(M(), mode="bogus")
+
+
+def test_uninstall_gives_the_logits_path_back():
+    """VERDICT r2 (#6c): install() must be reversible.  After uninstall() the model holds the very objects it had
+    before -- its own output projection (a TiedLinear in the reference, tt/torchtune/models/llama3_2/
+    _component_builders.py:123), embedding module, final norm and chunk count -- so TransformerDecoder.forward returns
+    logits again (tt/torchtune/modules/transformer.py:651-661); parameters were shared all along."""
+    class Norm(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.scale = nn.Parameter(torch.ones(16, dtype=torch.bfloat16))
+            self.eps = 1e-6
+
+        def forward(self, x):
+            return x
+
+    class Tiny(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.tok_embeddings = nn.Embedding(50, 16, dtype=torch.bfloat16)
+            self.norm = Norm()
+            self.output = lambda x: torch.nn.functional.linear(x, self.tok_embeddings.weight)
+            self.num_output_chunks = 0
+
+        def set_num_output_chunks(self, n):
+            self.num_output_chunks = n
+
+    m = Tiny()
+    emb, out, norm, w = m.tok_embeddings, m.output, m.norm, m.tok_embeddings.weight
+    keys = list(m.state_dict().keys())
+    ssi_b200.uninstall(m)  # never installed: nothing happens
+    ssi_b200.install(m, fuse_norm=True)
+    ssi_b200.install(m, replace_norm=True)  # a second install keeps the ORIGINAL parts for uninstall
+    assert isinstance(m.output, ssi_b200.HiddenPassthroughOutput) and m.num_output_chunks == 8
+    assert list(m.state_dict().keys()) == keys
+    ssi_b200.uninstall(m)
+    assert m.tok_embeddings is emb and m.output is out and m.norm is norm and m.tok_embeddings.weight is w
+    assert m.num_output_chunks == 0 and list(m.state_dict().keys()) == keys
+    assert not hasattr(m, "_ssi_b200_saved")
+    h = torch.randn(2, 3, 16).to(torch.bfloat16)
+    assert m.output(h).shape == (2, 3, 50)  # logits again, not hidden states
+    ssi_b200.uninstall(m)  # idempotent
